@@ -1,0 +1,86 @@
+// Shared helpers for libgance_b200.so: error reporting, launch accounting, dtype traits.
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+
+#include "../../include/gance_b200.h"
+
+namespace gance {
+
+// One message buffer per host thread; gance_last_error_string() returns the caller's.
+char* error_buffer();
+int fail(int code, const char* fmt, ...);
+extern std::atomic<unsigned long long> g_launches;
+bool is_initialised();
+
+inline int check_launch(const char* what) {
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    cudaError_t err = cudaGetLastError();
+    if (err != cudaSuccess) {
+        fail(-(int)err, "%s: %s", what, cudaGetErrorString(err));
+        return -(int)err;
+    }
+    return GANCE_OK;
+}
+
+#define GANCE_REQUIRE(cond, code, ...)                 \
+    do {                                               \
+        if (!(cond)) return gance::fail(code, __VA_ARGS__); \
+    } while (0)
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// ---- element-type traits for the bandwidth kernels (fp32 validation mode / bf16 fast mode) ----
+template <typename T>
+struct Vec;  // a 16-byte vector of T
+
+template <>
+struct Vec<float> {
+    static constexpr int N = 4;
+    float4 raw;
+    __device__ __forceinline__ void load(const float* p) { raw = *reinterpret_cast<const float4*>(p); }
+    __device__ __forceinline__ void store(float* p) const { *reinterpret_cast<float4*>(p) = raw; }
+    __device__ __forceinline__ void to_float(float* f) const {
+        f[0] = raw.x; f[1] = raw.y; f[2] = raw.z; f[3] = raw.w;
+    }
+    __device__ __forceinline__ void from_float(const float* f) { raw = make_float4(f[0], f[1], f[2], f[3]); }
+    __device__ __forceinline__ void zero() { raw = make_float4(0.f, 0.f, 0.f, 0.f); }
+};
+
+template <>
+struct Vec<__nv_bfloat16> {
+    static constexpr int N = 8;
+    uint4 raw;
+    __device__ __forceinline__ void load(const __nv_bfloat16* p) { raw = *reinterpret_cast<const uint4*>(p); }
+    __device__ __forceinline__ void store(__nv_bfloat16* p) const { *reinterpret_cast<uint4*>(p) = raw; }
+    __device__ __forceinline__ void to_float(float* f) const {
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            float2 v = __bfloat1622float2(h[i]);
+            f[2 * i] = v.x;
+            f[2 * i + 1] = v.y;
+        }
+    }
+    __device__ __forceinline__ void from_float(const float* f) {
+        __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&raw);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+    }
+    __device__ __forceinline__ void zero() { raw = make_uint4(0u, 0u, 0u, 0u); }
+};
+
+constexpr float kLreluAlpha = 0.2f;
+constexpr float kLreluGain = 1.41421356237309504880f;  // sqrt(2), fused_bias_act 'lrelu' def_gain
+
+__device__ __forceinline__ float bias_lrelu(float v) {
+    return (v > 0.f ? v : v * kLreluAlpha) * kLreluGain;
+}
+
+}  // namespace gance

@@ -1,0 +1,526 @@
+// 3x3 modulated convolution as a tcgen05 / TMEM implicit GEMM fed by TMA (sm_100a).
+//
+// Math (SURVEY.md Appendix A.4 identity, proven in tests/test_oracle_stylegan2.py):
+//   modulated_conv2d_layer(x, w)  ==  conv(x * s, W) * d
+// so ONE weight matrix serves the whole batch and the batch folds into the GEMM M dimension:
+//   D[M = B*H*W pixels, N = Cout] = A[M, K = 9*Cin] * B[N, K]^T,   K ordered (ky, kx, ci)
+// A is never materialised: for tap (ky,kx) and channel chunk c0 the A tile is the NHWC box
+//   x[b0:b0+tb, h0+ky-pad : +th, w0+kx-pad : +tw, c0 : c0+BLOCK_K]
+// which one 4-D TMA load drops into shared memory in exactly the K-major SWIZZLE_128B (or 64B)
+// layout the UMMA shared-memory descriptor wants; out-of-range coordinates are zero-filled by the
+// TMA unit, which is the SAME padding. B tiles are 2-D TMA boxes of the [Cout][9*Cin] weight.
+//
+// CTA = 6 warps, persistent over (m-tile, n-tile) work items:
+//   warp 0   : TMA producer (one elected lane)           smem ring: full[] / empty[] mbarriers
+//   warp 1   : tcgen05.mma issuer (one elected lane), owns the TMEM allocation
+//   warps 2-5: epilogue, one TMEM lane quarter each: tcgen05.ld -> demod * acc + noise + bias ->
+//              leaky-ReLU * sqrt(2) -> (* next layer's style) -> bf16 -> 16-byte NHWC stores
+// Accumulators are double-buffered in TMEM (2 x N_TILE columns) so the epilogue of tile i
+// overlaps the MMAs of tile i+1.
+#include <cuda.h>
+
+#include "common.cuh"
+
+namespace gance {
+
+namespace tc {
+
+constexpr int kTileM = 128;
+constexpr int kThreads = 192;
+constexpr int kUmmaK = 16;  // bf16
+
+struct ConvParams {
+    int batch, h_out, w_out, c_in, c_out, pad;
+    int tile_w, tile_h, tile_b;      // tile_w * tile_h * tile_b == 128 output pixels
+    int tiles_w, tiles_h, tiles_b;   // m-tiles per dimension
+    int n_tiles;                     // c_out / N_TILE
+    int k_chunks;                    // c_in / BLOCK_K
+    const float* demod;
+    const float* noise;
+    long long noise_batch_stride;
+    float noise_strength;
+    const float* bias;
+    const float* next_styles;
+    __nv_bfloat16* out;
+};
+
+// ---- PTX wrappers --------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    const uint32_t addr = smem_u32(bar);
+    uint32_t done;
+    uint32_t spins = 0;
+    do {  // try_wait suspends the thread in hardware until the phase flips or a time-out elapses
+        // A pipeline bug must surface as a launch error, never as a hung GPU: give up after ~seconds.
+        if (++spins == (1u << 26)) __trap();
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t"
+            "}"
+            : "=r"(done)
+            : "r"(addr), "r"(parity)
+            : "memory");
+    } while (!done);
+}
+__device__ __forceinline__ void fence_barrier_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_before() {
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_after() {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void prefetch_tmap(const CUtensorMap* m) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1,
+                                            int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(smem_u32(dst)),
+        "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(dst)),
+        "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)),
+                 "r"(cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]^T ; both operands K-major, bf16, fp32 accumulate.
+__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                          uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(d_tmem),
+        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// Arrive on an mbarrier once every previously issued tcgen05.mma of this thread has completed.
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+                 : "memory");
+}
+// 32 lanes x 32 columns of fp32 accumulator -> 32 registers per thread (thread i = TMEM lane base+i).
+__device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]),
+          "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]),
+          "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// UMMA shared-memory descriptor for a K-major tile whose rows are SWIZZLE_BYTES wide
+// (cute::UMMA::SmemDescriptor, mma_sm100_desc.hpp): start address >> 4 in bits [0,14),
+// LBO (ignored for swizzled K-major, canonical value 1) in [16,30), SBO = 8 rows * row bytes >> 4
+// in [32,46), version = 1 in [46,48), layout type in [61,64): 2 = SWIZZLE_128B, 4 = SWIZZLE_64B.
+template <int SWIZZLE_BYTES>
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
+    constexpr uint64_t layout = SWIZZLE_BYTES == 128 ? 2ull : (SWIZZLE_BYTES == 64 ? 4ull : 6ull);
+    constexpr uint64_t sbo = (8ull * SWIZZLE_BYTES) >> 4;
+    return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | (1ull << 16) | (sbo << 32) | (1ull << 46) | (layout << 61);
+}
+
+// tcgen05 instruction descriptor (cute::UMMA::InstrDescriptor): c_format F32 = 1 @ [4,6),
+// a_format / b_format BF16 = 1 @ [7,10) / [10,13), a_major = b_major = K (0) @ 15 / 16,
+// N >> 3 @ [17,23), M >> 4 @ [24,29).
+__host__ __device__ constexpr uint32_t make_instr_desc(int m, int n) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+template <int N_TILE, int BLOCK_K, int STAGES>
+struct SmemLayout {
+    static constexpr int kABytes = kTileM * BLOCK_K * 2;
+    static constexpr int kBBytes = N_TILE * BLOCK_K * 2;
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kBarrierOffset = STAGES * kStageBytes;
+    static constexpr int kBytes = kBarrierOffset + (2 * STAGES + 4) * 8 + 16 + 1024;  // + alignment slack
+};
+
+struct TileCoord {
+    int n0, b0, h0, w0;
+};
+
+__device__ __forceinline__ TileCoord decode_tile(const ConvParams& p, int tile, int n_tile_size) {
+    TileCoord t;
+    int nt = tile % p.n_tiles;
+    int m = tile / p.n_tiles;
+    int tw = m % p.tiles_w;
+    m /= p.tiles_w;
+    int th = m % p.tiles_h;
+    int tb = m / p.tiles_h;
+    t.n0 = nt * n_tile_size;
+    t.w0 = tw * p.tile_w;
+    t.h0 = th * p.tile_h;
+    t.b0 = tb * p.tile_b;
+    return t;
+}
+
+template <int N_TILE, int BLOCK_K, int STAGES>
+__global__ void __launch_bounds__(kThreads, 1)
+modconv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
+                     const ConvParams p) {
+    using L = SmemLayout<N_TILE, BLOCK_K, STAGES>;
+    constexpr int kSwizzle = BLOCK_K * 2;
+    constexpr uint32_t kTmemCols = 2 * N_TILE < 32 ? 32 : 2 * N_TILE;
+    static_assert((kTmemCols & (kTmemCols - 1)) == 0 && kTmemCols <= 512, "TMEM columns must be a power of two");
+    static_assert(L::kABytes % 1024 == 0 && L::kBBytes % 1024 == 0, "stage buffers must stay 1024-byte aligned");
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarrierOffset);
+    uint64_t* empty_bar = full_bar + STAGES;
+    uint64_t* tmem_full_bar = empty_bar + STAGES;
+    uint64_t* tmem_empty_bar = tmem_full_bar + 2;
+    uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmap_x);
+        prefetch_tmap(&tmap_w);
+        for (int i = 0; i < STAGES; ++i) {
+            mbar_init(full_bar + i, 1);
+            mbar_init(empty_bar + i, 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(tmem_full_bar + i, 1);
+            mbar_init(tmem_empty_bar + i, 4);  // one arrival per epilogue warp
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_base_slot, kTmemCols);
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_base_slot;
+
+    const int total_tiles = p.tiles_b * p.tiles_h * p.tiles_w * p.n_tiles;
+    const int k_iters = 9 * p.k_chunks;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ===== TMA producer =====
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+                const TileCoord t = decode_tile(p, tile, N_TILE);
+                for (int tap = 0; tap < 9; ++tap) {
+                    const int dy = tap / 3 - p.pad, dx = tap % 3 - p.pad;
+                    for (int kc = 0; kc < p.k_chunks; ++kc) {
+                        mbar_wait(empty_bar + stage, phase ^ 1u);
+                        uint8_t* a_dst = smem + stage * L::kStageBytes;
+                        uint8_t* b_dst = a_dst + L::kABytes;
+                        mbar_expect_tx(full_bar + stage, L::kStageBytes);
+                        tma_load_4d(a_dst, &tmap_x, full_bar + stage, kc * BLOCK_K, t.w0 + dx, t.h0 + dy, t.b0);
+                        tma_load_2d(b_dst, &tmap_w, full_bar + stage, tap * p.c_in + kc * BLOCK_K, t.n0);
+                        if (++stage == STAGES) {
+                            stage = 0;
+                            phase ^= 1u;
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // ===== MMA issuer =====
+            constexpr uint32_t idesc = make_instr_desc(kTileM, N_TILE);
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+                mbar_wait(tmem_empty_bar + acc, acc_phase ^ 1u);  // epilogue has drained this accumulator
+                tcgen05_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * N_TILE);
+                for (int it = 0; it < k_iters; ++it) {
+                    mbar_wait(full_bar + stage, phase);  // TMA bytes have landed
+                    tcgen05_fence_after();
+                    const uint32_t a_addr = smem_u32(smem + stage * L::kStageBytes);
+                    const uint64_t a_desc = make_smem_desc<kSwizzle>(a_addr);
+                    const uint64_t b_desc = make_smem_desc<kSwizzle>(a_addr + L::kABytes);
+#pragma unroll
+                    for (int k = 0; k < BLOCK_K / kUmmaK; ++k) {
+                        // advance along K inside the swizzle atom: +32 bytes = +2 in the >>4 address field
+                        umma_bf16(d_tmem, a_desc + (uint64_t)(k * 2), b_desc + (uint64_t)(k * 2), idesc,
+                                  (it | k) != 0 ? 1u : 0u);
+                    }
+                    umma_commit(empty_bar + stage);  // frees the smem slot when these MMAs retire
+                    if (it == k_iters - 1) umma_commit(tmem_full_bar + acc);
+                    if (++stage == STAGES) {
+                        stage = 0;
+                        phase ^= 1u;
+                    }
+                }
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1u;
+            }
+        }
+    } else {
+        // ===== epilogue warps: TMEM lane quarter = warp % 4 =====
+        const int quarter = warp & 3;
+        const int row = quarter * 32 + lane;
+        const int wl = row % p.tile_w;
+        const int hl = (row / p.tile_w) % p.tile_h;
+        const int bl = row / (p.tile_w * p.tile_h);
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            const TileCoord t = decode_tile(p, tile, N_TILE);
+            const int b = t.b0 + bl, h = t.h0 + hl, w = t.w0 + wl;
+            const bool valid = b < p.batch && h < p.h_out && w < p.w_out;
+            float nz = 0.f;
+            if (valid && p.noise != nullptr)
+                nz = __ldg(p.noise + (size_t)b * p.noise_batch_stride + (size_t)h * p.w_out + w) * p.noise_strength;
+            const size_t bc = (size_t)(valid ? b : 0) * p.c_out + t.n0;
+            const float4* demod4 = reinterpret_cast<const float4*>(p.demod + bc);
+            const float4* bias4 = reinterpret_cast<const float4*>(p.bias + t.n0);
+            const float4* style4 = p.next_styles ? reinterpret_cast<const float4*>(p.next_styles + bc) : nullptr;
+            __nv_bfloat16* dst = p.out + (((size_t)(valid ? b : 0) * p.h_out + (valid ? h : 0)) * p.w_out +
+                                          (valid ? w : 0)) * p.c_out + t.n0;
+
+            mbar_wait(tmem_full_bar + acc, acc_phase);
+            tcgen05_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * N_TILE);
+#pragma unroll 1
+            for (int c0 = 0; c0 < N_TILE; c0 += 32) {
+                uint32_t r[32];
+                tmem_ld_32x32(taddr + (uint32_t)c0, r);
+                tmem_ld_wait();
+                if (valid) {
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {  // 8 channels -> one 16-byte store
+                        float v[8];
+#pragma unroll
+                        for (int q = 0; q < 2; ++q) {
+                            const int idx = (c0 >> 2) + g * 2 + q;
+                            const float4 d = __ldg(demod4 + idx);
+                            const float4 bs = __ldg(bias4 + idx);
+                            float o0 = bias_lrelu(fmaf(__uint_as_float(r[g * 8 + q * 4 + 0]), d.x, nz + bs.x));
+                            float o1 = bias_lrelu(fmaf(__uint_as_float(r[g * 8 + q * 4 + 1]), d.y, nz + bs.y));
+                            float o2 = bias_lrelu(fmaf(__uint_as_float(r[g * 8 + q * 4 + 2]), d.z, nz + bs.z));
+                            float o3 = bias_lrelu(fmaf(__uint_as_float(r[g * 8 + q * 4 + 3]), d.w, nz + bs.w));
+                            if (style4 != nullptr) {
+                                const float4 s = __ldg(style4 + idx);
+                                o0 *= s.x; o1 *= s.y; o2 *= s.z; o3 *= s.w;
+                            }
+                            v[q * 4 + 0] = o0; v[q * 4 + 1] = o1; v[q * 4 + 2] = o2; v[q * 4 + 3] = o3;
+                        }
+                        Vec<__nv_bfloat16> packed;
+                        packed.from_float(v);
+                        packed.store(dst + c0 + g * 8);
+                    }
+                }
+            }
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tmem_empty_bar + acc);
+            acc ^= 1;
+            if (acc == 0) acc_phase ^= 1u;
+        }
+    }
+
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tcgen05_fence_after();
+        tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
+// ---- host side -------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn g_encode_tiled = nullptr;
+static int g_num_sms = 148;
+
+template <int N_TILE, int BLOCK_K, int STAGES>
+static int configure() {
+    using L = SmemLayout<N_TILE, BLOCK_K, STAGES>;
+    cudaError_t err = cudaFuncSetAttribute(modconv3x3_tc_kernel<N_TILE, BLOCK_K, STAGES>,
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes);
+    if (err != cudaSuccess)
+        return fail(-(int)err, "cudaFuncSetAttribute(modconv3x3_tc<%d,%d,%d>, %d B): %s", N_TILE, BLOCK_K, STAGES,
+                    L::kBytes, cudaGetErrorString(err));
+    return GANCE_OK;
+}
+
+static int make_tmap(CUtensorMap* map, const void* base, int rank, const cuuint64_t* dims,
+                     const cuuint64_t* strides_bytes, const cuuint32_t* box, int swizzle_bytes) {
+    cuuint32_t elem_strides[5] = {1, 1, 1, 1, 1};
+    CUtensorMapSwizzle sw = swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                                                 : (swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                                                                        : CU_TENSOR_MAP_SWIZZLE_32B);
+    CUresult rc = g_encode_tiled(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base),
+                                 dims, strides_bytes, box, elem_strides, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (rc != CUDA_SUCCESS) return fail(GANCE_E_DRIVER, "cuTensorMapEncodeTiled failed with CUresult %d", (int)rc);
+    return GANCE_OK;
+}
+
+template <int N_TILE, int BLOCK_K, int STAGES>
+static int launch(const ConvParams& p, const void* x, const void* weight, int h_in, int w_in, cudaStream_t stream) {
+    using L = SmemLayout<N_TILE, BLOCK_K, STAGES>;
+    CUtensorMap tmap_x, tmap_w;
+    {
+        cuuint64_t dims[4] = {(cuuint64_t)p.c_in, (cuuint64_t)w_in, (cuuint64_t)h_in, (cuuint64_t)p.batch};
+        cuuint64_t strides[3] = {(cuuint64_t)p.c_in * 2, (cuuint64_t)w_in * p.c_in * 2,
+                                 (cuuint64_t)h_in * w_in * p.c_in * 2};
+        cuuint32_t box[4] = {(cuuint32_t)BLOCK_K, (cuuint32_t)p.tile_w, (cuuint32_t)p.tile_h, (cuuint32_t)p.tile_b};
+        int rc = make_tmap(&tmap_x, x, 4, dims, strides, box, BLOCK_K * 2);
+        if (rc != GANCE_OK) return rc;
+    }
+    {
+        cuuint64_t dims[2] = {(cuuint64_t)9 * p.c_in, (cuuint64_t)p.c_out};
+        cuuint64_t strides[1] = {(cuuint64_t)9 * p.c_in * 2};
+        cuuint32_t box[2] = {(cuuint32_t)BLOCK_K, (cuuint32_t)N_TILE};
+        int rc = make_tmap(&tmap_w, weight, 2, dims, strides, box, BLOCK_K * 2);
+        if (rc != GANCE_OK) return rc;
+    }
+    const int total_tiles = p.tiles_b * p.tiles_h * p.tiles_w * p.n_tiles;
+    const int grid = total_tiles < g_num_sms ? total_tiles : g_num_sms;
+    modconv3x3_tc_kernel<N_TILE, BLOCK_K, STAGES><<<grid, kThreads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
+    return check_launch("modconv3x3_tc_kernel");
+}
+
+}  // namespace tc
+
+int init_tensor_core_path() {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t err = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (err != cudaSuccess || qres != cudaDriverEntryPointSuccess || fn == nullptr)
+        return fail(GANCE_E_DRIVER, "cuTensorMapEncodeTiled is not exported by this driver (%s)",
+                    err == cudaSuccess ? "symbol not found" : cudaGetErrorString(err));
+    tc::g_encode_tiled = reinterpret_cast<tc::EncodeTiledFn>(fn);
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&tc::g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    int rc;
+    if ((rc = tc::configure<256, 64, 4>()) != GANCE_OK) return rc;
+    if ((rc = tc::configure<128, 64, 6>()) != GANCE_OK) return rc;
+    if ((rc = tc::configure<64, 64, 8>()) != GANCE_OK) return rc;
+    if ((rc = tc::configure<32, 64, 8>()) != GANCE_OK) return rc;
+    if ((rc = tc::configure<32, 32, 8>()) != GANCE_OK) return rc;
+    return GANCE_OK;
+}
+
+int launch_modconv3x3_f32(const float* x, int batch, int h_out, int w_out, int c_in, int c_out, int pad,
+                          const float* weight, const float* demod, const float* noise,
+                          long long noise_batch_stride, float noise_strength, const float* bias,
+                          const float* next_styles, float* out, cudaStream_t stream);
+
+}  // namespace gance
+
+using namespace gance;
+
+extern "C" int gance_modconv3x3(const void* x, int dtype, int batch, int h_out, int w_out, int c_in, int c_out,
+                                int pad, const void* weight, const float* demod, const float* noise,
+                                long long noise_batch_stride, float noise_strength, const float* bias,
+                                const float* next_styles, void* out, void* stream) {
+    GANCE_REQUIRE(is_initialised(), GANCE_E_NOT_INIT, "gance_init() has not been called");
+    GANCE_REQUIRE(x && weight && demod && bias && out, GANCE_E_NULL, "gance_modconv3x3: NULL pointer");
+    GANCE_REQUIRE(batch > 0 && h_out > 0 && w_out > 0 && c_in > 0 && c_out > 0 && (pad == 0 || pad == 1),
+                  GANCE_E_SHAPE, "gance_modconv3x3: shape B=%d H=%d W=%d Cin=%d Cout=%d pad=%d", batch, h_out, w_out,
+                  c_in, c_out, pad);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (dtype == GANCE_F32)
+        return launch_modconv3x3_f32((const float*)x, batch, h_out, w_out, c_in, c_out, pad, (const float*)weight,
+                                     demod, noise, noise_batch_stride, noise_strength, bias, next_styles,
+                                     (float*)out, s);
+    GANCE_REQUIRE(dtype == GANCE_BF16, GANCE_E_DTYPE, "gance_modconv3x3: dtype %d", dtype);
+    GANCE_REQUIRE(c_in % 32 == 0 && c_out % 32 == 0, GANCE_E_SHAPE,
+                  "gance_modconv3x3: the tcgen05 path needs Cin %% 32 == 0 and Cout %% 32 == 0 (got %d, %d)", c_in,
+                  c_out);
+    GANCE_REQUIRE(aligned16(x) && aligned16(weight) && aligned16(out) && aligned16(demod) && aligned16(bias) &&
+                      aligned16(next_styles),
+                  GANCE_E_ALIGN, "gance_modconv3x3: pointers must be 16-byte aligned");
+
+    tc::ConvParams p;
+    p.batch = batch; p.h_out = h_out; p.w_out = w_out; p.c_in = c_in; p.c_out = c_out; p.pad = pad;
+    // 128 output pixels per tile: as wide as the image allows (<= 16), then rows, then samples.
+    p.tile_w = w_out >= 16 ? 16 : w_out;
+    GANCE_REQUIRE((p.tile_w & (p.tile_w - 1)) == 0, GANCE_E_SHAPE, "gance_modconv3x3: W=%d (< 16) must be a power of two",
+                  w_out);
+    int rows = tc::kTileM / p.tile_w;
+    p.tile_h = h_out >= rows ? rows : h_out;
+    GANCE_REQUIRE(rows % p.tile_h == 0, GANCE_E_SHAPE, "gance_modconv3x3: H=%d does not tile 128 pixels", h_out);
+    p.tile_b = rows / p.tile_h;
+    p.tiles_w = (w_out + p.tile_w - 1) / p.tile_w;
+    p.tiles_h = (h_out + p.tile_h - 1) / p.tile_h;
+    p.tiles_b = (batch + p.tile_b - 1) / p.tile_b;
+    p.demod = demod; p.noise = noise; p.noise_batch_stride = noise_batch_stride; p.noise_strength = noise_strength;
+    p.bias = bias; p.next_styles = next_styles; p.out = (__nv_bfloat16*)out;
+    const int h_in = h_out + 2 - 2 * pad, w_in = w_out + 2 - 2 * pad;
+    const int m_tiles = p.tiles_w * p.tiles_h * p.tiles_b;
+
+    if (c_in % 64 != 0) {  // Cin = 32 (1024^2 Conv1 in config-f): 64-byte rows, SWIZZLE_64B
+        GANCE_REQUIRE(c_out % 32 == 0, GANCE_E_SHAPE, "Cout %d", c_out);
+        p.n_tiles = c_out / 32; p.k_chunks = c_in / 32;
+        return tc::launch<32, 32, 8>(p, x, weight, h_in, w_in, s);
+    }
+    p.k_chunks = c_in / 64;
+    if (c_out % 256 == 0 && m_tiles >= 148) {
+        p.n_tiles = c_out / 256;
+        return tc::launch<256, 64, 4>(p, x, weight, h_in, w_in, s);
+    }
+    if (c_out % 128 == 0) {
+        p.n_tiles = c_out / 128;
+        return tc::launch<128, 64, 6>(p, x, weight, h_in, w_in, s);
+    }
+    if (c_out % 64 == 0) {
+        p.n_tiles = c_out / 64;
+        return tc::launch<64, 64, 8>(p, x, weight, h_in, w_in, s);
+    }
+    p.n_tiles = c_out / 32;
+    return tc::launch<32, 64, 8>(p, x, weight, h_in, w_in, s);
+}
+
+extern "C" int gance_modconv3x3_up2_fir(const void* x, int dtype, int batch, int h_in, int w_in, int c_in,
+                                        int c_out, const float* styles, const void* weight, const float* demod,
+                                        const float* noise, long long noise_batch_stride, float noise_strength,
+                                        const float* bias, const float* next_styles, void* scratch, void* out,
+                                        void* stream) {
+    GANCE_REQUIRE(scratch != nullptr, GANCE_E_NULL, "gance_modconv3x3_up2_fir: scratch is NULL");
+    int rc = gance_upfir2x_pad(x, dtype, batch, h_in, w_in, c_in, styles, scratch, stream);
+    if (rc != GANCE_OK) return rc;
+    return gance_modconv3x3(scratch, dtype, batch, 2 * h_in, 2 * w_in, c_in, c_out, /*pad=*/0, weight, demod, noise,
+                            noise_batch_stride, noise_strength, bias, next_styles, out, stream);
+}

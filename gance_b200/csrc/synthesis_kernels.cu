@@ -1,0 +1,529 @@
+// Bandwidth-bound and small kernels of G_mapping / G_synthesis, plus the fp32 validation-mode
+// convolution. Everything is NHWC; T is float (validation mode) or __nv_bfloat16 (fast mode).
+// Reference semantics: SURVEY.md Appendix A.4 (NVlabs/stylegan2 networks_stylegan2.py,
+// upfirdn_2d.py, fused_bias_act.py, tfutil.convert_images_to_uint8).
+#include "common.cuh"
+
+namespace gance {
+
+// ------------------------------------------------------------------------------------------------
+// G_mapping + truncation. One CTA per latent; 512 threads, thread j owns output feature j.
+// W is [layer][in][out] so the inner loop reads a coalesced row of W per input feature.
+// ------------------------------------------------------------------------------------------------
+constexpr int kLatent = 512;
+
+__global__ void __launch_bounds__(kLatent) mapping_kernel(const float* __restrict__ z,
+                                                          const float* __restrict__ weights,
+                                                          const float* __restrict__ biases,
+                                                          const float* __restrict__ dlatent_avg,
+                                                          float psi, int num_ws,
+                                                          float* __restrict__ wplus) {
+    __shared__ float x[kLatent];
+    __shared__ float red[kLatent / 32];
+    const int b = blockIdx.x, j = threadIdx.x;
+    float v = z[(size_t)b * kLatent + j];
+    // normalize_2nd_moment: x * rsqrt(mean(x^2) + 1e-8)
+    float sq = v * v;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+    if ((j & 31) == 0) red[j >> 5] = sq;
+    __syncthreads();
+    float total = 0.f;
+#pragma unroll
+    for (int i = 0; i < kLatent / 32; ++i) total += red[i];
+    v *= rsqrtf(total * (1.0f / kLatent) + 1e-8f);
+    x[j] = v;
+    __syncthreads();
+    for (int layer = 0; layer < 8; ++layer) {
+        const float* w = weights + (size_t)layer * kLatent * kLatent + j;
+        float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
+#pragma unroll 4
+        for (int k = 0; k < kLatent; k += 4) {
+            acc0 = fmaf(x[k], __ldg(w + (size_t)k * kLatent), acc0);
+            acc1 = fmaf(x[k + 1], __ldg(w + (size_t)(k + 1) * kLatent), acc1);
+            acc2 = fmaf(x[k + 2], __ldg(w + (size_t)(k + 2) * kLatent), acc2);
+            acc3 = fmaf(x[k + 3], __ldg(w + (size_t)(k + 3) * kLatent), acc3);
+        }
+        float out = bias_lrelu((acc0 + acc1) + (acc2 + acc3) + biases[layer * kLatent + j]);
+        __syncthreads();
+        x[j] = out;
+        __syncthreads();
+    }
+    float w_out = x[j];
+    if (psi != 1.0f) {  // G_main 'Truncation': lerp(dlatent_avg, w, psi)
+        float avg = dlatent_avg[j];
+        w_out = avg + (w_out - avg) * psi;
+    }
+    for (int l = 0; l < num_ws; ++l) wplus[((size_t)b * num_ws + l) * kLatent + j] = w_out;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Style affine + demodulation coefficients. One CTA per sample.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) style_demod_kernel(const float* __restrict__ wplus, int num_ws,
+                                                          int w_index,
+                                                          const float* __restrict__ mod_weight,
+                                                          const float* __restrict__ mod_bias,
+                                                          const float* __restrict__ wsq, int c_in,
+                                                          int c_out, float* __restrict__ styles,
+                                                          float* __restrict__ demod) {
+    __shared__ float w[kLatent];
+    __shared__ float s2[kLatent];
+    const int b = blockIdx.x;
+    const float* src = wplus + ((size_t)b * num_ws + w_index) * kLatent;
+    for (int k = threadIdx.x; k < kLatent; k += blockDim.x) w[k] = src[k];
+    __syncthreads();
+    for (int ci = threadIdx.x; ci < c_in; ci += blockDim.x) {
+        float acc0 = 0.f, acc1 = 0.f;
+        for (int k = 0; k < kLatent; k += 2) {
+            acc0 = fmaf(w[k], __ldg(mod_weight + (size_t)k * c_in + ci), acc0);
+            acc1 = fmaf(w[k + 1], __ldg(mod_weight + (size_t)(k + 1) * c_in + ci), acc1);
+        }
+        float s = acc0 + acc1 + mod_bias[ci] + 1.0f;
+        styles[(size_t)b * c_in + ci] = s;
+        s2[ci] = s * s;
+    }
+    if (demod == nullptr) return;
+    __syncthreads();
+    for (int co = threadIdx.x; co < c_out; co += blockDim.x) {
+        float acc0 = 0.f, acc1 = 0.f;
+        for (int ci = 0; ci < c_in; ci += 2) {
+            acc0 = fmaf(s2[ci], __ldg(wsq + (size_t)ci * c_out + co), acc0);
+            acc1 = fmaf(s2[ci + 1], __ldg(wsq + (size_t)(ci + 1) * c_out + co), acc1);
+        }
+        demod[(size_t)b * c_out + co] = rsqrtf(acc0 + acc1 + 1e-8f);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// const * style
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void const_input_kernel(const float* __restrict__ konst, const float* __restrict__ styles,
+                                   int batch, int channels, T* __restrict__ out) {
+    constexpr int V = Vec<T>::N;
+    const int vec_per_pixel = channels / V;
+    const size_t total = (size_t)batch * 16 * vec_per_pixel;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total;
+         i += (size_t)gridDim.x * blockDim.x) {
+        int cv = (int)(i % vec_per_pixel);
+        size_t rest = i / vec_per_pixel;
+        int p = (int)(rest % 16);
+        int b = (int)(rest / 16);
+        float f[V];
+#pragma unroll
+        for (int k = 0; k < V; ++k)
+            f[k] = konst[p * channels + cv * V + k] * styles[(size_t)b * channels + cv * V + k];
+        Vec<T> v;
+        v.from_float(f);
+        v.store(out + ((size_t)b * 16 + p) * channels + cv * V);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// 2x FIR upsample with one sample of apron: u [B,2H+2,2W+2,C].
+// One thread = one 16-byte channel vector of a 2x2 output quad, built from the 2x2 input
+// neighbourhood x[a-1..a, b-1..b]; per axis even taps (.75,.25), odd taps (.25,.75).
+// Reads are coalesced along C and each input vector is re-read by 4 quads out of L1/L2.
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) upfir2x_pad_kernel(const T* __restrict__ x, int batch, int h, int w,
+                                                          int channels, const float* __restrict__ styles,
+                                                          T* __restrict__ u) {
+    constexpr int V = Vec<T>::N;
+    const int vec_per_pixel = channels / V;
+    const int qh = h + 1, qw = w + 1;
+    const int uh = 2 * h + 2, uw = 2 * w + 2;
+    const size_t total = (size_t)batch * qh * qw * vec_per_pixel;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total;
+         i += (size_t)gridDim.x * blockDim.x) {
+        int cv = (int)(i % vec_per_pixel);
+        size_t rest = i / vec_per_pixel;
+        int bq = (int)(rest % qw);
+        rest /= qw;
+        int aq = (int)(rest % qh);
+        int b = (int)(rest / qh);
+        float in[2][2][V];
+#pragma unroll
+        for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+            for (int dx = 0; dx < 2; ++dx) {
+                int yy = aq - 1 + dy, xx = bq - 1 + dx;
+                Vec<T> v;
+                if (yy >= 0 && yy < h && xx >= 0 && xx < w)
+                    v.load(x + (((size_t)b * h + yy) * w + xx) * channels + cv * V);
+                else
+                    v.zero();
+                v.to_float(in[dy][dx]);
+            }
+        float s[V];
+#pragma unroll
+        for (int k = 0; k < V; ++k) s[k] = styles ? styles[(size_t)b * channels + cv * V + k] : 1.0f;
+#pragma unroll
+        for (int py = 0; py < 2; ++py) {
+            const float wy0 = py == 0 ? 0.75f : 0.25f, wy1 = 1.0f - wy0;
+#pragma unroll
+            for (int px = 0; px < 2; ++px) {
+                const float wx0 = px == 0 ? 0.75f : 0.25f, wx1 = 1.0f - wx0;
+                float out[V];
+#pragma unroll
+                for (int k = 0; k < V; ++k) {
+                    float top = in[0][0][k] * wx0 + in[0][1][k] * wx1;
+                    float bot = in[1][0][k] * wx0 + in[1][1][k] * wx1;
+                    out[k] = (top * wy0 + bot * wy1) * s[k];
+                }
+                Vec<T> v;
+                v.from_float(out);
+                v.store(u + (((size_t)b * uh + 2 * aq + py) * uw + 2 * bq + px) * channels + cv * V);
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// ToRGB (1x1 modulated conv, no demod) + bias + skip upsample-add (+ uint8 conversion).
+// A group of LANES lanes owns one pixel and splits its channels in 16-byte vectors, so a warp
+// reads 32 consecutive 16-byte vectors: fully coalesced. wmod[c][j] = styles[b,c]*weight[c,j]
+// sits in shared memory (one sample per CTA row of the grid).
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float4 upsample_tap(const float* __restrict__ y_prev, int b, int hp, int wp,
+                                               int h, int w) {
+    // upsample_2d(k=[1,3,3,1]): y[2a] = .25 p[a-1] + .75 p[a]; y[2a+1] = .75 p[a] + .25 p[a+1]
+    const int a = h >> 1, c = w >> 1;
+    const int a2 = (h & 1) ? a + 1 : a - 1, c2 = (w & 1) ? c + 1 : c - 1;
+    const float4* base = reinterpret_cast<const float4*>(y_prev) + (size_t)b * hp * wp;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4 p00 = __ldg(base + (size_t)a * wp + c);
+    acc.x = 0.5625f * p00.x; acc.y = 0.5625f * p00.y; acc.z = 0.5625f * p00.z;
+    if (c2 >= 0 && c2 < wp) {
+        const float4 p = __ldg(base + (size_t)a * wp + c2);
+        acc.x += 0.1875f * p.x; acc.y += 0.1875f * p.y; acc.z += 0.1875f * p.z;
+    }
+    if (a2 >= 0 && a2 < hp) {
+        const float4 p = __ldg(base + (size_t)a2 * wp + c);
+        acc.x += 0.1875f * p.x; acc.y += 0.1875f * p.y; acc.z += 0.1875f * p.z;
+        if (c2 >= 0 && c2 < wp) {
+            const float4 q = __ldg(base + (size_t)a2 * wp + c2);
+            acc.x += 0.0625f * q.x; acc.y += 0.0625f * q.y; acc.z += 0.0625f * q.z;
+        }
+    }
+    return acc;
+}
+
+__device__ __forceinline__ uint8_t to_u8(float v) {
+    // convert_images_to_uint8: v*127.5 + 128, saturate_cast<uint8> = clamp then truncate
+    float s = fmaf(v, 127.5f, 128.0f);
+    s = fminf(fmaxf(s, 0.0f), 255.0f);
+    return (uint8_t)(int)s;
+}
+
+template <typename T, int LANES>
+__global__ void __launch_bounds__(256) torgb_skip_kernel(const T* __restrict__ x, int h, int w, int channels,
+                                                         const float* __restrict__ styles,
+                                                         const float* __restrict__ weight,
+                                                         const float* __restrict__ bias,
+                                                         const float* __restrict__ y_prev,
+                                                         float* __restrict__ y_out,
+                                                         uint8_t* __restrict__ frames) {
+    constexpr int V = Vec<T>::N;
+    extern __shared__ float wmod[];  // [channels][3]
+    const int b = blockIdx.y;
+    for (int i = threadIdx.x; i < channels * 3; i += blockDim.x)
+        wmod[i] = styles[(size_t)b * channels + i / 3] * weight[i];
+    __syncthreads();
+    const int pixels = h * w;
+    const int group = threadIdx.x / LANES, lane = threadIdx.x % LANES;
+    const int groups_per_block = blockDim.x / LANES;
+    const int vec_per_pixel = channels / V;
+    // the loop bound is CTA-uniform so the group shuffles below always see a full warp
+    for (int base = blockIdx.x * groups_per_block; base < pixels; base += gridDim.x * groups_per_block) {
+        const int p = base + group;
+        const bool valid = p < pixels;
+        const T* px = x + ((size_t)b * pixels + (valid ? p : 0)) * channels;
+        float r = 0.f, g = 0.f, bl = 0.f;
+        for (int cv = lane; valid && cv < vec_per_pixel; cv += LANES) {
+            Vec<T> v;
+            v.load(px + cv * V);
+            float f[V];
+            v.to_float(f);
+#pragma unroll
+            for (int k = 0; k < V; ++k) {
+                const float* wm = wmod + (cv * V + k) * 3;
+                r = fmaf(f[k], wm[0], r);
+                g = fmaf(f[k], wm[1], g);
+                bl = fmaf(f[k], wm[2], bl);
+            }
+        }
+#pragma unroll
+        for (int o = LANES / 2; o > 0; o >>= 1) {
+            r += __shfl_xor_sync(0xffffffffu, r, o);
+            g += __shfl_xor_sync(0xffffffffu, g, o);
+            bl += __shfl_xor_sync(0xffffffffu, bl, o);
+        }
+        if (lane == 0 && valid) {
+            r += bias[0]; g += bias[1]; bl += bias[2];
+            const int hh = p / w, ww = p % w;
+            if (y_prev != nullptr) {
+                float4 up = upsample_tap(y_prev, b, h >> 1, w >> 1, hh, ww);
+                r += up.x; g += up.y; bl += up.z;
+            }
+            if (y_out != nullptr)
+                reinterpret_cast<float4*>(y_out)[(size_t)b * pixels + p] = make_float4(r, g, bl, 0.f);
+            if (frames != nullptr) {
+                uint8_t* f = frames + ((size_t)b * pixels + p) * 3;
+                f[0] = to_u8(r); f[1] = to_u8(g); f[2] = to_u8(bl);
+            }
+        }
+    }
+}
+
+__global__ void to_uint8_kernel(const float4* __restrict__ y, size_t pixels, uint8_t* __restrict__ frames) {
+    for (size_t p = blockIdx.x * (size_t)blockDim.x + threadIdx.x; p < pixels;
+         p += (size_t)gridDim.x * blockDim.x) {
+        float4 v = y[p];
+        frames[p * 3 + 0] = to_u8(v.x);
+        frames[p * 3 + 1] = to_u8(v.y);
+        frames[p * 3 + 2] = to_u8(v.z);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// fp32 validation-mode 3x3 convolution on CUDA cores (the numerical yard-stick for the tcgen05
+// path). CTA = 8x8 output pixels x 64 output channels; thread = 4 pixels x 4 channels;
+// input channels are staged through shared memory 8 at a time. Weights are HWIO (TF layout).
+// ------------------------------------------------------------------------------------------------
+constexpr int kF32TileP = 8;    // 8x8 pixels
+constexpr int kF32TileC = 64;   // output channels per CTA
+constexpr int kF32ChunkK = 8;   // input channels per smem stage
+
+__global__ void __launch_bounds__(256) modconv3x3_f32_kernel(
+    const float* __restrict__ x, int batch, int h_out, int w_out, int c_in, int c_out, int pad,
+    const float* __restrict__ weight, const float* __restrict__ demod, const float* __restrict__ noise,
+    long long noise_batch_stride, float noise_strength, const float* __restrict__ bias,
+    const float* __restrict__ next_styles, float* __restrict__ out) {
+    __shared__ float xs[kF32TileP + 2][kF32TileP + 2][kF32ChunkK];
+    __shared__ __align__(16) float ws[9][kF32ChunkK][kF32TileC];
+    const int h_in = h_out + 2 - 2 * pad, w_in = w_out + 2 - 2 * pad;
+    const int tiles_w = (w_out + kF32TileP - 1) / kF32TileP;
+    const int tile_h0 = (blockIdx.x / tiles_w) * kF32TileP, tile_w0 = (blockIdx.x % tiles_w) * kF32TileP;
+    const int co0 = blockIdx.y * kF32TileC;
+    const int b = blockIdx.z;
+    const int cg = threadIdx.x % 16;  // 4 output channels: co0 + cg*4 ..
+    const int pg = threadIdx.x / 16;  // 4 pixels: row (pg/2), cols (pg%2)*4 ..
+    const int prow = pg / 2, pcol0 = (pg % 2) * 4;
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+    for (int c0 = 0; c0 < c_in; c0 += kF32ChunkK) {
+        for (int i = threadIdx.x; i < (kF32TileP + 2) * (kF32TileP + 2) * kF32ChunkK; i += blockDim.x) {
+            int k = i % kF32ChunkK;
+            int xx = (i / kF32ChunkK) % (kF32TileP + 2);
+            int yy = i / (kF32ChunkK * (kF32TileP + 2));
+            int gy = tile_h0 + yy - pad, gx = tile_w0 + xx - pad;
+            float v = 0.f;
+            if (gy >= 0 && gy < h_in && gx >= 0 && gx < w_in && c0 + k < c_in)
+                v = x[(((size_t)b * h_in + gy) * w_in + gx) * c_in + c0 + k];
+            xs[yy][xx][k] = v;
+        }
+        for (int i = threadIdx.x; i < 9 * kF32ChunkK * kF32TileC; i += blockDim.x) {
+            int co = i % kF32TileC;
+            int k = (i / kF32TileC) % kF32ChunkK;
+            int tap = i / (kF32TileC * kF32ChunkK);
+            float v = 0.f;
+            if (c0 + k < c_in && co0 + co < c_out)
+                v = weight[((size_t)tap * c_in + c0 + k) * c_out + co0 + co];
+            ws[tap][k][co] = v;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int tap = 0; tap < 9; ++tap) {
+            const int ky = tap / 3, kx = tap % 3;
+#pragma unroll
+            for (int k = 0; k < kF32ChunkK; ++k) {
+                const float4 wv = *reinterpret_cast<const float4*>(&ws[tap][k][cg * 4]);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float xv = xs[prow + ky][pcol0 + i + kx][k];
+                    acc[i][0] = fmaf(xv, wv.x, acc[i][0]);
+                    acc[i][1] = fmaf(xv, wv.y, acc[i][1]);
+                    acc[i][2] = fmaf(xv, wv.z, acc[i][2]);
+                    acc[i][3] = fmaf(xv, wv.w, acc[i][3]);
+                }
+            }
+        }
+        __syncthreads();
+    }
+    const int hh = tile_h0 + prow;
+    if (hh >= h_out) return;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int ww = tile_w0 + pcol0 + i;
+        if (ww >= w_out) continue;
+        float nz = 0.f;
+        if (noise != nullptr)
+            nz = noise[(size_t)b * noise_batch_stride + (size_t)hh * w_out + ww] * noise_strength;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int co = co0 + cg * 4 + j;
+            if (co >= c_out) continue;
+            float v = acc[i][j] * demod[(size_t)b * c_out + co] + nz + bias[co];
+            v = bias_lrelu(v);
+            if (next_styles != nullptr) v *= next_styles[(size_t)b * c_out + co];
+            out[(((size_t)b * h_out + hh) * w_out + ww) * c_out + co] = v;
+        }
+    }
+}
+
+int launch_modconv3x3_f32(const float* x, int batch, int h_out, int w_out, int c_in, int c_out, int pad,
+                          const float* weight, const float* demod, const float* noise,
+                          long long noise_batch_stride, float noise_strength, const float* bias,
+                          const float* next_styles, float* out, cudaStream_t stream) {
+    dim3 grid(((h_out + kF32TileP - 1) / kF32TileP) * ((w_out + kF32TileP - 1) / kF32TileP),
+              (c_out + kF32TileC - 1) / kF32TileC, batch);
+    modconv3x3_f32_kernel<<<grid, 256, 0, stream>>>(x, batch, h_out, w_out, c_in, c_out, pad, weight, demod,
+                                                    noise, noise_batch_stride, noise_strength, bias,
+                                                    next_styles, out);
+    return check_launch("modconv3x3_f32_kernel");
+}
+
+static int grid_for(size_t work_items, int block) {
+    size_t blocks = (work_items + block - 1) / block;
+    const size_t cap = 148u * 16u;  // 148 SMs x enough resident CTAs to cover latency
+    return (int)(blocks < cap ? (blocks ? blocks : 1) : cap);
+}
+
+}  // namespace gance
+
+using namespace gance;
+
+template <typename T>
+static int launch_torgb(const void* x, int batch, int h, int w, int channels, const float* styles,
+                        const float* weight, const float* bias, const float* y_prev, float* y_out,
+                        uint8_t* frames, cudaStream_t s) {
+    const int vec_per_pixel = channels / Vec<T>::N;
+    const size_t smem = (size_t)channels * 3 * sizeof(float);
+    int lanes = 1;
+    while (lanes < 32 && lanes < vec_per_pixel) lanes <<= 1;
+    const int groups = 256 / lanes;
+    int gx = (h * w + groups - 1) / groups;
+    const int cap = (148 * 8 + batch - 1) / batch;
+    if (gx > cap) gx = cap;
+    if (gx < 1) gx = 1;
+    dim3 grid(gx, batch);
+#define GANCE_TORGB(L)                                                                                   \
+    torgb_skip_kernel<T, L><<<grid, 256, smem, s>>>((const T*)x, h, w, channels, styles, weight, bias, \
+                                                    y_prev, y_out, frames)
+    switch (lanes) {
+        case 1: GANCE_TORGB(1); break;
+        case 2: GANCE_TORGB(2); break;
+        case 4: GANCE_TORGB(4); break;
+        case 8: GANCE_TORGB(8); break;
+        case 16: GANCE_TORGB(16); break;
+        default: GANCE_TORGB(32); break;
+    }
+#undef GANCE_TORGB
+    return check_launch("torgb_skip_kernel");
+}
+
+extern "C" {
+
+int gance_mapping(const float* z, int batch, const float* weights, const float* biases,
+                  const float* dlatent_avg, float truncation_psi, int num_ws, float* wplus, void* stream) {
+    GANCE_REQUIRE(is_initialised(), GANCE_E_NOT_INIT, "gance_init() has not been called");
+    GANCE_REQUIRE(z && weights && biases && dlatent_avg && wplus, GANCE_E_NULL, "gance_mapping: NULL pointer");
+    GANCE_REQUIRE(batch > 0 && num_ws > 0, GANCE_E_SHAPE, "gance_mapping: batch=%d num_ws=%d", batch, num_ws);
+    mapping_kernel<<<batch, kLatent, 0, (cudaStream_t)stream>>>(z, weights, biases, dlatent_avg, truncation_psi,
+                                                               num_ws, wplus);
+    return check_launch("mapping_kernel");
+}
+
+int gance_style_demod(const float* wplus, int batch, int num_ws, int w_index, const float* mod_weight,
+                      const float* mod_bias, const float* wsq, int c_in, int c_out, float* styles,
+                      float* demod, void* stream) {
+    GANCE_REQUIRE(is_initialised(), GANCE_E_NOT_INIT, "gance_init() has not been called");
+    GANCE_REQUIRE(wplus && mod_weight && mod_bias && styles, GANCE_E_NULL, "gance_style_demod: NULL pointer");
+    GANCE_REQUIRE((wsq == nullptr) == (demod == nullptr), GANCE_E_NULL,
+                  "gance_style_demod: wsq and demod must both be given or both be NULL");
+    GANCE_REQUIRE(batch > 0 && w_index >= 0 && w_index < num_ws, GANCE_E_SHAPE,
+                  "gance_style_demod: w_index %d outside [0,%d)", w_index, num_ws);
+    GANCE_REQUIRE(c_in > 0 && c_in <= kLatent && c_in % 2 == 0 && c_out > 0, GANCE_E_SHAPE,
+                  "gance_style_demod: c_in=%d c_out=%d unsupported", c_in, c_out);
+    style_demod_kernel<<<batch, 256, 0, (cudaStream_t)stream>>>(wplus, num_ws, w_index, mod_weight, mod_bias, wsq,
+                                                                c_in, c_out, styles, demod);
+    return check_launch("style_demod_kernel");
+}
+
+int gance_const_input(const float* konst, const float* styles, int batch, int channels, int dtype, void* out,
+                      void* stream) {
+    GANCE_REQUIRE(is_initialised(), GANCE_E_NOT_INIT, "gance_init() has not been called");
+    GANCE_REQUIRE(konst && styles && out, GANCE_E_NULL, "gance_const_input: NULL pointer");
+    GANCE_REQUIRE(batch > 0 && channels > 0 && channels % 8 == 0, GANCE_E_SHAPE, "gance_const_input: channels=%d",
+                  channels);
+    GANCE_REQUIRE(aligned16(out), GANCE_E_ALIGN, "gance_const_input: out not 16-byte aligned");
+    cudaStream_t s = (cudaStream_t)stream;
+    if (dtype == GANCE_F32) {
+        int grid = grid_for((size_t)batch * 16 * channels / 4, 256);
+        const_input_kernel<float><<<grid, 256, 0, s>>>(konst, styles, batch, channels, (float*)out);
+    } else if (dtype == GANCE_BF16) {
+        int grid = grid_for((size_t)batch * 16 * channels / 8, 256);
+        const_input_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(konst, styles, batch, channels, (__nv_bfloat16*)out);
+    } else {
+        return fail(GANCE_E_DTYPE, "gance_const_input: dtype %d", dtype);
+    }
+    return check_launch("const_input_kernel");
+}
+
+int gance_upfir2x_pad(const void* x, int dtype, int batch, int h, int w, int channels, const float* styles,
+                      void* u, void* stream) {
+    GANCE_REQUIRE(is_initialised(), GANCE_E_NOT_INIT, "gance_init() has not been called");
+    GANCE_REQUIRE(x && u, GANCE_E_NULL, "gance_upfir2x_pad: NULL pointer");
+    GANCE_REQUIRE(batch > 0 && h > 0 && w > 0 && channels > 0 && channels % 8 == 0, GANCE_E_SHAPE,
+                  "gance_upfir2x_pad: shape [%d,%d,%d,%d]", batch, h, w, channels);
+    GANCE_REQUIRE(aligned16(x) && aligned16(u), GANCE_E_ALIGN, "gance_upfir2x_pad: pointers must be 16-byte aligned");
+    cudaStream_t s = (cudaStream_t)stream;
+    if (dtype == GANCE_F32) {
+        int grid = grid_for((size_t)batch * (h + 1) * (w + 1) * channels / 4, 256);
+        upfir2x_pad_kernel<float><<<grid, 256, 0, s>>>((const float*)x, batch, h, w, channels, styles, (float*)u);
+    } else if (dtype == GANCE_BF16) {
+        int grid = grid_for((size_t)batch * (h + 1) * (w + 1) * channels / 8, 256);
+        upfir2x_pad_kernel<__nv_bfloat16>
+            <<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, batch, h, w, channels, styles, (__nv_bfloat16*)u);
+    } else {
+        return fail(GANCE_E_DTYPE, "gance_upfir2x_pad: dtype %d", dtype);
+    }
+    return check_launch("upfir2x_pad_kernel");
+}
+
+int gance_torgb_skip(const void* x, int dtype, int batch, int h, int w, int channels, const float* styles,
+                     const float* weight, const float* bias, const float* y_prev, float* y_out, uint8_t* frames,
+                     void* stream) {
+    GANCE_REQUIRE(is_initialised(), GANCE_E_NOT_INIT, "gance_init() has not been called");
+    GANCE_REQUIRE(x && styles && weight && bias, GANCE_E_NULL, "gance_torgb_skip: NULL pointer");
+    GANCE_REQUIRE(y_out || frames, GANCE_E_NULL, "gance_torgb_skip: neither y_out nor frames given");
+    GANCE_REQUIRE(batch > 0 && h > 0 && w > 0 && channels % 8 == 0 && channels <= 4096, GANCE_E_SHAPE,
+                  "gance_torgb_skip: shape [%d,%d,%d,%d]", batch, h, w, channels);
+    GANCE_REQUIRE(y_prev == nullptr || (h % 2 == 0 && w % 2 == 0), GANCE_E_SHAPE,
+                  "gance_torgb_skip: skip input needs even h,w");
+    GANCE_REQUIRE(aligned16(x) && aligned16(y_prev) && aligned16(y_out), GANCE_E_ALIGN,
+                  "gance_torgb_skip: pointers must be 16-byte aligned");
+    cudaStream_t s = (cudaStream_t)stream;
+    if (dtype == GANCE_F32)
+        return launch_torgb<float>(x, batch, h, w, channels, styles, weight, bias, y_prev, y_out, frames, s);
+    if (dtype == GANCE_BF16)
+        return launch_torgb<__nv_bfloat16>(x, batch, h, w, channels, styles, weight, bias, y_prev, y_out, frames, s);
+    return fail(GANCE_E_DTYPE, "gance_torgb_skip: dtype %d", dtype);
+}
+
+int gance_to_uint8_nhwc(const float* y, int batch, int h, int w, uint8_t* frames, void* stream) {
+    GANCE_REQUIRE(is_initialised(), GANCE_E_NOT_INIT, "gance_init() has not been called");
+    GANCE_REQUIRE(y && frames, GANCE_E_NULL, "gance_to_uint8_nhwc: NULL pointer");
+    GANCE_REQUIRE(batch > 0 && h > 0 && w > 0, GANCE_E_SHAPE, "gance_to_uint8_nhwc: shape");
+    size_t pixels = (size_t)batch * h * w;
+    to_uint8_kernel<<<grid_for(pixels, 256), 256, 0, (cudaStream_t)stream>>>((const float4*)y, pixels, frames);
+    return check_launch("to_uint8_kernel");
+}
+
+}  // extern "C"

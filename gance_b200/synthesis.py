@@ -1,0 +1,273 @@
+"""
+G_mapping + G_synthesis on one B200, driving libgance_b200.so through ctypes. PyTorch only owns
+the device memory and the stream; every arithmetic step is one of our kernels.
+
+Replaces the TF1 graph the reference runs in `wrap_loaded_network`
+(/root/reference/gance/network_interface/network_functions.py:114-192):
+  create_image_vector -> Gs.run(z, None, truncation_psi=1.2)                  -> `run_vectors`
+  create_image_matrix -> Gs.components.synthesis.run(w+, randomize_noise=False) -> `run_matrices`
+Both accept a whole batch of frames (the reference renders one frame per call).
+
+Data flow per batch (NHWC activations, `mode` = "bf16" | "fp32"; DESIGN.md has the full table):
+  styles/demod for every layer      gance_style_demod   (fp32)
+  const * s0                        gance_const_input
+  4x4 conv                          gance_modconv3x3            -> x (unscaled)
+  per resolution:
+      Conv0_up                      gance_modconv3x3_up2_fir    -> x * s_conv1
+      Conv1                         gance_modconv3x3            -> x (unscaled)
+      ToRGB + skip (+ uint8)        gance_torgb_skip
+"""
+
+from typing import Dict, List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from gance_b200 import _lib
+from gance_b200.networks.generator_spec import (
+    MAPPING_LAYERS,
+    MAPPING_LRMUL,
+    GeneratorSpec,
+    synthesis_layers,
+)
+
+MODES = {"fp32": (_lib.GANCE_F32, torch.float32), "bf16": (_lib.GANCE_BF16, torch.bfloat16)}
+NOISE_MODES = ("const", "random", "provided", "none")
+
+
+def _ptr(tensor: Optional[torch.Tensor]) -> Optional[int]:
+    return None if tensor is None else tensor.data_ptr()
+
+
+class GeneratorOnDevice:
+    """One generator's weights resident in HBM in kernel layout, plus per-batch work buffers."""
+
+    def __init__(self, spec: GeneratorSpec, variables: Dict[str, np.ndarray], device: torch.device, mode: str = "bf16") -> None:
+        if mode not in MODES:
+            raise ValueError(f"mode must be one of {sorted(MODES)}, got {mode!r}")
+        if device.type != "cuda":
+            raise _lib.GanceError("GeneratorOnDevice needs a CUDA device: there is no CPU fallback")
+        self.spec = spec
+        self.device = device
+        self.mode = mode
+        self.dtype_code, self.torch_dtype = MODES[mode]
+        self.lib = _lib.init(device.index if device.index is not None else torch.cuda.current_device())
+        self.num_ws = spec.num_ws
+        self.resolution = spec.resolution
+        self.convs, self.rgbs = synthesis_layers(spec)
+        self._buffers: Dict[tuple, torch.Tensor] = {}
+        self._upload(variables)
+
+    # ---- weights ---------------------------------------------------------------------------------
+    def _upload(self, v: Dict[str, np.ndarray]) -> None:
+        dev = self.device
+
+        def f32(array) -> torch.Tensor:
+            return torch.as_tensor(np.ascontiguousarray(array, dtype=np.float32)).to(dev)
+
+        # G_mapping: runtime coefficient lrmul/sqrt(fan_in) folded into W, lrmul into b (get_weight)
+        weights = [v[f"G_mapping/Dense{i}/weight"] for i in range(MAPPING_LAYERS)]
+        biases = [v[f"G_mapping/Dense{i}/bias"] for i in range(MAPPING_LAYERS)]
+        self.map_w = f32(np.stack([w * (MAPPING_LRMUL / np.sqrt(w.shape[0])) for w in weights]))
+        self.map_b = f32(np.stack([b * MAPPING_LRMUL for b in biases]))
+        self.dlatent_avg = f32(v["dlatent_avg"])
+        self.const = f32(np.transpose(v["G_synthesis/4x4/Const/const"][0], (1, 2, 0)))  # [4,4,C]
+
+        self.conv_w: List[torch.Tensor] = []
+        self.conv_wsq: List[torch.Tensor] = []
+        self.conv_mod_w: List[torch.Tensor] = []
+        self.conv_mod_b: List[torch.Tensor] = []
+        self.conv_bias: List[torch.Tensor] = []
+        self.conv_noise: List[torch.Tensor] = []
+        self.conv_strength: List[float] = []
+        for conv in self.convs:
+            hwio = torch.as_tensor(v[f"{conv.name}/weight"], dtype=torch.float32).to(dev)
+            hwio = hwio * float(1.0 / np.sqrt(9 * conv.in_channels))  # runtime_coef
+            self.conv_wsq.append((hwio * hwio).sum(dim=(0, 1)).contiguous())  # [Cin,Cout]
+            if self.mode == "fp32":
+                self.conv_w.append(hwio.contiguous())  # [3,3,Cin,Cout]
+            else:
+                self.conv_w.append(hwio.permute(3, 0, 1, 2).contiguous().to(torch.bfloat16))  # [Cout,3,3,Cin]
+            self.conv_mod_w.append(f32(v[f"{conv.name}/mod_weight"] * (1.0 / np.sqrt(512.0))))
+            self.conv_mod_b.append(f32(v[f"{conv.name}/mod_bias"]))
+            self.conv_bias.append(f32(v[f"{conv.name}/bias"]))
+            self.conv_noise.append(f32(v[f"G_synthesis/noise{conv.noise_index}"][0, 0]))
+            self.conv_strength.append(float(v[f"{conv.name}/noise_strength"]))
+        self.rgb_w: List[torch.Tensor] = []
+        self.rgb_mod_w: List[torch.Tensor] = []
+        self.rgb_mod_b: List[torch.Tensor] = []
+        self.rgb_bias: List[torch.Tensor] = []
+        for rgb in self.rgbs:
+            w = v[f"{rgb.name}/weight"][0, 0] * (1.0 / np.sqrt(rgb.in_channels))  # [C,3]
+            self.rgb_w.append(f32(w))
+            self.rgb_mod_w.append(f32(v[f"{rgb.name}/mod_weight"] * (1.0 / np.sqrt(512.0))))
+            self.rgb_mod_b.append(f32(v[f"{rgb.name}/mod_bias"]))
+            self.rgb_bias.append(f32(v[f"{rgb.name}/bias"]))
+
+    def weight_bytes(self) -> int:
+        tensors = [self.map_w, self.map_b, self.dlatent_avg, self.const]
+        for group in (self.conv_w, self.conv_wsq, self.conv_mod_w, self.conv_mod_b, self.conv_bias,
+                      self.conv_noise, self.rgb_w, self.rgb_mod_w, self.rgb_mod_b, self.rgb_bias):
+            tensors.extend(group)
+        return sum(t.numel() * t.element_size() for t in tensors)
+
+    # ---- buffers ---------------------------------------------------------------------------------
+    def _buffer(self, name: str, shape: Sequence[int], dtype: torch.dtype) -> torch.Tensor:
+        key = (name, tuple(shape), dtype)
+        buf = self._buffers.get(key)
+        if buf is None:
+            buf = torch.empty(tuple(shape), dtype=dtype, device=self.device)
+            self._buffers[key] = buf
+        return buf
+
+    def release_buffers(self) -> None:
+        self._buffers.clear()
+
+    def _stream(self) -> int:
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    # ---- entry points ----------------------------------------------------------------------------
+    def mapping(self, z: torch.Tensor, truncation_psi: float = 1.2) -> torch.Tensor:
+        """G_mapping + truncation lerp: z [B,512] -> w+ [B,num_ws,512] (fp32, device)."""
+        z = z.to(self.device, torch.float32).reshape(-1, 512).contiguous()
+        batch = z.shape[0]
+        wplus = torch.empty((batch, self.num_ws, 512), dtype=torch.float32, device=self.device)
+        _lib.check(
+            self.lib.gance_mapping(z.data_ptr(), batch, self.map_w.data_ptr(), self.map_b.data_ptr(),
+                                   self.dlatent_avg.data_ptr(), float(truncation_psi), self.num_ws,
+                                   wplus.data_ptr(), self._stream()),
+            "gance_mapping",
+        )
+        return wplus
+
+    def synthesis(
+        self,
+        wplus: torch.Tensor,
+        noise_mode: str = "const",
+        noise: Optional[Sequence[torch.Tensor]] = None,
+        return_float_image: bool = False,
+        out: Optional[torch.Tensor] = None,
+    ):
+        """
+        G_synthesis + convert_images_to_uint8: w+ [B,num_ws,512] -> uint8 frames [B,R,R,3] on the
+        device (`out` if given). noise_mode: "const" = the network's noise buffers
+        (randomize_noise=False, the matrix path), "random" = fresh N(0,1) per call (the vector
+        path's default), "provided" = `noise[layer]` of shape [B,H,W], "none" = no noise.
+        With return_float_image the fp32 skip sum [B,R,R,4] (RGB + zero pad) is returned as well.
+        """
+        if noise_mode not in NOISE_MODES:
+            raise ValueError(f"noise_mode must be one of {NOISE_MODES}")
+        wplus = wplus.to(self.device, torch.float32).reshape(-1, self.num_ws, 512).contiguous()
+        batch = wplus.shape[0]
+        lib, stream, code, dt = self.lib, self._stream(), self.dtype_code, self.torch_dtype
+        res = self.resolution
+        frames = out if out is not None else torch.empty((batch, res, res, 3), dtype=torch.uint8, device=self.device)
+        if tuple(frames.shape) != (batch, res, res, 3) or frames.dtype != torch.uint8 or not frames.is_contiguous():
+            raise ValueError("out must be a contiguous uint8 [B,R,R,3] tensor")
+
+        # -- styles and demodulation coefficients of every layer
+        styles, demods = [], []
+        for i, conv in enumerate(self.convs):
+            s = self._buffer(f"style{i}", (batch, conv.in_channels), torch.float32)
+            d = self._buffer(f"demod{i}", (batch, conv.out_channels), torch.float32)
+            _lib.check(
+                lib.gance_style_demod(wplus.data_ptr(), batch, self.num_ws, conv.w_index,
+                                      self.conv_mod_w[i].data_ptr(), self.conv_mod_b[i].data_ptr(),
+                                      self.conv_wsq[i].data_ptr(), conv.in_channels, conv.out_channels,
+                                      s.data_ptr(), d.data_ptr(), stream),
+                "gance_style_demod",
+            )
+            styles.append(s)
+            demods.append(d)
+        rgb_styles = []
+        for i, rgb in enumerate(self.rgbs):
+            s = self._buffer(f"rgbstyle{i}", (batch, rgb.in_channels), torch.float32)
+            _lib.check(
+                lib.gance_style_demod(wplus.data_ptr(), batch, self.num_ws, rgb.w_index,
+                                      self.rgb_mod_w[i].data_ptr(), self.rgb_mod_b[i].data_ptr(), None,
+                                      rgb.in_channels, 3, s.data_ptr(), None, stream),
+                "gance_style_demod(torgb)",
+            )
+            rgb_styles.append(s)
+
+        def layer_noise(i: int, side: int):
+            if noise_mode == "none" or (noise_mode != "provided" and self.conv_strength[i] == 0.0):
+                return None, 0
+            if noise_mode == "const":
+                return self.conv_noise[i], 0
+            if noise_mode == "random":
+                return torch.randn((batch, side, side), dtype=torch.float32, device=self.device), side * side
+            tensor = noise[i].to(self.device, torch.float32).reshape(batch, side, side).contiguous()
+            return tensor, side * side
+
+        # -- 4x4 block
+        c0 = self.convs[0]
+        x_in = self._buffer("const_in", (batch, 4, 4, c0.in_channels), dt)
+        _lib.check(lib.gance_const_input(self.const.data_ptr(), styles[0].data_ptr(), batch, c0.in_channels, code,
+                                         x_in.data_ptr(), stream), "gance_const_input")
+        x = self._buffer("act4", (batch, 4, 4, c0.out_channels), dt)
+        nz, nz_stride = layer_noise(0, 4)
+        _lib.check(
+            lib.gance_modconv3x3(x_in.data_ptr(), code, batch, 4, 4, c0.in_channels, c0.out_channels, 1,
+                                 self.conv_w[0].data_ptr(), demods[0].data_ptr(), _ptr(nz), nz_stride,
+                                 self.conv_strength[0], self.conv_bias[0].data_ptr(), None, x.data_ptr(), stream),
+            "gance_modconv3x3(4x4)",
+        )
+        last = len(self.rgbs) - 1
+        want_float = return_float_image or last != 0
+        y = self._buffer("skip4", (batch, 4, 4, 4), torch.float32) if want_float else None
+        _lib.check(
+            lib.gance_torgb_skip(x.data_ptr(), code, batch, 4, 4, c0.out_channels, rgb_styles[0].data_ptr(),
+                                 self.rgb_w[0].data_ptr(), self.rgb_bias[0].data_ptr(), None, _ptr(y),
+                                 frames.data_ptr() if last == 0 else None, stream),
+            "gance_torgb_skip(4x4)",
+        )
+
+        # -- one block per resolution
+        for block in range(1, len(self.rgbs)):
+            up_i, conv_i = 2 * block - 1, 2 * block
+            up, conv = self.convs[up_i], self.convs[conv_i]
+            side_in, side = up.in_resolution, up.out_resolution
+            scratch = self._buffer("upfir", (batch, 2 * side_in + 2, 2 * side_in + 2, up.in_channels), dt)
+            x_up = self._buffer(f"up{side}", (batch, side, side, up.out_channels), dt)
+            nz, nz_stride = layer_noise(up_i, side)
+            _lib.check(
+                lib.gance_modconv3x3_up2_fir(x.data_ptr(), code, batch, side_in, side_in, up.in_channels,
+                                             up.out_channels, styles[up_i].data_ptr(),
+                                             self.conv_w[up_i].data_ptr(), demods[up_i].data_ptr(), _ptr(nz),
+                                             nz_stride, self.conv_strength[up_i],
+                                             self.conv_bias[up_i].data_ptr(), styles[conv_i].data_ptr(),
+                                             scratch.data_ptr(), x_up.data_ptr(), stream),
+                f"gance_modconv3x3_up2_fir({side})",
+            )
+            x = self._buffer(f"act{side}", (batch, side, side, conv.out_channels), dt)
+            nz, nz_stride = layer_noise(conv_i, side)
+            _lib.check(
+                lib.gance_modconv3x3(x_up.data_ptr(), code, batch, side, side, conv.in_channels,
+                                     conv.out_channels, 1, self.conv_w[conv_i].data_ptr(),
+                                     demods[conv_i].data_ptr(), _ptr(nz), nz_stride, self.conv_strength[conv_i],
+                                     self.conv_bias[conv_i].data_ptr(), None, x.data_ptr(), stream),
+                f"gance_modconv3x3({side})",
+            )
+            is_last = block == last
+            want_float = return_float_image or not is_last
+            y_out = self._buffer(f"skip{side}", (batch, side, side, 4), torch.float32) if want_float else None
+            _lib.check(
+                lib.gance_torgb_skip(x.data_ptr(), code, batch, side, side, conv.out_channels,
+                                     rgb_styles[block].data_ptr(), self.rgb_w[block].data_ptr(),
+                                     self.rgb_bias[block].data_ptr(), _ptr(y), _ptr(y_out),
+                                     frames.data_ptr() if is_last else None, stream),
+                f"gance_torgb_skip({side})",
+            )
+            y = y_out
+        if return_float_image:
+            return frames, y
+        return frames
+
+    def run_vectors(self, z: torch.Tensor, truncation_psi: float = 1.2, noise_mode: str = "random", **kwargs):
+        """Batched `Gs.run(z, None, truncation_psi=1.2)` (network_functions.py:151-158)."""
+        return self.synthesis(self.mapping(z, truncation_psi), noise_mode=noise_mode, **kwargs)
+
+    def run_matrices(self, wplus: torch.Tensor, **kwargs):
+        """Batched `Gs.components.synthesis.run(w+, randomize_noise=False)` (network_functions.py:167-169)."""
+        return self.synthesis(wplus, noise_mode="const", **kwargs)

@@ -1,0 +1,183 @@
+/*
+ * gance_b200.h - C ABI of libgance_b200.so: the B200 (sm_100a) kernels behind GANce's
+ * audio -> latents -> StyleGAN2 frames path.
+ *
+ * What this replaces. The reference (esologic/GANce) is pure Python and has no FFI of its own;
+ * its device code is reached through TF1/dnnlib calls made in
+ *   gance/network_interface/network_functions.py:151-158  Gs.run(z, None, truncation_psi=1.2, ...)
+ *   gance/network_interface/network_functions.py:167-169  Gs.components.synthesis.run(w+, ...)
+ * whose CUDA side is the (missing) submodule gance/stylegan2 = NVlabs/stylegan2:
+ *   dnnlib/tflib/ops/fused_bias_act.cu (FusedBiasAct), dnnlib/tflib/ops/upfirdn_2d.cu (UpFirDn2D),
+ *   cuDNN grouped conv inside training/networks_stylegan2.py:modulated_conv2d_layer,
+ * and the numpy/scipy audio code in
+ *   gance/apply_spectrogram.py:20-118, gance/vector_sources/vector_sources_common.py:136-428,
+ *   gance/data_into_network_visualization/visualization_inputs.py:53-270.
+ * Each entry below cites the reference code it stands in for. The Python host
+ * (gance_b200/network_interface, gance_b200/vector_sources) binds these with ctypes and keeps the
+ * reference's call signatures; INTEGRATION.md shows the stub a GANce maintainer would add.
+ *
+ * Conventions (every entry):
+ *   - returns 0 on success, a positive GANCE_E_* code for a rejected argument, or
+ *     -(cudaError_t) if a launch failed; gance_last_error_string() has the message;
+ *   - never throws, never synchronises, never allocates device memory (callers pass scratch);
+ *   - every pointer is a DEVICE pointer unless named host_*, owned by the caller (PyTorch
+ *     tensor.data_ptr()), alive until the work on `stream` has completed;
+ *   - `stream` is a cudaStream_t passed as void*; calls on distinct streams are thread-safe;
+ *   - activations are NHWC; `dtype` selects the activation/weight element type:
+ *       GANCE_F32  = 0  fp32 validation mode (CUDA-core FMA, fp32 everywhere)
+ *       GANCE_BF16 = 1  bf16 operands, fp32 accumulate in TMEM (tcgen05), fp32 epilogue
+ *   - there is NO CPU fallback: without a CUDA device every compute entry fails.
+ */
+#ifndef GANCE_B200_H
+#define GANCE_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GANCE_ABI_VERSION 1
+
+#define GANCE_F32 0
+#define GANCE_BF16 1
+
+#define GANCE_OK 0
+#define GANCE_E_NULL 1        /* a required pointer was NULL */
+#define GANCE_E_SHAPE 2       /* a dimension is unsupported by this kernel */
+#define GANCE_E_DTYPE 3       /* unknown dtype code */
+#define GANCE_E_ALIGN 4       /* a pointer is not aligned as the kernel requires (16 B) */
+#define GANCE_E_NOT_INIT 5    /* gance_init() has not succeeded on this device */
+#define GANCE_E_DRIVER 6      /* CUDA driver entry point (TMA descriptor encode) unavailable */
+
+/* ---- lifecycle ------------------------------------------------------------------------------
+ * Replaces dnnlib.tflib.init_tf() + custom_ops.get_plugin() (nvcc build of the TF plugin) called
+ * from network_functions.py:101-103: selects the device, checks it is sm_100, resolves the
+ * driver's cuTensorMapEncodeTiled and raises the kernels' dynamic shared-memory limits. */
+int gance_abi_version(void);
+int gance_init(int device);
+const char* gance_last_error_string(void);
+/* Number of kernel launches issued through this library since load (bench.py's gpu_launches). */
+unsigned long long gance_launch_count(void);
+
+/* ---- G_mapping + truncation ------------------------------------------------------------------
+ * networks_stylegan2.G_mapping + the 'Truncation' block of G_main, as run by Gs.run
+ * (network_functions.py:151-158). z [B,512] f32 -> wplus [B,num_ws,512] f32.
+ * weights [8][512][512] (in,out) and biases [8][512] are pre-multiplied by their runtime
+ * coefficients (lrmul/sqrt(fan_in), lrmul). psi == 1 skips the lerp. */
+int gance_mapping(const float* z, int batch, const float* weights, const float* biases,
+                  const float* dlatent_avg, float truncation_psi, int num_ws, float* wplus,
+                  void* stream);
+
+/* ---- style affine + demodulation coefficients -------------------------------------------------
+ * The `s = dense(w) + bias + 1` and `d = rsqrt(sum (w*s)^2 + 1e-8)` lines of
+ * modulated_conv2d_layer. styles[b,ci] = wplus[b,w_index,:] @ mod_weight[:,ci] + mod_bias[ci] + 1;
+ * demod[b,co] = rsqrt(sum_ci styles[b,ci]^2 * wsq[ci,co] + 1e-8) with wsq = sum over taps of the
+ * squared runtime-scaled conv weight. wsq/demod may be NULL (ToRGB: demodulate=False).
+ * mod_weight [512,Cin] is pre-multiplied by 1/sqrt(512). */
+int gance_style_demod(const float* wplus, int batch, int num_ws, int w_index,
+                      const float* mod_weight, const float* mod_bias, const float* wsq, int c_in,
+                      int c_out, float* styles, float* demod, void* stream);
+
+/* ---- learned constant input ------------------------------------------------------------------
+ * tile(const, B) * styles: out[b,h,w,c] = konst[h,w,c] * styles[b,c]; konst is [4,4,C] f32. */
+int gance_const_input(const float* konst, const float* styles, int batch, int channels, int dtype,
+                      void* out, void* stream);
+
+/* ---- 3x3 modulated convolution with fused epilogue ---------------------------------------------
+ * modulated_conv2d_layer(kernel=3, demodulate=True) + noise + fused_bias_act('lrelu'), computed
+ * as conv(x*s, W) * d (SURVEY.md Appendix A.4 identity): `x` is ALREADY multiplied by this
+ * layer's styles. out = lrelu(acc*demod[b,co] + noise*noise_strength + bias[co], 0.2)*sqrt(2),
+ * then * next_styles[b,co] when next_styles != NULL (pre-scaling for the next conv).
+ *   x      [B, H+2-2*pad, W+2-2*pad, Cin]   pad = 1: SAME (zero border), pad = 0: VALID
+ *   weight GANCE_BF16: [Cout][3][3][Cin] bf16 (K-major GEMM operand, fed by TMA)
+ *          GANCE_F32 : [3][3][Cin][Cout] f32 (the TF HWIO layout)
+ *          both pre-multiplied by 1/sqrt(9*Cin)
+ *   noise  [H,W] f32 (noise_batch_stride = 0) or [B,H,W] (stride = H*W); may be NULL
+ *   out    [B,H,W,Cout]
+ * GANCE_BF16 runs the tcgen05/TMEM implicit GEMM and needs Cin % 32 == 0, Cout % 32 == 0. */
+int gance_modconv3x3(const void* x, int dtype, int batch, int h_out, int w_out, int c_in,
+                     int c_out, int pad, const void* weight, const float* demod,
+                     const float* noise, long long noise_batch_stride, float noise_strength,
+                     const float* bias, const float* next_styles, void* out, void* stream);
+
+/* ---- 2x FIR upsampling feeding the up-convolution ----------------------------------------------
+ * First half of upsample_conv_2d in FIR-first form (tests/test_oracle_stylegan2.py proves
+ * conv_transpose(stride 2) -> upfirdn([1,3,3,1]*4, pad 1,1) == VALID 3x3 conv of this tensor):
+ * u[b,j,i,c] over j,i in [0,2H+2): per axis u[2a] = .75 x[a-1] + .25 x[a], u[2a+1] = .25 x[a-1]
+ * + .75 x[a], x[-1] = x[H] = 0; multiplied by styles[b,c] when styles != NULL.
+ * Replaces UpFirDn2D (upfirdn_2d.cu) on this path. x [B,H,W,C] -> u [B,2H+2,2W+2,C]. */
+int gance_upfir2x_pad(const void* x, int dtype, int batch, int h, int w, int channels,
+                      const float* styles, void* u, void* stream);
+
+/* ---- up-convolution = upfir2x_pad + VALID modconv3x3 ---------------------------------------------
+ * modulated_conv2d_layer(up=True) + noise + bias/lrelu. `x` is the UNSCALED input [B,H,W,Cin];
+ * styles [B,Cin] are applied inside; scratch holds [B,2H+2,2W+2,Cin] elements of `dtype`. */
+int gance_modconv3x3_up2_fir(const void* x, int dtype, int batch, int h_in, int w_in, int c_in,
+                             int c_out, const float* styles, const void* weight,
+                             const float* demod, const float* noise,
+                             long long noise_batch_stride, float noise_strength, const float* bias,
+                             const float* next_styles, void* scratch, void* out, void* stream);
+
+/* ---- ToRGB + skip accumulation (+ uint8 conversion) ---------------------------------------------
+ * torgb(): modulated 1x1 conv without demodulation + bias, y = upsample_2d(y_prev) + t, and on
+ * the last block tflib.convert_images_to_uint8(nchw_to_nhwc=True): trunc(clamp(y*127.5+128)).
+ *   x [B,H,W,C] unscaled; styles [B,C]; weight [C,3] f32 pre-multiplied by 1/sqrt(C); bias [3]
+ *   y_prev [B,H/2,W/2,4] f32 or NULL; y_out [B,H,W,4] f32 or NULL; frames [B,H,W,3] u8 or NULL */
+int gance_torgb_skip(const void* x, int dtype, int batch, int h, int w, int channels,
+                     const float* styles, const float* weight, const float* bias,
+                     const float* y_prev, float* y_out, uint8_t* frames, void* stream);
+
+/* Stand-alone convert_images_to_uint8 on a [B,H,W,4] f32 skip tensor -> [B,H,W,3] u8. */
+int gance_to_uint8_nhwc(const float* y, int batch, int h, int w, uint8_t* frames, void* stream);
+
+/* ---- audio: windowed real DFT -> magnitude ------------------------------------------------------
+ * apply_spectrogram.compute_spectrogram (apply_spectrogram.py:49-82) up to |X|: frames of
+ * `window` (=vector_length-2) samples at hop vector_length, periodic Hann, DFT bins
+ * [0, window/2). audio f32 [T*vector_length] -> mag f64 [T, window/2]; block maxima of |X| are
+ * written to partial_max[grid] for the global max the dB conversion needs. */
+int gance_stft_mag(const float* audio, int num_frames, int vector_length, double* mag,
+                   double* global_max, void* stream);
+
+/* 20*log10(mag/max) (apply_spectrogram.py:80-81), Fourier resample bins -> vector_length
+ * (scipy.signal.resample as the fixed matrix `resample_matrix` [vector_length, bins] f64,
+ * vector_sources_common.py:211-230); writes out [T, vector_length] f64 and its global min/max
+ * (minmax[0], minmax[1]) for the min-max scale of apply_spectrogram.py:43. */
+int gance_db_resample(const double* mag, const double* global_max, int num_frames, int bins,
+                      int vector_length, const double* resample_matrix, double* out,
+                      double* minmax, void* stream);
+
+/* Min-max scale to [range_lo, range_hi] fused with the Savitzky-Golay filter along TIME
+ * (smooth_across_vectors, window 7 poly 3; vector_sources_common.py:136-166). `coeffs` is the
+ * [window, window] f64 matrix whose row r gives output sample r of an edge fit (rows
+ * 0..half-1 and half+1..window-1) and whose middle row is the interior FIR. */
+int gance_minmax_savgol_time(const double* in, const double* minmax, double range_lo,
+                             double range_hi, int num_frames, int vector_length,
+                             const double* coeffs, int window, double* out, void* stream);
+
+/* Savitzky-Golay within each vector (smooth_each_vector, vector_sources_common.py:169-188),
+ * optionally preceded by the circular left shift of rotate_vectors_over_time
+ * (vector_sources_common.py:408-428): in row t is read at (i + shift[t]) mod L. shift may be
+ * NULL. coeffs as above. in/out [T, L] f64. */
+int gance_roll_savgol_vector(const double* in, const int* shift, int num_frames,
+                             int vector_length, const double* coeffs, int window, double* out,
+                             void* stream);
+
+/* Alpha blends (visualization_inputs.py:144 and 233-243).
+ * noise-blend:      z[t,i]     = noise[t,i]*(1-alpha) + spec[t,i]*alpha           (noise f32)
+ * projection-blend: w[t,r,i]   = r < blend_depth ? proj[t/dup,i]*(1-alpha) + spec[t,i]*alpha
+ *                                                : proj[t/dup,i]                  (proj f32 [F,L])
+ * Outputs: latents_f64 (what the reference returns, may be NULL) and latents_f32 (what the
+ * generator consumes, may be NULL). */
+int gance_alpha_blend_noise(const double* spec, const float* noise, double alpha, int num_frames,
+                            int vector_length, double* latents_f64, float* latents_f32,
+                            void* stream);
+int gance_alpha_blend_wplus(const double* spec, const float* projected, int duplication,
+                            double alpha, int blend_depth, int depth, int num_frames,
+                            int vector_length, double* latents_f64, float* latents_f32,
+                            void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GANCE_B200_H */

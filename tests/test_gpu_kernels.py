@@ -1,0 +1,272 @@
+"""
+`-m gpu` parity tests, one kernel at a time, called THROUGH THE C ABI (ctypes) and compared with
+the oracle (oracle/stylegan2_ref.py, float64) on the same seeded inputs.
+
+Tolerances: fp32 validation mode - 2e-4 relative to the tensor's max (fp32 accumulation order);
+bf16 mode - the inputs are rounded to bf16 first and the oracle evaluated on the ROUNDED values, so
+what remains is fp32 accumulation order plus the final bf16 rounding of the output (2^-8 relative).
+"""
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from gance_b200 import _lib
+from oracle import stylegan2_ref as ref
+
+pytestmark = pytest.mark.gpu
+
+F64 = torch.float64
+
+
+@pytest.fixture(scope="module")
+def lib():
+    if not torch.cuda.is_available():
+        pytest.fail("these tests need a CUDA device; there is no CPU fallback to test")
+    torch.cuda.set_device(0)
+    return _lib.init(0)
+
+
+def stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def dev(array, dtype=torch.float32):
+    return torch.as_tensor(np.asarray(array)).to("cuda", dtype).contiguous()
+
+
+def rel_err(got: torch.Tensor, want: torch.Tensor) -> float:
+    got, want = got.double().cpu(), want.double().cpu()
+    return float((got - want).abs().max() / want.abs().max().clamp_min(1e-30))
+
+
+def test_library_reports_version_and_counts_launches(lib):
+    assert lib.gance_abi_version() == 1
+    before = _lib.launch_count()
+    z = dev(np.random.RandomState(0).randn(2, 512))
+    w = dev(np.zeros((8, 512, 512)))
+    b = dev(np.zeros((8, 512)))
+    avg = dev(np.zeros(512))
+    out = torch.empty(2, 4, 512, device="cuda")
+    _lib.check(lib.gance_mapping(z.data_ptr(), 2, w.data_ptr(), b.data_ptr(), avg.data_ptr(), 1.0, 4, out.data_ptr(), stream()), "map")
+    torch.cuda.synchronize()
+    assert _lib.launch_count() == before + 1
+
+
+def test_argument_validation_returns_codes(lib):
+    z = dev(np.zeros((1, 512)))
+    assert lib.gance_mapping(None, 1, z.data_ptr(), z.data_ptr(), z.data_ptr(), 1.0, 4, z.data_ptr(), stream()) == 1
+    assert "NULL" in _lib.last_error()
+    x = torch.zeros(1, 8, 8, 48, device="cuda", dtype=torch.bfloat16)
+    rc = lib.gance_modconv3x3(x.data_ptr(), 1, 1, 8, 8, 48, 48, 1, x.data_ptr(), z.data_ptr(), None, 0, 0.0,
+                              z.data_ptr(), None, x.data_ptr(), stream())
+    assert rc == 2  # GANCE_E_SHAPE: Cin % 32 != 0 on the tcgen05 path
+    with pytest.raises(_lib.GanceError):
+        _lib.check(rc, "modconv")
+
+
+def test_mapping_matches_oracle(lib):
+    from gance_b200.networks.generator_spec import GeneratorSpec, random_init_variables
+
+    variables = random_init_variables(GeneratorSpec(8), seed=3, perturbed=True)
+    gen = ref.ReferenceGenerator(variables, F64)
+    z = np.random.RandomState(5).randn(5, 512)
+    want = gen.truncate(gen.mapping(z), 1.2)
+    w = dev(np.stack([variables[f"G_mapping/Dense{i}/weight"] * (0.01 / np.sqrt(512)) for i in range(8)]))
+    b = dev(np.stack([variables[f"G_mapping/Dense{i}/bias"] * 0.01 for i in range(8)]))
+    avg = dev(variables["dlatent_avg"])
+    out = torch.empty(5, gen.num_ws, 512, device="cuda")
+    _lib.check(lib.gance_mapping(dev(z).data_ptr(), 5, w.data_ptr(), b.data_ptr(), avg.data_ptr(), 1.2, gen.num_ws,
+                                 out.data_ptr(), stream()), "gance_mapping")
+    assert rel_err(out, want) < 2e-5
+
+
+def _style_case(cin, cout, batch, seed):
+    g = torch.Generator().manual_seed(seed)
+    wplus = torch.randn(batch, 6, 512, dtype=F64, generator=g)
+    weight = torch.randn(3, 3, cin, cout, dtype=F64, generator=g)
+    mod_w = torch.randn(512, cin, dtype=F64, generator=g)
+    mod_b = torch.randn(cin, dtype=F64, generator=g) * 0.1
+    return wplus, weight, mod_w, mod_b
+
+
+def run_style_demod(lib, wplus, w_index, weight, mod_w, mod_b):
+    batch, cin, cout = wplus.shape[0], weight.shape[2], weight.shape[3]
+    w_eff = ref.get_weight(weight)
+    wsq = dev((w_eff * w_eff).sum((0, 1)))
+    s = torch.empty(batch, cin, device="cuda")
+    d = torch.empty(batch, cout, device="cuda")
+    _lib.check(
+        lib.gance_style_demod(dev(wplus).data_ptr(), batch, wplus.shape[1], w_index,
+                              dev(mod_w / np.sqrt(512.0)).data_ptr(), dev(mod_b).data_ptr(), wsq.data_ptr(), cin, cout,
+                              s.data_ptr(), d.data_ptr(), stream()),
+        "gance_style_demod",
+    )
+    return s, d
+
+
+@pytest.mark.parametrize("cin,cout", [(512, 512), (64, 32), (32, 32)])
+def test_style_demod_matches_oracle(lib, cin, cout):
+    wplus, weight, mod_w, mod_b = _style_case(cin, cout, 3, 0)
+    s, d = run_style_demod(lib, wplus, 2, weight, mod_w, mod_b)
+    s_ref = ref.dense_layer(wplus[:, 2], mod_w) + mod_b + 1
+    w_eff = ref.get_weight(weight)
+    d_ref = torch.rsqrt((s_ref * s_ref) @ (w_eff * w_eff).sum((0, 1)) + 1e-8)
+    assert rel_err(s, s_ref) < 1e-5
+    assert rel_err(d, d_ref) < 1e-5
+
+
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+def test_upfir2x_pad_matches_oracle(lib, mode):
+    code, dt = (0, torch.float32) if mode == "fp32" else (1, torch.bfloat16)
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn(2, 16, 6, 10, dtype=F64, generator=g)  # NCHW for the oracle
+    s = torch.randn(2, 16, dtype=F64, generator=g)
+    x_dev = dev(x.permute(0, 2, 3, 1), dt)
+    x_used = x_dev.double().cpu().permute(0, 3, 1, 2)  # what the kernel actually saw
+    k = ref._setup_kernel(ref.RESAMPLE_KERNEL) * 4
+    want = ref.upfirdn_2d(x_used * s[:, :, None, None], k, upx=2, upy=2, padx0=3, padx1=2, pady0=3, pady1=2)
+    u = torch.empty(2, 14, 22, 16, device="cuda", dtype=dt)
+    _lib.check(lib.gance_upfir2x_pad(x_dev.data_ptr(), code, 2, 6, 10, 16, dev(s).data_ptr(), u.data_ptr(), stream()),
+               "gance_upfir2x_pad")
+    tol = 1e-5 if mode == "fp32" else 2.0 ** -8
+    assert rel_err(u.permute(0, 3, 1, 2), want) < tol
+
+
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+@pytest.mark.parametrize("channels,side,last", [(512, 4, False), (64, 16, False), (32, 32, True)])
+def test_torgb_skip_matches_oracle(lib, mode, channels, side, last):
+    code, dt = (0, torch.float32) if mode == "fp32" else (1, torch.bfloat16)
+    g = torch.Generator().manual_seed(2)
+    batch = 2
+    x = torch.randn(batch, channels, side, side, dtype=F64, generator=g)
+    x_dev = dev(x.permute(0, 2, 3, 1), dt)
+    x_used = x_dev.double().cpu().permute(0, 3, 1, 2)
+    y_prev = torch.randn(batch, 3, side // 2, side // 2, dtype=F64, generator=g)
+    y_prev_f32 = y_prev.float().double()
+    wdl = torch.randn(batch, 512, dtype=F64, generator=g)
+    weight = torch.randn(1, 1, channels, 3, dtype=F64, generator=g)
+    mod_w = torch.randn(512, channels, dtype=F64, generator=g)
+    mod_b = torch.randn(channels, dtype=F64, generator=g) * 0.1
+    bias = torch.randn(3, dtype=F64, generator=g) * 0.1
+    t = ref.modulated_conv2d_layer(x_used, wdl, weight, mod_w, mod_b, demodulate=False)
+    want = ref.upsample_2d(y_prev_f32) + ref.apply_bias_act(t, bias)
+    s_ref = (ref.dense_layer(wdl, mod_w) + mod_b + 1).float()
+    y_prev_dev = torch.zeros(batch, side // 2, side // 2, 4, device="cuda")
+    y_prev_dev[..., :3] = dev(y_prev.permute(0, 2, 3, 1))
+    y_out = torch.empty(batch, side, side, 4, device="cuda")
+    frames = torch.empty(batch, side, side, 3, device="cuda", dtype=torch.uint8)
+    _lib.check(
+        lib.gance_torgb_skip(x_dev.data_ptr(), code, batch, side, side, channels, dev(s_ref).data_ptr(),
+                             dev(weight[0, 0] / np.sqrt(channels)).data_ptr(), dev(bias).data_ptr(),
+                             y_prev_dev.data_ptr(), y_out.data_ptr(), frames.data_ptr() if last else None, stream()),
+        "gance_torgb_skip",
+    )
+    assert rel_err(y_out[..., :3].permute(0, 3, 1, 2), want) < 2e-5
+    assert float(y_out[..., 3].abs().max()) == 0.0
+    if last:
+        want_u8 = ref.convert_images_to_uint8(y_out[..., :3].permute(0, 3, 1, 2).cpu())
+        assert np.array_equal(frames.cpu().numpy(), want_u8)  # bit-exact on identical fp32 input
+
+
+CONV_CASES = [
+    # cin, cout, side, batch, pad, name
+    (512, 512, 4, 9, 1, "4x4 tile (4,4,8) + batch tail, N=128"),
+    (512, 512, 8, 3, 1, "8x8 tile (8,8,2) + batch tail"),
+    (512, 256, 16, 2, 1, "16x16 N=128"),
+    (256, 256, 64, 5, 1, "N=256 path (m_tiles >= 148)"),
+    (128, 64, 32, 2, 1, "N=64"),
+    (64, 32, 32, 2, 1, "N=32 K=64"),
+    (32, 32, 64, 2, 1, "Cin=32: SWIZZLE_64B"),
+    (64, 64, 32, 2, 0, "VALID (up-conv second half)"),
+    (512, 512, 8, 2, 0, "VALID 8x8"),
+]
+
+
+def _run_modconv(lib, mode, cin, cout, side, batch, pad, seed=0, with_next=True):
+    code, dt = (0, torch.float32) if mode == "fp32" else (1, torch.bfloat16)
+    g = torch.Generator().manual_seed(seed)
+    side_in = side + 2 - 2 * pad
+    x = torch.randn(batch, cin, side_in, side_in, dtype=F64, generator=g)
+    weight = torch.randn(3, 3, cin, cout, dtype=F64, generator=g) / np.sqrt(9 * cin)
+    demod = torch.rand(batch, cout, dtype=F64, generator=g) + 0.5
+    noise = torch.randn(side, side, dtype=F64, generator=g)
+    bias = torch.randn(cout, dtype=F64, generator=g) * 0.1
+    nxt = torch.randn(batch, cout, dtype=F64, generator=g) if with_next else None
+    strength = 0.07
+    x_dev = dev(x.permute(0, 2, 3, 1), dt)
+    if mode == "fp32":
+        w_dev = dev(weight)  # HWIO
+        w_used = w_dev.double().cpu()
+    else:
+        w_dev = dev(weight.permute(3, 0, 1, 2), dt)  # [Cout,3,3,Cin]
+        w_used = w_dev.double().cpu().permute(1, 2, 3, 0)
+    x_used = x_dev.double().cpu().permute(0, 3, 1, 2)
+    acc = F.conv2d(x_used, w_used.permute(3, 2, 0, 1), padding=pad)
+    demod32, bias32, noise32 = demod.float().double(), bias.float().double(), noise.float().double()
+    want = acc * demod32[:, :, None, None] + noise32[None, None] * np.float32(strength) + bias32[None, :, None, None]
+    want = F.leaky_relu(want, 0.2) * np.sqrt(2.0)
+    if with_next:
+        want = want * nxt.float().double()[:, :, None, None]
+    out = torch.full((batch, side, side, cout), float("nan"), device="cuda", dtype=dt)
+    _lib.check(
+        lib.gance_modconv3x3(x_dev.data_ptr(), code, batch, side, side, cin, cout, pad, w_dev.data_ptr(),
+                             dev(demod).data_ptr(), dev(noise).data_ptr(), 0, strength, dev(bias).data_ptr(),
+                             dev(nxt).data_ptr() if with_next else None, out.data_ptr(), stream()),
+        "gance_modconv3x3",
+    )
+    torch.cuda.synchronize()
+    return out.permute(0, 3, 1, 2), want
+
+
+@pytest.mark.parametrize("cin,cout,side,batch,pad,name", CONV_CASES)
+def test_modconv3x3_fp32_matches_oracle(lib, cin, cout, side, batch, pad, name):
+    got, want = _run_modconv(lib, "fp32", cin, cout, side, batch, pad)
+    assert not torch.isnan(got).any(), "kernel left output unwritten"
+    assert rel_err(got, want) < 2e-5, name
+
+
+@pytest.mark.parametrize("cin,cout,side,batch,pad,name", CONV_CASES)
+def test_modconv3x3_tcgen05_matches_oracle(lib, cin, cout, side, batch, pad, name):
+    got, want = _run_modconv(lib, "bf16", cin, cout, side, batch, pad)
+    assert not torch.isnan(got.float()).any(), "kernel left output unwritten"
+    err = rel_err(got, want)
+    assert err < 2.0 ** -7, f"{name}: rel err {err}"
+    # element-wise: |got - want| <= 2^-8 |want| + small absolute slack for accumulation order
+    diff = (got.double().cpu() - want).abs()
+    bound = want.abs() * 2.0 ** -8 + 1e-3 * float(want.abs().max())
+    assert bool((diff <= bound).all()), f"{name}: {int((diff > bound).sum())} elements out of bound"
+
+
+def test_modconv3x3_tcgen05_without_next_style_and_noise_per_sample(lib):
+    got, want = _run_modconv(lib, "bf16", 64, 64, 16, 3, 1, seed=4, with_next=False)
+    assert rel_err(got, want) < 2.0 ** -7
+
+
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+def test_up_convolution_matches_oracle(lib, mode):
+    """gance_modconv3x3_up2_fir against the reference's transposed-conv + upfirdn formulation."""
+    code, dt = (0, torch.float32) if mode == "fp32" else (1, torch.bfloat16)
+    g = torch.Generator().manual_seed(7)
+    batch, cin, cout, side = 2, 64, 32, 16
+    x = torch.randn(batch, cin, side, side, dtype=F64, generator=g)
+    wplus, weight, mod_w, mod_b = _style_case(cin, cout, batch, 8)
+    bias = torch.randn(cout, dtype=F64, generator=g) * 0.1
+    x_dev = dev(x.permute(0, 2, 3, 1), dt)
+    x_used = x_dev.double().cpu().permute(0, 3, 1, 2)
+    s, d = run_style_demod(lib, wplus, 1, weight, mod_w, mod_b)
+    want = ref.modulated_conv2d_layer(x_used, wplus[:, 1], weight, mod_w, mod_b, up=True)
+    want = ref.apply_bias_act(want, bias, act="lrelu")
+    w_eff = ref.get_weight(weight)
+    w_dev = dev(w_eff) if mode == "fp32" else dev(w_eff.permute(3, 0, 1, 2), dt)
+    scratch = torch.empty(batch, 2 * side + 2, 2 * side + 2, cin, device="cuda", dtype=dt)
+    out = torch.empty(batch, 2 * side, 2 * side, cout, device="cuda", dtype=dt)
+    _lib.check(
+        lib.gance_modconv3x3_up2_fir(x_dev.data_ptr(), code, batch, side, side, cin, cout, s.data_ptr(),
+                                     w_dev.data_ptr(), d.data_ptr(), None, 0, 0.0, dev(bias).data_ptr(), None,
+                                     scratch.data_ptr(), out.data_ptr(), stream()),
+        "gance_modconv3x3_up2_fir",
+    )
+    tol = 5e-5 if mode == "fp32" else 2.0 ** -5  # bf16: weights, upsampled activations and output all rounded
+    assert rel_err(out.permute(0, 3, 1, 2), want) < tol

@@ -1,0 +1,120 @@
+"""
+`-m gpu` whole-generator parity: gance_b200.synthesis.GeneratorOnDevice (CUDA, through the C ABI)
+against oracle/stylegan2_ref.py (float64 CPU) on the same random-init / perturbed-init networks.
+
+Tolerances are BASELINE.json's: fp32 mode images within 1e-3 max-abs in [-1,1]; bf16 mode uint8
+frames within +-1 LSB on >= 99.9 % of pixels. (Pixel parity is "unpinned": the oracle is a
+restatement, the reference's StyleGAN2 code is absent - see oracle/stylegan2_ref.py.)
+"""
+
+import numpy as np
+import pytest
+import torch
+
+from gance_b200.networks.generator_spec import GeneratorSpec, random_init_variables
+from gance_b200.synthesis import GeneratorOnDevice
+from oracle import stylegan2_ref as ref
+
+pytestmark = pytest.mark.gpu
+
+
+def _device():
+    if not torch.cuda.is_available():
+        pytest.fail("these tests need a CUDA device; there is no CPU fallback to test")
+    torch.cuda.set_device(0)
+    return torch.device("cuda", 0)
+
+
+def _case(resolution, seed, perturbed, batch):
+    spec = GeneratorSpec(resolution)
+    variables = random_init_variables(spec, seed=seed, perturbed=perturbed)
+    oracle = ref.ReferenceGenerator(variables, torch.float64)
+    z = np.random.RandomState(100 + seed).randn(batch, 512)
+    return spec, variables, oracle, z
+
+
+def lsb_stats(got_u8: np.ndarray, want_u8: np.ndarray):
+    diff = np.abs(got_u8.astype(np.int32) - want_u8.astype(np.int32))
+    return float((diff <= 1).mean()), int(diff.max()), float((diff == 0).mean())
+
+
+@pytest.mark.parametrize("resolution,perturbed", [(32, False), (64, True)])
+def test_fp32_mode_matches_oracle(resolution, perturbed):
+    spec, variables, oracle, z = _case(resolution, 0, perturbed, 3)
+    gen = GeneratorOnDevice(spec, variables, _device(), mode="fp32")
+    wplus = gen.mapping(torch.as_tensor(z), truncation_psi=1.2)
+    want_w = oracle.truncate(oracle.mapping(z), 1.2)
+    assert float((wplus.double().cpu() - want_w).abs().max() / want_w.abs().max()) < 2e-5
+    frames, image = gen.synthesis(wplus, noise_mode="const", return_float_image=True)
+    want = oracle.synthesis(want_w.numpy())  # [B,3,R,R] float64
+    got = image[..., :3].permute(0, 3, 1, 2).double().cpu()
+    max_abs = float((got - want).abs().max())
+    print(f"fp32 mode {resolution}^2 perturbed={perturbed}: max-abs {max_abs:.3e} (|image| max {float(want.abs().max()):.2f})")
+    assert max_abs < 1e-3
+    within, worst, exact = lsb_stats(frames.cpu().numpy(), ref.convert_images_to_uint8(want))
+    print(f"   uint8: exact {exact:.5f}, within 1 LSB {within:.5f}, worst {worst}")
+    assert within >= 0.999
+
+
+@pytest.mark.parametrize("resolution,perturbed", [(32, False), (64, True), (128, True)])
+def test_bf16_mode_matches_oracle(resolution, perturbed):
+    spec, variables, oracle, z = _case(resolution, 1, perturbed, 2)
+    gen = GeneratorOnDevice(spec, variables, _device(), mode="bf16")
+    want_w = oracle.truncate(oracle.mapping(z), 1.2)
+    frames, image = gen.synthesis(torch.as_tensor(want_w.numpy()), noise_mode="const", return_float_image=True)
+    want = oracle.synthesis(want_w.numpy())
+    got = image[..., :3].permute(0, 3, 1, 2).double().cpu()
+    within, worst, exact = lsb_stats(frames.cpu().numpy(), ref.convert_images_to_uint8(want))
+    print(f"bf16 mode {resolution}^2 perturbed={perturbed}: float max-abs {float((got - want).abs().max()):.3e}; "
+          f"uint8 exact {exact:.5f}, within 1 LSB {within:.5f}, worst {worst}")
+    assert within >= 0.999
+
+
+def test_vector_and_matrix_paths_agree_with_oracle_semantics():
+    """Vector path = mapping + psi 1.2 + synthesis; matrix path = synthesis only, constant noise."""
+    spec, variables, oracle, z = _case(32, 2, True, 2)
+    gen = GeneratorOnDevice(spec, variables, _device(), mode="fp32")
+    frames_vec = gen.run_vectors(torch.as_tensor(z), noise_mode="const")
+    want = ref.convert_images_to_uint8(oracle.run_vector(z))
+    within, worst, _ = lsb_stats(frames_vec.cpu().numpy(), want)
+    assert within >= 0.999, worst
+    wplus = oracle.truncate(oracle.mapping(z), 1.2).numpy()
+    frames_mat = gen.run_matrices(torch.as_tensor(wplus))
+    assert lsb_stats(frames_mat.cpu().numpy(), ref.convert_images_to_uint8(oracle.run_matrix(wplus)))[0] >= 0.999
+    # provided noise = what tf.random_normal would have drawn, handed to both sides
+    rng = np.random.RandomState(9)
+    noise = [rng.randn(2, 1, c.out_resolution, c.out_resolution) for c in gen.convs]
+    got = gen.synthesis(torch.as_tensor(wplus), noise_mode="provided",
+                        noise=[torch.as_tensor(n[:, 0]) for n in noise])
+    want = ref.convert_images_to_uint8(oracle.synthesis(wplus, noise=noise))
+    assert lsb_stats(got.cpu().numpy(), want)[0] >= 0.999
+    # random noise only changes the image when noise_strength != 0 (perturbed init)
+    a = gen.synthesis(torch.as_tensor(wplus), noise_mode="random")
+    assert not np.array_equal(a.cpu().numpy(), frames_mat.cpu().numpy())
+
+
+def test_batch_independence_and_ordering():
+    """Frame i of a batch equals the same latent rendered alone: ordering is bit-exact."""
+    spec, variables, _, z = _case(32, 3, True, 5)
+    gen = GeneratorOnDevice(spec, variables, _device(), mode="bf16")
+    wplus = gen.mapping(torch.as_tensor(z))
+    together = gen.synthesis(wplus).cpu().numpy()
+    for i in (0, 3, 4):
+        alone = gen.synthesis(wplus[i : i + 1]).cpu().numpy()
+        assert np.array_equal(alone[0], together[i])
+    reversed_frames = gen.synthesis(torch.flip(wplus, [0])).cpu().numpy()
+    assert np.array_equal(reversed_frames[::-1], together)
+
+
+def test_config1_256_frames_match_oracle():
+    """BASELINE config 1 shape: 256^2 config-f generator; 2 of its frames against the fp64 oracle."""
+    spec, variables, oracle, z = _case(256, 0, False, 2)
+    for mode in ("fp32", "bf16"):
+        gen = GeneratorOnDevice(spec, variables, _device(), mode=mode)
+        frames = gen.run_vectors(torch.as_tensor(z), noise_mode="const")
+        assert frames.shape == (2, 256, 256, 3) and int(frames.sum()) > 0
+        want = ref.convert_images_to_uint8(oracle.run_vector(z))
+        within, worst, exact = lsb_stats(frames.cpu().numpy(), want)
+        print(f"256^2 {mode}: exact {exact:.5f} within1 {within:.5f} worst {worst}")
+        assert within >= 0.999
+        gen.release_buffers()
