@@ -13,6 +13,7 @@ LIBRARY_PATH = Path(__file__).resolve().parent / "csrc" / "libgance_b200.so"
 
 GANCE_F32 = 0
 GANCE_BF16 = 1
+GANCE_F16 = 2
 
 _SIGNATURES = {
     "gance_abi_version": (c_int, []),
@@ -42,6 +43,18 @@ _SIGNATURES = {
          c_void_p],
     ),
     "gance_to_uint8_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "gance_stft_mag": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "gance_db_resample": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "gance_minmax_savgol_time": (
+        c_int,
+        [c_void_p, c_void_p, c_double, c_double, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p],
+    ),
+    "gance_roll_savgol_vector": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p]),
+    "gance_alpha_blend_noise": (c_int, [c_void_p, c_void_p, c_double, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "gance_alpha_blend_wplus": (
+        c_int,
+        [c_void_p, c_void_p, c_int, c_double, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p],
+    ),
 }
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)

@@ -2,6 +2,7 @@
 #pragma once
 
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -72,6 +73,29 @@ struct Vec<__nv_bfloat16> {
         __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&raw);
 #pragma unroll
         for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+    }
+    __device__ __forceinline__ void zero() { raw = make_uint4(0u, 0u, 0u, 0u); }
+};
+
+template <>
+struct Vec<__half> {
+    static constexpr int N = 8;
+    uint4 raw;
+    __device__ __forceinline__ void load(const __half* p) { raw = *reinterpret_cast<const uint4*>(p); }
+    __device__ __forceinline__ void store(__half* p) const { *reinterpret_cast<uint4*>(p) = raw; }
+    __device__ __forceinline__ void to_float(float* f) const {
+        const __half2* h = reinterpret_cast<const __half2*>(&raw);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            float2 v = __half22float2(h[i]);
+            f[2 * i] = v.x;
+            f[2 * i + 1] = v.y;
+        }
+    }
+    __device__ __forceinline__ void from_float(const float* f) {
+        __half2* h = reinterpret_cast<__half2*>(&raw);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) h[i] = __floats2half2_rn(f[2 * i], f[2 * i + 1]);
     }
     __device__ __forceinline__ void zero() { raw = make_uint4(0u, 0u, 0u, 0u); }
 };

@@ -19,6 +19,8 @@
 // overlaps the MMAs of tile i+1.
 #include <cuda.h>
 
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace gance {
@@ -41,7 +43,7 @@ struct ConvParams {
     float noise_strength;
     const float* bias;
     const float* next_styles;
-    __nv_bfloat16* out;
+    void* out;  // [B,h_out,w_out,c_out] bf16 or half
 };
 
 // ---- PTX wrappers --------------------------------------------------------------------------------
@@ -111,7 +113,7 @@ __device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t cols) {
 __device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
 }
-// D[tmem] (+)= A[smem] * B[smem]^T ; both operands K-major, bf16, fp32 accumulate.
+// D[tmem] (+)= A[smem] * B[smem]^T ; both operands K-major, bf16 or half, fp32 accumulate.
 __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
                                           uint32_t accumulate) {
     asm volatile(
@@ -158,8 +160,9 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
 // tcgen05 instruction descriptor (cute::UMMA::InstrDescriptor): c_format F32 = 1 @ [4,6),
 // a_format / b_format BF16 = 1 @ [7,10) / [10,13), a_major = b_major = K (0) @ 15 / 16,
 // N >> 3 @ [17,23), M >> 4 @ [24,29).
-__host__ __device__ constexpr uint32_t make_instr_desc(int m, int n) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+__host__ __device__ constexpr uint32_t make_instr_desc(int m, int n, bool half_operands) {
+    const uint32_t fmt = half_operands ? 0u : 1u;  // F16 = 0, BF16 = 1
+    return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
 template <int N_TILE, int BLOCK_K, int STAGES>
@@ -190,7 +193,7 @@ __device__ __forceinline__ TileCoord decode_tile(const ConvParams& p, int tile, 
     return t;
 }
 
-template <int N_TILE, int BLOCK_K, int STAGES>
+template <typename T, int N_TILE, int BLOCK_K, int STAGES>
 __global__ void __launch_bounds__(kThreads, 1)
 modconv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
                      const ConvParams p) {
@@ -260,7 +263,7 @@ modconv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
     } else if (warp == 1) {
         if (lane == 0) {
             // ===== MMA issuer =====
-            constexpr uint32_t idesc = make_instr_desc(kTileM, N_TILE);
+            constexpr uint32_t idesc = make_instr_desc(kTileM, N_TILE, sizeof(T) == 2 && !std::is_same<T, __nv_bfloat16>::value);
             int stage = 0;
             uint32_t phase = 0;
             int acc = 0;
@@ -312,8 +315,8 @@ modconv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             const float4* demod4 = reinterpret_cast<const float4*>(p.demod + bc);
             const float4* bias4 = reinterpret_cast<const float4*>(p.bias + t.n0);
             const float4* style4 = p.next_styles ? reinterpret_cast<const float4*>(p.next_styles + bc) : nullptr;
-            __nv_bfloat16* dst = p.out + (((size_t)(valid ? b : 0) * p.h_out + (valid ? h : 0)) * p.w_out +
-                                          (valid ? w : 0)) * p.c_out + t.n0;
+            T* dst = reinterpret_cast<T*>(p.out) + (((size_t)(valid ? b : 0) * p.h_out + (valid ? h : 0)) * p.w_out +
+                                                    (valid ? w : 0)) * p.c_out + t.n0;
 
             mbar_wait(tmem_full_bar + acc, acc_phase);
             tcgen05_fence_after();
@@ -342,7 +345,7 @@ modconv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                             }
                             v[q * 4 + 0] = o0; v[q * 4 + 1] = o1; v[q * 4 + 2] = o2; v[q * 4 + 3] = o3;
                         }
-                        Vec<__nv_bfloat16> packed;
+                        Vec<T> packed;
                         packed.from_float(v);
                         packed.store(dst + c0 + g * 8);
                     }
@@ -371,10 +374,10 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
 static EncodeTiledFn g_encode_tiled = nullptr;
 static int g_num_sms = 148;
 
-template <int N_TILE, int BLOCK_K, int STAGES>
-static int configure() {
+template <typename T, int N_TILE, int BLOCK_K, int STAGES>
+static int configure_one() {
     using L = SmemLayout<N_TILE, BLOCK_K, STAGES>;
-    cudaError_t err = cudaFuncSetAttribute(modconv3x3_tc_kernel<N_TILE, BLOCK_K, STAGES>,
+    cudaError_t err = cudaFuncSetAttribute(modconv3x3_tc_kernel<T, N_TILE, BLOCK_K, STAGES>,
                                            cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes);
     if (err != cudaSuccess)
         return fail(-(int)err, "cudaFuncSetAttribute(modconv3x3_tc<%d,%d,%d>, %d B): %s", N_TILE, BLOCK_K, STAGES,
@@ -382,42 +385,59 @@ static int configure() {
     return GANCE_OK;
 }
 
-static int make_tmap(CUtensorMap* map, const void* base, int rank, const cuuint64_t* dims,
+template <int N_TILE, int BLOCK_K, int STAGES>
+static int configure() {
+    int rc = configure_one<__nv_bfloat16, N_TILE, BLOCK_K, STAGES>();
+    if (rc != GANCE_OK) return rc;
+    return configure_one<__half, N_TILE, BLOCK_K, STAGES>();
+}
+
+static int make_tmap(CUtensorMap* map, const void* base, bool half_operands, int rank, const cuuint64_t* dims,
                      const cuuint64_t* strides_bytes, const cuuint32_t* box, int swizzle_bytes) {
     cuuint32_t elem_strides[5] = {1, 1, 1, 1, 1};
     CUtensorMapSwizzle sw = swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
                                                  : (swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
                                                                         : CU_TENSOR_MAP_SWIZZLE_32B);
-    CUresult rc = g_encode_tiled(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base),
+    CUresult rc = g_encode_tiled(map, half_operands ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16,
+                                 (cuuint32_t)rank, const_cast<void*>(base),
                                  dims, strides_bytes, box, elem_strides, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
                                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (rc != CUDA_SUCCESS) return fail(GANCE_E_DRIVER, "cuTensorMapEncodeTiled failed with CUresult %d", (int)rc);
     return GANCE_OK;
 }
 
-template <int N_TILE, int BLOCK_K, int STAGES>
-static int launch(const ConvParams& p, const void* x, const void* weight, int h_in, int w_in, cudaStream_t stream) {
+template <typename T, int N_TILE, int BLOCK_K, int STAGES>
+static int launch_typed(const ConvParams& p, const void* x, const void* weight, int h_in, int w_in,
+                        cudaStream_t stream) {
     using L = SmemLayout<N_TILE, BLOCK_K, STAGES>;
+    constexpr bool kHalf = std::is_same<T, __half>::value;
     CUtensorMap tmap_x, tmap_w;
     {
         cuuint64_t dims[4] = {(cuuint64_t)p.c_in, (cuuint64_t)w_in, (cuuint64_t)h_in, (cuuint64_t)p.batch};
         cuuint64_t strides[3] = {(cuuint64_t)p.c_in * 2, (cuuint64_t)w_in * p.c_in * 2,
                                  (cuuint64_t)h_in * w_in * p.c_in * 2};
         cuuint32_t box[4] = {(cuuint32_t)BLOCK_K, (cuuint32_t)p.tile_w, (cuuint32_t)p.tile_h, (cuuint32_t)p.tile_b};
-        int rc = make_tmap(&tmap_x, x, 4, dims, strides, box, BLOCK_K * 2);
+        int rc = make_tmap(&tmap_x, x, kHalf, 4, dims, strides, box, BLOCK_K * 2);
         if (rc != GANCE_OK) return rc;
     }
     {
         cuuint64_t dims[2] = {(cuuint64_t)9 * p.c_in, (cuuint64_t)p.c_out};
         cuuint64_t strides[1] = {(cuuint64_t)9 * p.c_in * 2};
         cuuint32_t box[2] = {(cuuint32_t)BLOCK_K, (cuuint32_t)N_TILE};
-        int rc = make_tmap(&tmap_w, weight, 2, dims, strides, box, BLOCK_K * 2);
+        int rc = make_tmap(&tmap_w, weight, kHalf, 2, dims, strides, box, BLOCK_K * 2);
         if (rc != GANCE_OK) return rc;
     }
     const int total_tiles = p.tiles_b * p.tiles_h * p.tiles_w * p.n_tiles;
     const int grid = total_tiles < g_num_sms ? total_tiles : g_num_sms;
-    modconv3x3_tc_kernel<N_TILE, BLOCK_K, STAGES><<<grid, kThreads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
+    modconv3x3_tc_kernel<T, N_TILE, BLOCK_K, STAGES><<<grid, kThreads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
     return check_launch("modconv3x3_tc_kernel");
+}
+
+template <int N_TILE, int BLOCK_K, int STAGES>
+static int launch(bool half_operands, const ConvParams& p, const void* x, const void* weight, int h_in, int w_in,
+                  cudaStream_t stream) {
+    if (half_operands) return launch_typed<__half, N_TILE, BLOCK_K, STAGES>(p, x, weight, h_in, w_in, stream);
+    return launch_typed<__nv_bfloat16, N_TILE, BLOCK_K, STAGES>(p, x, weight, h_in, w_in, stream);
 }
 
 }  // namespace tc
@@ -465,7 +485,8 @@ extern "C" int gance_modconv3x3(const void* x, int dtype, int batch, int h_out, 
         return launch_modconv3x3_f32((const float*)x, batch, h_out, w_out, c_in, c_out, pad, (const float*)weight,
                                      demod, noise, noise_batch_stride, noise_strength, bias, next_styles,
                                      (float*)out, s);
-    GANCE_REQUIRE(dtype == GANCE_BF16, GANCE_E_DTYPE, "gance_modconv3x3: dtype %d", dtype);
+    GANCE_REQUIRE(dtype == GANCE_BF16 || dtype == GANCE_F16, GANCE_E_DTYPE, "gance_modconv3x3: dtype %d", dtype);
+    const bool half_operands = dtype == GANCE_F16;
     GANCE_REQUIRE(c_in % 32 == 0 && c_out % 32 == 0, GANCE_E_SHAPE,
                   "gance_modconv3x3: the tcgen05 path needs Cin %% 32 == 0 and Cout %% 32 == 0 (got %d, %d)", c_in,
                   c_out);
@@ -487,30 +508,30 @@ extern "C" int gance_modconv3x3(const void* x, int dtype, int batch, int h_out, 
     p.tiles_h = (h_out + p.tile_h - 1) / p.tile_h;
     p.tiles_b = (batch + p.tile_b - 1) / p.tile_b;
     p.demod = demod; p.noise = noise; p.noise_batch_stride = noise_batch_stride; p.noise_strength = noise_strength;
-    p.bias = bias; p.next_styles = next_styles; p.out = (__nv_bfloat16*)out;
+    p.bias = bias; p.next_styles = next_styles; p.out = out;
     const int h_in = h_out + 2 - 2 * pad, w_in = w_out + 2 - 2 * pad;
     const int m_tiles = p.tiles_w * p.tiles_h * p.tiles_b;
 
     if (c_in % 64 != 0) {  // Cin = 32 (1024^2 Conv1 in config-f): 64-byte rows, SWIZZLE_64B
         GANCE_REQUIRE(c_out % 32 == 0, GANCE_E_SHAPE, "Cout %d", c_out);
         p.n_tiles = c_out / 32; p.k_chunks = c_in / 32;
-        return tc::launch<32, 32, 8>(p, x, weight, h_in, w_in, s);
+        return tc::launch<32, 32, 8>(half_operands, p, x, weight, h_in, w_in, s);
     }
     p.k_chunks = c_in / 64;
     if (c_out % 256 == 0 && m_tiles >= 148) {
         p.n_tiles = c_out / 256;
-        return tc::launch<256, 64, 4>(p, x, weight, h_in, w_in, s);
+        return tc::launch<256, 64, 4>(half_operands, p, x, weight, h_in, w_in, s);
     }
     if (c_out % 128 == 0) {
         p.n_tiles = c_out / 128;
-        return tc::launch<128, 64, 6>(p, x, weight, h_in, w_in, s);
+        return tc::launch<128, 64, 6>(half_operands, p, x, weight, h_in, w_in, s);
     }
     if (c_out % 64 == 0) {
         p.n_tiles = c_out / 64;
-        return tc::launch<64, 64, 8>(p, x, weight, h_in, w_in, s);
+        return tc::launch<64, 64, 8>(half_operands, p, x, weight, h_in, w_in, s);
     }
     p.n_tiles = c_out / 32;
-    return tc::launch<32, 64, 8>(p, x, weight, h_in, w_in, s);
+    return tc::launch<32, 64, 8>(half_operands, p, x, weight, h_in, w_in, s);
 }
 
 extern "C" int gance_modconv3x3_up2_fir(const void* x, int dtype, int batch, int h_in, int w_in, int c_in,

@@ -470,6 +470,9 @@ int gance_const_input(const float* konst, const float* styles, int batch, int ch
     } else if (dtype == GANCE_BF16) {
         int grid = grid_for((size_t)batch * 16 * channels / 8, 256);
         const_input_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(konst, styles, batch, channels, (__nv_bfloat16*)out);
+    } else if (dtype == GANCE_F16) {
+        int grid = grid_for((size_t)batch * 16 * channels / 8, 256);
+        const_input_kernel<__half><<<grid, 256, 0, s>>>(konst, styles, batch, channels, (__half*)out);
     } else {
         return fail(GANCE_E_DTYPE, "gance_const_input: dtype %d", dtype);
     }
@@ -491,6 +494,9 @@ int gance_upfir2x_pad(const void* x, int dtype, int batch, int h, int w, int cha
         int grid = grid_for((size_t)batch * (h + 1) * (w + 1) * channels / 8, 256);
         upfir2x_pad_kernel<__nv_bfloat16>
             <<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, batch, h, w, channels, styles, (__nv_bfloat16*)u);
+    } else if (dtype == GANCE_F16) {
+        int grid = grid_for((size_t)batch * (h + 1) * (w + 1) * channels / 8, 256);
+        upfir2x_pad_kernel<__half><<<grid, 256, 0, s>>>((const __half*)x, batch, h, w, channels, styles, (__half*)u);
     } else {
         return fail(GANCE_E_DTYPE, "gance_upfir2x_pad: dtype %d", dtype);
     }
@@ -514,6 +520,8 @@ int gance_torgb_skip(const void* x, int dtype, int batch, int h, int w, int chan
         return launch_torgb<float>(x, batch, h, w, channels, styles, weight, bias, y_prev, y_out, frames, s);
     if (dtype == GANCE_BF16)
         return launch_torgb<__nv_bfloat16>(x, batch, h, w, channels, styles, weight, bias, y_prev, y_out, frames, s);
+    if (dtype == GANCE_F16)
+        return launch_torgb<__half>(x, batch, h, w, channels, styles, weight, bias, y_prev, y_out, frames, s);
     return fail(GANCE_E_DTYPE, "gance_torgb_skip: dtype %d", dtype);
 }
 

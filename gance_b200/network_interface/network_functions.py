@@ -1,0 +1,348 @@
+"""
+Drop-in for /root/reference/gance/network_interface/network_functions.py: the same public names,
+argument meaning and error behaviour, backed by the B200 kernels (gance_b200.synthesis) instead of
+a TF1 session in a child process.
+
+What is kept: `NetworkInterface` field order (reference :66-78),
+`create_network_interface` (:195-204), `NetworkInterfaceInProcess` + `stop_function` (:207-214),
+`create_network_interface_process` raising the load error in the caller (:270-278),
+`MultiNetwork` with its ValueError-before-load contract (:450-481), context manager returning None
+on RuntimeError (:516-529), no reload for identical paths (:552-556), `parse_network_paths`
+(:643-682) and `NetworksFile` (:685-690).
+
+What changes underneath: the network lives in THIS process on the GPU (no multiprocessing queues,
+no 3 MB pickles per frame); weights of every network a process has loaded stay resident in HBM
+(all three config-f networks are ~200 MB), so `MultiNetwork` switching is a dictionary lookup
+instead of killing and re-spawning a TF child (reference :543-563); and every interface also
+exposes `create_images_batch`, which renders many frames per call - the reference renders one.
+There is no CPU fallback: without a CUDA device loading a network raises.
+"""
+
+import json
+import logging
+import typing
+from functools import wraps
+from pathlib import Path
+from typing import Callable, Dict, List, NamedTuple, Optional, Tuple, Union
+
+import numpy as np
+import pydantic
+import torch
+from pydantic import BaseModel, FilePath
+from typing_extensions import Protocol
+
+from gance_b200.gance_types import RGBInt8ImageType
+from gance_b200.logger_common import LOGGER
+from gance_b200.networks.container import NETWORK_SUFFIX, LoadedNetwork, read_network
+from gance_b200.synthesis import GeneratorOnDevice
+from gance_b200.vector_sources.vector_types import SingleMatrix, SingleVector, is_vector
+
+TRUNCATION_PSI = 1.2  # hard-wired in the reference (:124, :155)
+DEFAULT_MODE = "fp16"  # operand type of the tcgen05 path; "bf16" and "fp32" (validation) also exist
+
+
+def sorted_networks_in_directory(networks_directory: Path) -> List[Path]:
+    """Paths of the `.pkl` files in a directory, sorted alphabetically (reference :41-48)."""
+    return list(sorted(networks_directory.glob(f"*{NETWORK_SUFFIX}")))
+
+
+class ImageFunction(Protocol):  # pylint: disable=too-few-public-methods
+    """A vector or matrix in, one RGB uint8 image out (reference :51-63)."""
+
+    def __call__(self: "ImageFunction", data: Union[SingleVector, SingleMatrix]) -> RGBInt8ImageType:
+        ...
+
+
+class BatchImageFunction(Protocol):  # pylint: disable=too-few-public-methods
+    """(N,512) vectors or (N,num_ws,512) matrices in, (N,H,W,3) uint8 out."""
+
+    def __call__(self: "BatchImageFunction", data: np.ndarray) -> np.ndarray:
+        ...
+
+
+class NetworkInterface(NamedTuple):
+    """
+    The only view of a network the rest of GANce uses. The first four fields are the reference's,
+    in the reference's order (:66-78); `create_images_batch` is an addition with a default so that
+    code constructing the tuple from the four original fields keeps working.
+    """
+
+    expected_vector_length: int
+    create_image_vector: ImageFunction
+    create_image_matrix: ImageFunction
+    create_image_generic: ImageFunction
+    create_images_batch: Optional[BatchImageFunction] = None
+
+
+def fix_cuda_path() -> None:
+    """Kept for API compatibility (reference :81-90): nothing is JIT-compiled at run time here."""
+
+
+def _device() -> torch.device:
+    if not torch.cuda.is_available():
+        raise RuntimeError("No CUDA device: gance_b200 has no CPU fallback for network synthesis")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def load_network_network(network_path: Path, call_init_function: bool) -> LoadedNetwork:
+    """
+    Reads the network file (reference :93-111 does `pickle.load(f)[2]`). `call_init_function`
+    initialised the TF session there; here the CUDA library is initialised when the weights are
+    uploaded, so the flag only decides whether the device is checked eagerly.
+    """
+    if call_init_function:
+        _device()
+    return read_network(Path(network_path))
+
+
+def wrap_loaded_network(network: LoadedNetwork, mode: str = DEFAULT_MODE) -> NetworkInterface:
+    """Upload the weights and build the interface NT (reference :114-192)."""
+    generator = GeneratorOnDevice(network.spec, network.variables, _device(), mode=mode)
+    return _wrap_generator(generator)
+
+
+def _wrap_generator(generator: GeneratorOnDevice, alive: Optional[List[bool]] = None) -> NetworkInterface:
+    num_ws = generator.num_ws
+
+    def check_alive() -> None:
+        if alive is not None and not alive[0]:
+            raise RuntimeError("This network interface has been stopped")
+
+    def to_host(frames: torch.Tensor) -> np.ndarray:
+        return frames.cpu().numpy()
+
+    def vectors(data: np.ndarray) -> torch.Tensor:
+        # Gs.run(z, None, truncation_psi=1.2): randomize_noise is NOT overridden -> fresh noise
+        z = torch.as_tensor(np.asarray(data, dtype=np.float32)).reshape(-1, 512)
+        return generator.run_vectors(z, truncation_psi=TRUNCATION_PSI, noise_mode="random")
+
+    def matrices(data: np.ndarray) -> torch.Tensor:
+        # Gs.components.synthesis.run(w+, randomize_noise=False); truncation_psi is ignored there
+        array = np.asarray(data, dtype=np.float32)
+        array = array.reshape(-1, array.shape[-2], 512)
+        if array.shape[1] < num_ws:
+            raise ValueError(f"latents have {array.shape[1]} rows, this network needs {num_ws}")
+        # a 512^2 network takes 16 rows of an 18-row projection
+        return generator.run_matrices(torch.as_tensor(np.ascontiguousarray(array[:, :num_ws])))
+
+    def create_image_vector(data: SingleVector) -> RGBInt8ImageType:
+        check_alive()
+        return RGBInt8ImageType(to_host(vectors(data))[0])
+
+    def create_image_matrix(data: SingleMatrix) -> RGBInt8ImageType:
+        check_alive()
+        return RGBInt8ImageType(to_host(matrices(data))[0])
+
+    def create_image_generic(data: Union[SingleVector, SingleMatrix]) -> RGBInt8ImageType:
+        if is_vector(data):
+            return create_image_vector(data)
+        return create_image_matrix(data)
+
+    def create_images_batch(data: np.ndarray) -> np.ndarray:
+        check_alive()
+        array = np.asarray(data)
+        if array.ndim == 2 and array.shape[-1] == 512 and array.shape[0] != num_ws:
+            return to_host(vectors(array))
+        if array.ndim == 2:  # ambiguous (num_ws,512): the reference treats 2-D data as ONE matrix
+            return to_host(matrices(array[None]))
+        return to_host(matrices(array))
+
+    return NetworkInterface(
+        expected_vector_length=512,
+        create_image_vector=create_image_vector,
+        create_image_matrix=create_image_matrix,
+        create_image_generic=create_image_generic,
+        create_images_batch=create_images_batch,
+    )
+
+
+def create_network_interface(network_path: Path, call_init_function: bool) -> NetworkInterface:
+    """Load + wrap (reference :195-204)."""
+    return wrap_loaded_network(load_network_network(network_path, call_init_function))
+
+
+class NetworkInterfaceInProcess(NamedTuple):
+    """Interface plus the function that releases it (reference :207-214)."""
+
+    network_interface: NetworkInterface
+    stop_function: Callable[[], None]
+
+
+# Weights of every network this process has loaded, keyed by (resolved path, mode).
+_RESIDENT: Dict[Tuple[str, str], GeneratorOnDevice] = {}
+
+
+def resident_generator(network_path: Path, mode: str = DEFAULT_MODE) -> GeneratorOnDevice:
+    """The GPU-resident generator for a network file, loading it on first use."""
+    key = (str(Path(network_path).resolve()), mode)
+    generator = _RESIDENT.get(key)
+    if generator is None:
+        network = load_network_network(Path(network_path), call_init_function=True)
+        generator = GeneratorOnDevice(network.spec, network.variables, _device(), mode=mode)
+        _RESIDENT[key] = generator
+    return generator
+
+
+def evict_resident_networks() -> None:
+    """Free every cached generator (the reference frees by killing its TF child, :303-321)."""
+    _RESIDENT.clear()
+    if torch.cuda.is_available():
+        torch.cuda.empty_cache()
+
+
+def create_network_interface_process(network_path: Path, mode: str = DEFAULT_MODE) -> NetworkInterfaceInProcess:
+    """
+    Reference :232-340 spawns a TF worker and re-raises its start-up exception in the parent
+    (:270-278). Here loading happens in-process, so a bad path / bad file / missing GPU raises
+    directly; `stop_function()` invalidates the interface (later calls raise RuntimeError) and
+    drops this interface's work buffers. The weights stay resident for fast switching; call
+    `evict_resident_networks()` to free them.
+    """
+    generator = resident_generator(network_path, mode)
+    alive = [True]
+
+    def stop_function() -> None:
+        alive[0] = False
+        generator.release_buffers()
+
+    return NetworkInterfaceInProcess(
+        network_interface=_wrap_generator(generator, alive), stop_function=stop_function
+    )
+
+
+@typing.no_type_check
+def _raise_exception_if_unloaded(function):
+    """Decorator: ValueError unless `load()` has run (reference :450-481)."""
+
+    @wraps(function)
+    def wrapper(*args, **kwargs):
+        self = args[0]
+        if any(
+            member is None
+            for member in [
+                self._currently_loaded_network,  # pylint: disable=protected-access
+                self._expected_vector_length,  # pylint: disable=protected-access
+            ]
+        ):
+            raise ValueError("Multinetwork is not initialized! Call load or use context manager.")
+        return function(*args, **kwargs)
+
+    return wrapper
+
+
+class MultiNetwork:
+    """Switch between networks during a run (reference :484-640); switching costs a dict lookup."""
+
+    def __init__(self: "MultiNetwork", network_paths: List[Path], load: bool = False) -> None:
+        self._network_paths: List[Path] = network_paths
+        self._currently_loaded_network_index: int = 0
+        self._currently_loaded_network: Optional[NetworkInterfaceInProcess] = None
+        self._expected_vector_length: Optional[int] = None
+        if load:
+            self.load()
+
+    @property  # type: ignore
+    @_raise_exception_if_unloaded
+    def expected_vector_length(self: "MultiNetwork") -> int:
+        return self._expected_vector_length
+
+    def __enter__(self: "MultiNetwork") -> Optional["MultiNetwork"]:
+        """Returns None when the network cannot be put on the GPU (reference :516-529)."""
+        try:
+            self.load()
+        except RuntimeError:
+            logging.warning("Couldn't load network into GPU, proceeding without network.")
+            return None
+        return self
+
+    @typing.no_type_check
+    def __exit__(self, exec_type, exec_value, exec_traceback) -> None:
+        if self._currently_loaded_network is not None:
+            self.unload()
+
+    def _load_network_at_index(self: "MultiNetwork", index: int) -> None:
+        """Switch only if the index AND the path differ (reference :543-563)."""
+        if (
+            index != self._currently_loaded_network_index
+            and self._network_paths[self._currently_loaded_network_index] != self._network_paths[index]
+        ):
+            self._currently_loaded_network.stop_function()
+            self._currently_loaded_network_index = index
+            self.load()
+
+    @_raise_exception_if_unloaded
+    def indexed_create_image_vector(self: "MultiNetwork", index: int, data: SingleVector) -> RGBInt8ImageType:
+        self._load_network_at_index(index)
+        return self._currently_loaded_network.network_interface.create_image_vector(data)
+
+    @_raise_exception_if_unloaded
+    def indexed_create_image_matrix(self: "MultiNetwork", index: int, data: SingleMatrix) -> RGBInt8ImageType:
+        self._load_network_at_index(index)
+        return self._currently_loaded_network.network_interface.create_image_matrix(data)
+
+    @_raise_exception_if_unloaded
+    def indexed_create_image_generic(
+        self: "MultiNetwork", index: int, data: Union[SingleVector, SingleMatrix]
+    ) -> RGBInt8ImageType:
+        self._load_network_at_index(index)
+        return self._currently_loaded_network.network_interface.create_image_generic(data)
+
+    @_raise_exception_if_unloaded
+    def indexed_create_images_batch(self: "MultiNetwork", index: int, data: np.ndarray) -> np.ndarray:
+        """Addition: many frames of ONE network per call; (N,512) or (N,num_ws,512) -> (N,H,W,3)."""
+        self._load_network_at_index(index)
+        batch_function = self._currently_loaded_network.network_interface.create_images_batch
+        if batch_function is None:  # an interface built from the reference's four fields only
+            generic = self._currently_loaded_network.network_interface.create_image_generic
+            return np.stack([generic(item) for item in data])
+        return batch_function(data)
+
+    def load(self: "MultiNetwork") -> None:
+        network_path = self._network_paths[self._currently_loaded_network_index]
+        LOGGER.info(f"Loading network: {network_path}")
+        self._currently_loaded_network = create_network_interface_process(network_path=network_path)
+        self._expected_vector_length = self._currently_loaded_network.network_interface.expected_vector_length
+
+    @_raise_exception_if_unloaded
+    def unload(self: "MultiNetwork") -> None:
+        self._currently_loaded_network.stop_function()
+
+    @property
+    def network_indices(self: "MultiNetwork") -> List[int]:
+        return [index for index, _ in enumerate(self._network_paths)]
+
+    @property
+    def network_paths(self: "MultiNetwork") -> List[Path]:
+        return self._network_paths
+
+
+def parse_network_paths(
+    networks_directory: Optional[str], networks: Optional[List[str]], networks_json: Optional[str]
+) -> List[Path]:
+    """CLI input -> list of network paths; ValueError on any problem (reference :643-682)."""
+    all_networks: List[Path] = []
+    if networks_directory is not None:
+        all_networks += sorted_networks_in_directory(networks_directory=Path(networks_directory))
+    if networks is not None:
+        all_networks += list(map(Path, networks))
+    if networks_json is not None:
+        LOGGER.info(f"Loading network JSON: {networks_json}")
+        try:
+            with open(networks_json) as f:
+                all_networks += list(map(Path, NetworksFile(**json.load(f)).networks))
+        except pydantic.ValidationError as e:  # pydantic v2 spelling of error_wrappers.ValidationError
+            raise ValueError("Ran into formatting problem with networks JSON.") from e
+        except Exception as e:
+            raise ValueError("Couldn't open networks JSON.") from e
+    if not all_networks:
+        raise ValueError("No networks given, cannot continue.")
+    LOGGER.info("Discovered networks: ")
+    for path in all_networks:
+        LOGGER.info(f"\t{path}")
+    return all_networks
+
+
+class NetworksFile(BaseModel):
+    """A .json file listing network paths (reference :685-690)."""
+
+    networks: List[FilePath]

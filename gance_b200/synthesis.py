@@ -8,7 +8,7 @@ Replaces the TF1 graph the reference runs in `wrap_loaded_network`
   create_image_matrix -> Gs.components.synthesis.run(w+, randomize_noise=False) -> `run_matrices`
 Both accept a whole batch of frames (the reference renders one frame per call).
 
-Data flow per batch (NHWC activations, `mode` = "bf16" | "fp32"; DESIGN.md has the full table):
+Data flow per batch (NHWC activations, `mode` = "bf16" | "fp16" | "fp32"; DESIGN.md has the full table):
   styles/demod for every layer      gance_style_demod   (fp32)
   const * s0                        gance_const_input
   4x4 conv                          gance_modconv3x3            -> x (unscaled)
@@ -31,7 +31,11 @@ from gance_b200.networks.generator_spec import (
     synthesis_layers,
 )
 
-MODES = {"fp32": (_lib.GANCE_F32, torch.float32), "bf16": (_lib.GANCE_BF16, torch.bfloat16)}
+MODES = {
+    "fp32": (_lib.GANCE_F32, torch.float32),
+    "bf16": (_lib.GANCE_BF16, torch.bfloat16),
+    "fp16": (_lib.GANCE_F16, torch.float16),
+}
 NOISE_MODES = ("const", "random", "provided", "none")
 
 
@@ -56,6 +60,7 @@ class GeneratorOnDevice:
         self.resolution = spec.resolution
         self.convs, self.rgbs = synthesis_layers(spec)
         self._buffers: Dict[tuple, torch.Tensor] = {}
+        self.profile_events: Optional[list] = None  # set to [] to collect (name, cuda event) marks
         self._upload(variables)
 
     # ---- weights ---------------------------------------------------------------------------------
@@ -87,7 +92,7 @@ class GeneratorOnDevice:
             if self.mode == "fp32":
                 self.conv_w.append(hwio.contiguous())  # [3,3,Cin,Cout]
             else:
-                self.conv_w.append(hwio.permute(3, 0, 1, 2).contiguous().to(torch.bfloat16))  # [Cout,3,3,Cin]
+                self.conv_w.append(hwio.permute(3, 0, 1, 2).contiguous().to(self.torch_dtype))  # [Cout,3,3,Cin]
             self.conv_mod_w.append(f32(v[f"{conv.name}/mod_weight"] * (1.0 / np.sqrt(512.0))))
             self.conv_mod_b.append(f32(v[f"{conv.name}/mod_bias"]))
             self.conv_bias.append(f32(v[f"{conv.name}/bias"]))
@@ -125,6 +130,13 @@ class GeneratorOnDevice:
 
     def _stream(self) -> int:
         return torch.cuda.current_stream(self.device).cuda_stream
+
+    def _mark(self, name: str) -> None:
+        """Per-layer timing for tools/profile_layers.py: an event after the step called `name`."""
+        if self.profile_events is not None:
+            event = torch.cuda.Event(enable_timing=True)
+            event.record(torch.cuda.current_stream(self.device))
+            self.profile_events.append((name, event))
 
     # ---- entry points ----------------------------------------------------------------------------
     def mapping(self, z: torch.Tensor, truncation_psi: float = 1.2) -> torch.Tensor:
@@ -189,6 +201,7 @@ class GeneratorOnDevice:
                 "gance_style_demod(torgb)",
             )
             rgb_styles.append(s)
+        self._mark("styles")
 
         def layer_noise(i: int, side: int):
             if noise_mode == "none" or (noise_mode != "provided" and self.conv_strength[i] == 0.0):
@@ -213,6 +226,7 @@ class GeneratorOnDevice:
                                  self.conv_strength[0], self.conv_bias[0].data_ptr(), None, x.data_ptr(), stream),
             "gance_modconv3x3(4x4)",
         )
+        self._mark("4/conv")
         last = len(self.rgbs) - 1
         want_float = return_float_image or last != 0
         y = self._buffer("skip4", (batch, 4, 4, 4), torch.float32) if want_float else None
@@ -222,6 +236,7 @@ class GeneratorOnDevice:
                                  frames.data_ptr() if last == 0 else None, stream),
             "gance_torgb_skip(4x4)",
         )
+        self._mark("4/torgb")
 
         # -- one block per resolution
         for block in range(1, len(self.rgbs)):
@@ -240,6 +255,7 @@ class GeneratorOnDevice:
                                              scratch.data_ptr(), x_up.data_ptr(), stream),
                 f"gance_modconv3x3_up2_fir({side})",
             )
+            self._mark(f"{side}/conv0_up")
             x = self._buffer(f"act{side}", (batch, side, side, conv.out_channels), dt)
             nz, nz_stride = layer_noise(conv_i, side)
             _lib.check(
@@ -249,6 +265,7 @@ class GeneratorOnDevice:
                                      self.conv_bias[conv_i].data_ptr(), None, x.data_ptr(), stream),
                 f"gance_modconv3x3({side})",
             )
+            self._mark(f"{side}/conv1")
             is_last = block == last
             want_float = return_float_image or not is_last
             y_out = self._buffer(f"skip{side}", (batch, side, side, 4), torch.float32) if want_float else None
@@ -259,6 +276,7 @@ class GeneratorOnDevice:
                                      frames.data_ptr() if is_last else None, stream),
                 f"gance_torgb_skip({side})",
             )
+            self._mark(f"{side}/torgb")
             y = y_out
         if return_float_image:
             return frames, y

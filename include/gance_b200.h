@@ -26,6 +26,8 @@
  *   - activations are NHWC; `dtype` selects the activation/weight element type:
  *       GANCE_F32  = 0  fp32 validation mode (CUDA-core FMA, fp32 everywhere)
  *       GANCE_BF16 = 1  bf16 operands, fp32 accumulate in TMEM (tcgen05), fp32 epilogue
+ *       GANCE_F16  = 2  as GANCE_BF16 with IEEE half operands (same kernels, same speed,
+ *                       11-bit instead of 8-bit significand; |x| must stay below 65504)
  *   - there is NO CPU fallback: without a CUDA device every compute entry fails.
  */
 #ifndef GANCE_B200_H
@@ -41,6 +43,7 @@ extern "C" {
 
 #define GANCE_F32 0
 #define GANCE_BF16 1
+#define GANCE_F16 2
 
 #define GANCE_OK 0
 #define GANCE_E_NULL 1        /* a required pointer was NULL */
@@ -90,12 +93,12 @@ int gance_const_input(const float* konst, const float* styles, int batch, int ch
  * layer's styles. out = lrelu(acc*demod[b,co] + noise*noise_strength + bias[co], 0.2)*sqrt(2),
  * then * next_styles[b,co] when next_styles != NULL (pre-scaling for the next conv).
  *   x      [B, H+2-2*pad, W+2-2*pad, Cin]   pad = 1: SAME (zero border), pad = 0: VALID
- *   weight GANCE_BF16: [Cout][3][3][Cin] bf16 (K-major GEMM operand, fed by TMA)
+ *   weight GANCE_BF16 / GANCE_F16: [Cout][3][3][Cin] bf16 / half (K-major GEMM operand, fed by TMA)
  *          GANCE_F32 : [3][3][Cin][Cout] f32 (the TF HWIO layout)
  *          both pre-multiplied by 1/sqrt(9*Cin)
  *   noise  [H,W] f32 (noise_batch_stride = 0) or [B,H,W] (stride = H*W); may be NULL
  *   out    [B,H,W,Cout]
- * GANCE_BF16 runs the tcgen05/TMEM implicit GEMM and needs Cin % 32 == 0, Cout % 32 == 0. */
+ * GANCE_BF16 / GANCE_F16 run the tcgen05/TMEM implicit GEMM and need Cin % 32 == 0, Cout % 32 == 0. */
 int gance_modconv3x3(const void* x, int dtype, int batch, int h_out, int w_out, int c_in,
                      int c_out, int pad, const void* weight, const float* demod,
                      const float* noise, long long noise_batch_stride, float noise_strength,
@@ -133,18 +136,20 @@ int gance_to_uint8_nhwc(const float* y, int batch, int h, int w, uint8_t* frames
 
 /* ---- audio: windowed real DFT -> magnitude ------------------------------------------------------
  * apply_spectrogram.compute_spectrogram (apply_spectrogram.py:49-82) up to |X|: frames of
- * `window` (=vector_length-2) samples at hop vector_length, periodic Hann, DFT bins
- * [0, window/2). audio f32 [T*vector_length] -> mag f64 [T, window/2]; block maxima of |X| are
- * written to partial_max[grid] for the global max the dB conversion needs. */
+ * window = vector_length-2 samples at hop vector_length, periodic Hann np.hanning(window+1)[:-1],
+ * DFT bins [0, window/2), all in float64. audio f32 [T*vector_length] -> mag f64 [T, window/2].
+ * global_max is an 8-byte device slot that receives max|X| (needed by the dB conversion). */
 int gance_stft_mag(const float* audio, int num_frames, int vector_length, double* mag,
                    double* global_max, void* stream);
 
-/* 20*log10(mag/max) (apply_spectrogram.py:80-81), Fourier resample bins -> vector_length
- * (scipy.signal.resample as the fixed matrix `resample_matrix` [vector_length, bins] f64,
- * vector_sources_common.py:211-230); writes out [T, vector_length] f64 and its global min/max
- * (minmax[0], minmax[1]) for the min-max scale of apply_spectrogram.py:43. */
+/* 20*log10(mag/max) (apply_spectrogram.py:80-81) followed by the Fourier resample bins ->
+ * vector_length of reshape_spectrogram_to_vectors (apply_spectrogram.py:20-46,
+ * vector_sources_common.py:211-230): scipy.signal.resample is linear, so it is applied as the
+ * fixed matrix resample_matrix_t [bins, vector_length] f64 (host-built, transposed for coalescing).
+ * out [T, vector_length] f64. minmax is a 16-byte device slot that receives the global min and max
+ * of `out` in an order-preserving integer encoding; pass it on to gance_minmax_savgol_time. */
 int gance_db_resample(const double* mag, const double* global_max, int num_frames, int bins,
-                      int vector_length, const double* resample_matrix, double* out,
+                      int vector_length, const double* resample_matrix_t, double* out,
                       double* minmax, void* stream);
 
 /* Min-max scale to [range_lo, range_hi] fused with the Savitzky-Golay filter along TIME
@@ -167,8 +172,10 @@ int gance_roll_savgol_vector(const double* in, const int* shift, int num_frames,
  * noise-blend:      z[t,i]     = noise[t,i]*(1-alpha) + spec[t,i]*alpha           (noise f32)
  * projection-blend: w[t,r,i]   = r < blend_depth ? proj[t/dup,i]*(1-alpha) + spec[t,i]*alpha
  *                                                : proj[t/dup,i]                  (proj f32 [F,L])
- * Outputs: latents_f64 (what the reference returns, may be NULL) and latents_f32 (what the
- * generator consumes, may be NULL). */
+ * `a*(1-alpha)` is a float32 product as in the reference (float32 array times a Python float); the
+ * sum is float64 without FMA contraction, so results are bit-identical to numpy's.
+ * Outputs (either may be NULL): latents_f64 in the reference's layout - (T*L,) resp. (depth, T*L) -
+ * and latents_f32 in the generator's layout - [T,L] resp. [T,depth,L]. */
 int gance_alpha_blend_noise(const double* spec, const float* noise, double alpha, int num_frames,
                             int vector_length, double* latents_f64, float* latents_f32,
                             void* stream);

@@ -56,16 +56,17 @@ def test_fp32_mode_matches_oracle(resolution, perturbed):
     assert within >= 0.999
 
 
+@pytest.mark.parametrize("mode", ["bf16", "fp16"])
 @pytest.mark.parametrize("resolution,perturbed", [(32, False), (64, True), (128, True)])
-def test_bf16_mode_matches_oracle(resolution, perturbed):
+def test_16bit_modes_match_oracle(mode, resolution, perturbed):
     spec, variables, oracle, z = _case(resolution, 1, perturbed, 2)
-    gen = GeneratorOnDevice(spec, variables, _device(), mode="bf16")
+    gen = GeneratorOnDevice(spec, variables, _device(), mode=mode)
     want_w = oracle.truncate(oracle.mapping(z), 1.2)
     frames, image = gen.synthesis(torch.as_tensor(want_w.numpy()), noise_mode="const", return_float_image=True)
     want = oracle.synthesis(want_w.numpy())
     got = image[..., :3].permute(0, 3, 1, 2).double().cpu()
     within, worst, exact = lsb_stats(frames.cpu().numpy(), ref.convert_images_to_uint8(want))
-    print(f"bf16 mode {resolution}^2 perturbed={perturbed}: float max-abs {float((got - want).abs().max()):.3e}; "
+    print(f"{mode} mode {resolution}^2 perturbed={perturbed}: float max-abs {float((got - want).abs().max()):.3e}; "
           f"uint8 exact {exact:.5f}, within 1 LSB {within:.5f}, worst {worst}")
     assert within >= 0.999
 
@@ -109,7 +110,7 @@ def test_batch_independence_and_ordering():
 def test_config1_256_frames_match_oracle():
     """BASELINE config 1 shape: 256^2 config-f generator; 2 of its frames against the fp64 oracle."""
     spec, variables, oracle, z = _case(256, 0, False, 2)
-    for mode in ("fp32", "bf16"):
+    for mode in ("fp32", "bf16", "fp16"):
         gen = GeneratorOnDevice(spec, variables, _device(), mode=mode)
         frames = gen.run_vectors(torch.as_tensor(z), noise_mode="const")
         assert frames.shape == (2, 256, 256, 3) and int(frames.sum()) > 0

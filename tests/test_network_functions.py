@@ -1,0 +1,186 @@
+"""
+Boundary behaviour of gance_b200.network_interface.network_functions on CPU (no GPU needed).
+`test_multi_network_unloaded_leads_to_errors` is the reference's own contract test
+(/root/reference/test/test_network_functions.py:29-97) with pytest-mock replaced by unittest.mock.
+"""
+
+import json
+from pathlib import Path
+from typing import Union
+from unittest import mock
+
+import numpy as np
+import pytest
+
+from gance_b200 import _lib
+from gance_b200.gance_types import RGBInt8ImageType
+from gance_b200.network_interface import network_functions
+from gance_b200.network_interface.network_functions import (
+    MultiNetwork,
+    NetworkInterface,
+    NetworkInterfaceInProcess,
+    parse_network_paths,
+)
+from gance_b200.networks import container
+from gance_b200.vector_sources.vector_types import SingleMatrix, SingleVector, is_vector
+
+
+@pytest.mark.parametrize("load", [True, False])
+def test_multi_network_unloaded_leads_to_errors(load: bool) -> None:
+    expected_vector_length = 10
+    expected_image = RGBInt8ImageType(np.zeros((10, 10, 3)))
+
+    def fake_vector_function(data: Union[SingleVector, SingleMatrix]) -> RGBInt8ImageType:  # pylint: disable=unused-argument
+        return expected_image
+
+    patched_stop = mock.Mock()
+    with mock.patch.object(
+        network_functions,
+        "create_network_interface_process",
+        return_value=NetworkInterfaceInProcess(
+            NetworkInterface(
+                create_image_vector=fake_vector_function,
+                create_image_matrix=fake_vector_function,
+                create_image_generic=fake_vector_function,
+                expected_vector_length=expected_vector_length,
+            ),
+            stop_function=patched_stop,
+        ),
+    ) as patched_load:
+
+        def make_network() -> MultiNetwork:
+            return MultiNetwork(network_paths=[Path("sample_batch_1_network.pkl")])
+
+        assert not patched_stop.called
+        if load:
+            with make_network() as multi_network:
+                assert multi_network.expected_vector_length == expected_vector_length
+                assert (
+                    multi_network.indexed_create_image_vector(index=0, data=SingleVector(np.zeros((10,))))
+                    == expected_image
+                ).all()
+                # the batched addition degrades to per-frame calls on a four-field interface
+                batch = multi_network.indexed_create_images_batch(0, np.zeros((3, 10)))
+                assert batch.shape == (3, 10, 10, 3)
+            assert patched_load.called
+            assert patched_stop.called
+        else:
+            multi_network = make_network()
+            with pytest.raises(ValueError):
+                print(multi_network.expected_vector_length)
+            with pytest.raises(ValueError):
+                multi_network.indexed_create_image_vector(index=0, data=SingleVector(np.zeros((10,))))
+            assert not patched_load.called
+            assert not patched_stop.called
+
+
+def test_network_interface_field_order_is_the_references():
+    assert NetworkInterface._fields[:4] == (
+        "expected_vector_length",
+        "create_image_vector",
+        "create_image_matrix",
+        "create_image_generic",
+    )
+
+
+def test_identical_paths_do_not_reload():
+    """Reference :552-556: the same path at two indices is not a switch."""
+    loads = []
+
+    def fake_process(network_path, **_):
+        loads.append(network_path)
+        f = lambda data: np.zeros((2, 2, 3), np.uint8)  # noqa: E731
+        return NetworkInterfaceInProcess(NetworkInterface(512, f, f, f), stop_function=lambda: None)
+
+    with mock.patch.object(network_functions, "create_network_interface_process", side_effect=fake_process):
+        net = MultiNetwork([Path("a.pkl"), Path("a.pkl"), Path("b.pkl")], load=True)
+        net.indexed_create_image_vector(1, np.zeros(512))
+        assert loads == [Path("a.pkl")]
+        net.indexed_create_image_vector(2, np.zeros(512))
+        assert loads == [Path("a.pkl"), Path("b.pkl")]
+        assert net.network_indices == [0, 1, 2]
+
+
+def test_context_manager_returns_none_when_the_gpu_cannot_load():
+    """Reference :516-529. On this CPU-only machine loading a real file raises RuntimeError."""
+    with mock.patch.object(network_functions, "create_network_interface_process", side_effect=RuntimeError("no gpu")):
+        with MultiNetwork([Path("a.pkl")]) as net:
+            assert net is None
+
+
+def test_parse_network_paths(tmp_path):
+    for name in ("b.pkl", "a.pkl", "ignored.txt"):
+        (tmp_path / name).write_bytes(b"")
+    assert parse_network_paths(str(tmp_path), None, None) == [tmp_path / "a.pkl", tmp_path / "b.pkl"]
+    assert parse_network_paths(None, ["x.pkl"], None) == [Path("x.pkl")]
+    good = tmp_path / "networks.json"
+    good.write_text(json.dumps({"networks": [str(tmp_path / "a.pkl")]}))
+    assert parse_network_paths(None, None, str(good)) == [tmp_path / "a.pkl"]
+    bad = tmp_path / "bad.json"
+    bad.write_text(json.dumps({"networks": [str(tmp_path / "missing.pkl")]}))
+    with pytest.raises(ValueError):
+        parse_network_paths(None, None, str(bad))
+    with pytest.raises(ValueError):
+        parse_network_paths(None, None, str(tmp_path / "nope.json"))
+    with pytest.raises(ValueError):
+        parse_network_paths(None, None, None)
+
+
+def test_is_vector_truth_table():
+    """/root/reference/test/test_vector_sources_common.py:86-97."""
+    assert is_vector(np.zeros((512,)))
+    assert not is_vector(np.zeros((18, 512)))
+    assert not is_vector(np.zeros((1, 512)))
+    assert not is_vector(np.zeros((3, 18, 512)))
+
+
+def test_network_file_round_trip(tmp_path):
+    path = container.write_synthetic_network(tmp_path / "net.pkl", resolution=32, seed=5, perturbed=True)
+    loaded = container.read_network(path)
+    assert loaded.spec.resolution == 32 and loaded.input_shape[1] == 512
+    again = container.read_network(path)
+    assert all(np.array_equal(loaded.variables[k], again.variables[k]) for k in loaded.variables)
+    explicit = container.write_variables_network(tmp_path / "explicit.pkl", loaded.variables)
+    from_vars = container.read_network(explicit)
+    assert from_vars.spec == loaded.spec
+    broken = dict(loaded.variables)
+    broken.pop("dlatent_avg")
+    with pytest.raises(ValueError):
+        container.read_network(container.write_variables_network(tmp_path / "broken.pkl", broken))
+    (tmp_path / "junk.pkl").write_bytes(b"not a pickle")
+    with pytest.raises(Exception):
+        container.read_network(tmp_path / "junk.pkl")
+
+
+def test_loading_a_network_without_a_gpu_fails_loudly(tmp_path):
+    """No silent CPU path: on a machine without CUDA the load raises (RuntimeError -> __enter__ None)."""
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("needs a machine without CUDA")
+    path = container.write_synthetic_network(tmp_path / "net.pkl", resolution=8, seed=0)
+    with pytest.raises(RuntimeError):
+        network_functions.create_network_interface_process(path)
+    with MultiNetwork([path]) as net:
+        assert net is None
+
+
+def test_c_abi_library_exports_every_declared_symbol():
+    """The shared library loads on CPU and exports everything include/gance_b200.h declares."""
+    import re
+
+    header = (Path(__file__).resolve().parents[1] / "include" / "gance_b200.h").read_text()
+    header = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    declared = set(re.findall(r"\b(gance_[a-z0-9_]+)\s*\(", header))
+    assert len(declared) >= 10
+    lib = _lib.load_library()
+    for name in declared:
+        assert hasattr(lib, name), f"{name} is declared in the header but not exported"
+    assert declared == set(_lib.EXPORTED_SYMBOLS)
+    assert lib.gance_abi_version() == 1
+    # no compute without a GPU: init must refuse instead of falling back
+    import torch
+
+    if not torch.cuda.is_available():
+        assert lib.gance_init(0) != 0
+        assert "no CPU fallback" in _lib.last_error()

@@ -12,6 +12,6 @@ run() { # name, pytest args...
 : > gpurun_out/summary.txt
 run kernels_small tests/test_gpu_kernels.py -k "not modconv3x3 and not up_convolution"
 run conv_fp32 tests/test_gpu_kernels.py -k "fp32 and (modconv3x3 or up_convolution)"
-run conv_tc tests/test_gpu_kernels.py -k "tcgen05 or (bf16 and up_convolution)"
+run conv_tc tests/test_gpu_kernels.py -k "tcgen05 or ((bf16 or fp16) and up_convolution)"
 run synthesis_fp32 tests/test_gpu_synthesis.py -k "fp32 or vector_and_matrix"
-run synthesis_bf16 tests/test_gpu_synthesis.py -k "bf16 or batch_independence or config1"
+run synthesis_16bit tests/test_gpu_synthesis.py -k "16bit or batch_independence or config1"
