@@ -62,10 +62,8 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     const uint32_t addr = smem_u32(bar);
     uint32_t done;
-    uint32_t spins = 0;
-    do {  // try_wait suspends the thread in hardware until the phase flips or a time-out elapses
-        // A pipeline bug must surface as a launch error, never as a hung GPU: give up after ~seconds.
-        if (++spins == (1u << 26)) __trap();
+    long long start = 0;
+    for (;;) {  // try_wait suspends the thread in hardware until the phase flips or a time-out elapses
         asm volatile(
             "{\n\t"
             ".reg .pred p;\n\t"
@@ -75,7 +73,11 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
             : "=r"(done)
             : "r"(addr), "r"(parity)
             : "memory");
-    } while (!done);
+        if (done) break;
+        // A pipeline bug must surface as a launch error, never as a hung GPU: give up after ~2 s.
+        if (start == 0) start = clock64();
+        else if (clock64() - start > 4000000000ll) __trap();
+    }
 }
 __device__ __forceinline__ void fence_barrier_init() {
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
