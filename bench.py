@@ -1,0 +1,371 @@
+#!/usr/bin/env python
+"""
+bench.py - frames/sec of 1024^2 StyleGAN2 config-f frames from audio latents (BASELINE.json).
+
+    python bench.py --gpus N --steps K --warmup W            # this build (CUDA, libgance_b200.so)
+    python bench.py --impl reference --gpus N --steps K ...  # the CPU implementation of the path
+
+One STEP = one batch of 32 music latents (z from the noise-blend vector source) through
+G_mapping + truncation + G_synthesis (fresh noise per call, as `create_image_vector` does) ->
+32 uint8 1024x1024x3 frames, on every rank; with N > 1 the step ends with the NCCL gather of the
+ranks' uint8 frames to rank 0 (the encoder rank). Weak scaling: every rank renders its own
+contiguous frame range of the track, weights replicated.
+
+Prints ONE JSON line (rank 0): value = frames/s over all ranks with inputs resident in HBM; e2e =
+the same through the NetworkInterface boundary with host latents in / host frames out; roofline =
+the modulated-convolution kernel's achieved TFLOP/s (CUDA events around its launches) against the
+measured bf16 peak; cpu_baseline = the CPU restatement timed on this box's cores.
+"""
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+def _baseline_metric() -> str:
+    try:
+        return json.loads((ROOT / "BASELINE.json").read_text())["metric"]
+    except Exception:  # pylint: disable=broad-except
+        return "frames/sec, 1024\u00b2 StyleGAN2-f from audio latents, 1/2/4/8 B200; % tensor peak"
+
+
+METRIC = _baseline_metric()
+UNIT = "frames/s"
+# SURVEY.md §8(d) / BASELINE.md §3: algorithmic work per frame (conv + ToRGB MACs x2; HBM with 16-bit activations)
+FLOP_PER_FRAME = {1024: 148.52e9, 512: 119.33e9, 256: 90.24e9}
+HBM_BYTES_PER_FRAME = {1024: 627.7e6 + 3.15e6, 512: 297.4e6 + 0.79e6, 256: 139.3e6 + 0.2e6}
+FALLBACK_PEAKS = {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=32)
+    ap.add_argument("--resolution", type=int, default=1024)
+    ap.add_argument("--mode", default="fp16", choices=["fp16", "bf16", "fp32"])
+    ap.add_argument("--track-seconds", type=float, default=24.0, help="length of the synthetic chirp track")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def measured_peaks():
+    path = ROOT / "MEASURED_PEAKS.json"
+    if path.exists():
+        try:
+            data = json.loads(path.read_text())
+            return {k: float(data[k]) for k in FALLBACK_PEAKS}, "measured (MEASURED_PEAKS.json)"
+        except Exception:  # pylint: disable=broad-except
+            pass
+    return dict(FALLBACK_PEAKS), "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+
+    QUERY = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.rows = []
+        self.proc = None
+        self.gpu_index = gpu_index
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu_index), f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits",
+                 "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) >= 7:
+                self.rows.append(parts)
+
+    def __exit__(self, *exc):
+        if self.proc is not None:
+            time.sleep(0.25)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        sm = [float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit()]
+        sm_max = [float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()]
+        reasons = []
+        for idx, name in ((3, "hw_slowdown"), (4, "hw_thermal_slowdown"), (5, "sw_thermal_slowdown"), (6, "sw_power_cap")):
+            if any(r[idx].lower().startswith("active") for r in self.rows):
+                reasons.append(name)
+        power = [float(r[2]) for r in self.rows if r[2].replace(".", "").isdigit()]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(sm_max) if sm_max else None,
+                "power_w_max": max(power) if power else None, "samples": len(self.rows), "reasons": reasons}
+
+
+def track_latents(seconds: float, device):
+    """Synthetic chirp WAV -> noise-blend z latents [T,512] float32 on the device (our CUDA audio path)."""
+    from gance_b200 import synthetic
+    from gance_b200.data_into_network_visualization import visualization_inputs
+    from gance_b200.vector_sources import music
+
+    wav = synthetic.chirp_wav(seconds)
+    from gance_b200 import audio_device
+
+    as_float = audio_device.pcm_to_float(wav, device).cpu().numpy()
+    scaled = music.read_wavs_scale_for_video([music.WavFileProperties(44100, as_float, "chirp")], 512,
+                                             frames_per_second=60.0).wav_data
+    result = visualization_inputs.alpha_blend_vectors_max_rms_power_audio_device(
+        alpha=0.25, fft_roll_enabled=True, fft_amplitude_range=(-5, 5), time_series_audio_vectors=scaled,
+        vector_length=512, network_indices=[0])
+    return result.latents
+
+
+def cpu_frames_per_second(resolution: int, frames: int, seed: int = 0):
+    """The CPU restatement (oracle/, torch-CPU fp32, batch 1 per frame like the reference), all host threads."""
+    import torch
+
+    from gance_b200.networks.generator_spec import GeneratorSpec, random_init_variables
+    from oracle import stylegan2_ref
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    spec = GeneratorSpec(resolution)
+    generator = stylegan2_ref.ReferenceGenerator(random_init_variables(spec, seed, perturbed=True), torch.float32)
+    z = np.random.RandomState(1).randn(frames + 1, 512)
+    with torch.no_grad():
+        stylegan2_ref.convert_images_to_uint8(generator.run_vector(z[:1]))  # warm-up (thread pool, allocator)
+        start = time.perf_counter()
+        for i in range(frames):
+            stylegan2_ref.convert_images_to_uint8(generator.run_vector(z[i + 1: i + 2]))
+        elapsed = time.perf_counter() - start
+    return frames / elapsed, cores, elapsed
+
+
+def run_reference(args):
+    """--impl reference: the CPU implementation of the path on this box's host cores (rank 0 only)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    frames_per_step = 1  # bounded sample: one 1024^2 frame per step instead of 32
+    import torch
+
+    from gance_b200.networks.generator_spec import GeneratorSpec, random_init_variables
+    from oracle import stylegan2_ref
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    spec = GeneratorSpec(args.resolution)
+    generator = stylegan2_ref.ReferenceGenerator(random_init_variables(spec, 0, perturbed=True), torch.float32)
+    z = np.random.RandomState(1).randn((args.steps + args.warmup) * frames_per_step, 512)
+    with torch.no_grad():
+        for i in range(args.warmup):
+            stylegan2_ref.convert_images_to_uint8(generator.run_vector(z[i: i + 1]))
+        start = time.perf_counter()
+        for i in range(args.warmup, args.warmup + args.steps):
+            stylegan2_ref.convert_images_to_uint8(generator.run_vector(z[i: i + 1]))
+        elapsed = time.perf_counter() - start
+    value = args.steps * frames_per_step / elapsed
+    sample = (f"{frames_per_step} frame of the {args.resolution}^2 config-f generator per step (the GPU arm renders "
+              f"{args.batch}), batch 1 as the reference does, torch-CPU fp32 restatement of NVlabs/stylegan2 "
+              "(oracle/stylegan2_ref.py; the reference's TF1 code is absent), G_mapping+G_synthesis+uint8")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": elapsed / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
+        "config": {"workload": f"StyleGAN2 config-f {args.resolution}x{args.resolution} random-init, frame synthesis "
+                               "from music latents (BASELINE configs[1])", "frames_per_step": frames_per_step},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    from gance_b200 import _lib
+    from gance_b200.frame_sharding import frame_range, gather_frames
+    from gance_b200.network_interface import network_functions
+    from gance_b200.networks import container
+    from gance_b200.synthesis import GeneratorOnDevice  # noqa: F401  (fails loudly without the CUDA library)
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: the hot path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    batch, res = args.batch, args.resolution
+
+    # ---- set-up (untimed): network file -> resident weights; WAV -> latents on the device ----------
+    network_path = Path(f"/tmp/gance_b200_bench_{res}_{rank}.pkl")
+    container.write_synthetic_network(network_path, res, seed=0, perturbed=True)
+    networks = network_functions.MultiNetwork([network_path], load=False)
+    network_functions.DEFAULT_MODE = args.mode
+    generator = network_functions.resident_generator(network_path, args.mode)
+    networks.load()
+    latents_all = track_latents(args.track_seconds, device)  # [T,512] f32, identical on every rank
+    total_frames = latents_all.shape[0]
+    start_frame, stop_frame = frame_range(rank, world, total_frames)
+    latents = latents_all[start_frame:stop_frame].contiguous()
+    local_frames = latents.shape[0]
+    if local_frames < batch:
+        raise RuntimeError(f"track too short: rank {rank} has {local_frames} frames, needs {batch}")
+    frames_out = torch.empty((batch, res, res, 3), dtype=torch.uint8, device=device)
+
+    def step(i: int):
+        offset = (i * batch) % (local_frames - batch + 1)
+        generator.run_vectors(latents[offset: offset + batch], truncation_psi=1.2, noise_mode="random", out=frames_out)
+        if world > 1:
+            return gather_frames(frames_out, [batch] * world, dst=0)
+        return frames_out
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(args.warmup):
+        step(i)
+    barrier()
+    launches_before = _lib.launch_count()
+    start_event, stop_event = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local_rank) as clocks:
+        barrier()
+        start_event.record()
+        for i in range(args.steps):
+            step(args.warmup + i)
+        stop_event.record()
+        barrier()
+    elapsed_ms = start_event.elapsed_time(stop_event)
+    launches = _lib.launch_count() - launches_before
+    if world > 1:
+        t = torch.tensor([elapsed_ms], device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        elapsed_ms = float(t.item())
+    value = world * batch * args.steps / (elapsed_ms * 1e-3)
+
+    # ---- roofline of the dominant kernel: CUDA events around every conv launch of a step ---------
+    peaks, peak_source = measured_peaks()
+    conv_ms, other_ms = [], []
+    for i in range(3):
+        generator.profile_events = []
+        begin = torch.cuda.Event(enable_timing=True)
+        begin.record()
+        generator.run_vectors(latents[:batch], truncation_psi=1.2, noise_mode="random", out=frames_out)
+        torch.cuda.synchronize()
+        prev, conv, other = begin, 0.0, 0.0
+        for name, event in generator.profile_events:
+            dt = prev.elapsed_time(event)
+            if "conv" in name:
+                conv += dt
+            else:
+                other += dt
+            prev = event
+        conv_ms.append(conv)
+        other_ms.append(other)
+    generator.profile_events = None
+    conv_step_ms = float(np.median(conv_ms))
+    flop_per_step = FLOP_PER_FRAME.get(res, 0.0) * batch
+    achieved_tflops = flop_per_step / (conv_step_ms * 1e-3) / 1e12 if conv_step_ms > 0 else 0.0
+    tensor_peak = peaks["bf16_tflops_sustained"]
+    roofline = {
+        "bound": "tensor", "kernel": "modconv3x3_tc_kernel (all modulated-convolution launches of a step, incl. up-FIR staging)",
+        "achieved": achieved_tflops, "peak": tensor_peak, "unit": "TFLOP/s", "frac": achieved_tflops / tensor_peak,
+        "peak_source": f"bf16_tflops_sustained, {peak_source}", "traffic": None,
+        "conv_ms_per_step": conv_step_ms, "other_ms_per_step": float(np.median(other_ms)),
+        "hbm_algorithmic_gbs_whole_step": HBM_BYTES_PER_FRAME.get(res, 0.0) * batch / (elapsed_ms / args.steps * 1e-3) / 1e9,
+        "hbm_peak_gbs": peaks["hbm_gbs"],
+    }
+
+    # ---- e2e through the boundary: host latents -> MultiNetwork.indexed_render_batches -> host frames
+    e2e = None
+    if not args.no_e2e:
+        host_latents = latents.cpu().numpy()
+        renderer_steps = args.steps
+
+        def host_batches(count, first):
+            for i in range(count):
+                offset = ((first + i) * batch) % (local_frames - batch + 1)
+                yield host_latents[offset: offset + batch]
+
+        checksum = 0
+        for frames in networks.indexed_render_batches(0, host_batches(args.warmup, 0), max_batch=batch):
+            checksum += int(frames[0, 0, 0, 0])
+        barrier()
+        t0 = time.perf_counter()
+        for frames in networks.indexed_render_batches(0, host_batches(renderer_steps, args.warmup), max_batch=batch):
+            checksum += int(frames[0, 0, 0, 0])  # touch the host result of every step
+        torch.cuda.synchronize()
+        e2e_s = time.perf_counter() - t0
+        if world > 1:
+            t = torch.tensor([e2e_s], device=device)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            e2e_s = float(t.item())
+        e2e = {"value": world * batch * renderer_steps / e2e_s, "unit": UNIT,
+               "h2d_bytes_per_step": batch * 512 * 4, "d2h_bytes_per_step": batch * res * res * 3,
+               "api": "MultiNetwork.indexed_render_batches (pinned host latents in, pinned host uint8 frames out)"}
+
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        frames = 3 if res >= 1024 else 8
+        fps, cores, seconds = cpu_frames_per_second(res, frames)
+        cpu_baseline = {"value": fps, "unit": UNIT, "cores": cores, "kind": "port",
+                        "sample": f"{frames} frames of the same {res}^2 generator, batch 1, torch-CPU fp32 restatement "
+                                  f"(oracle/stylegan2_ref.py), {seconds:.1f} s"}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": args.mode, "data": "synthetic",
+            "config": {
+                "workload": f"StyleGAN2 config-f {res}x{res} random-init (perturbed), batch-{batch} frame synthesis from "
+                            "music latents (BASELINE configs[1]): z -> G_mapping -> psi 1.2 -> G_synthesis (fresh noise) -> uint8",
+                "global_batch": batch * world, "frames_per_rank_per_step": batch, "track_frames": int(total_frames),
+                "parallelism": f"frame-range x{world}, weights replicated" + (", NCCL gather of uint8 frames to rank 0 each step" if world > 1 else ""),
+                "l2": "per-step working set (activations of 32 frames, > 10 GB) far exceeds the 126 MB L2; no flush needed",
+                "realtime_multiple_at_60fps": value / 60.0,
+            },
+            "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu_baseline,
+            "clocks": clocks.summary(),
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -43,6 +43,11 @@ _SIGNATURES = {
          c_void_p],
     ),
     "gance_to_uint8_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "gance_pcm_to_float": (c_int, [c_void_p, c_int, c_longlong, c_void_p, c_void_p]),
+    "gance_sinc_resample": (
+        c_int,
+        [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_int, c_double, c_int, c_void_p, c_void_p],
+    ),
     "gance_stft_mag": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "gance_db_resample": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "gance_minmax_savgol_time": (

@@ -244,6 +244,62 @@ __global__ void alpha_blend_wplus_kernel(const double* __restrict__ spec, const 
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// a1: int16/int32/uint8 PCM -> float32 in [-1,1] (music.read_wav_file, music.py:190-205, through
+// remap_values_into_range = scipy interp1d, vector_sources_common.py:44-61):
+// y = slope*(x - x_lo) + y_lo in float64 with slope = (y_hi-y_lo)/(x_hi-x_lo), then float32.
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void pcm_to_float_kernel(const T* __restrict__ pcm, size_t n, double x_lo, double slope, double y_lo,
+                                    float* __restrict__ out) {
+    for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < n; e += (size_t)gridDim.x * blockDim.x)
+        out[e] = (float)__dadd_rn(__dmul_rn(slope, __dsub_rn((double)pcm[e], x_lo)), y_lo);
+}
+
+// ------------------------------------------------------------------------------------------------
+// a2: band-limited sinc resampling, resampy 0.2.2 interpn.resample_f with the kaiser_best filter
+// (music.py:212-230). One thread per OUTPUT sample walks the left wing then the right wing of the
+// interpolation window in the original order, accumulating like the numba loop does:
+// y (float32) <- float32(float64(y) + weight*x) with weight = win[o] + eta*delta[o] in float64, no FMA
+// contraction - so the result is bit-identical to the reference. `times` is the float64 running sum
+// time_register (built on the host by sequential addition, exactly as the loop accumulates it).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) sinc_resample_kernel(const float* __restrict__ x, int n_in,
+                                                            const double* __restrict__ times, int n_out,
+                                                            const double* __restrict__ win,
+                                                            const double* __restrict__ delta, int n_win,
+                                                            double scale, int num_table, int index_step,
+                                                            float* __restrict__ y) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_out) return;
+    const double time_register = times[t];
+    const int n = (int)time_register;
+    double frac = __dmul_rn(scale, __dsub_rn(time_register, (double)n));
+    double index_frac = __dmul_rn(frac, (double)num_table);
+    int offset = (int)index_frac;
+    double eta = __dsub_rn(index_frac, (double)offset);
+    float acc = 0.f;
+    int i_max = (n_win - offset) / index_step;
+    if (n + 1 < i_max) i_max = n + 1;
+    for (int i = 0; i < i_max; ++i) {
+        const int o = offset + i * index_step;
+        const double weight = __dadd_rn(__ldg(win + o), __dmul_rn(eta, __ldg(delta + o)));
+        acc = (float)__dadd_rn((double)acc, __dmul_rn(weight, (double)__ldg(x + n - i)));
+    }
+    frac = __dsub_rn(scale, frac);
+    index_frac = __dmul_rn(frac, (double)num_table);
+    offset = (int)index_frac;
+    eta = __dsub_rn(index_frac, (double)offset);
+    int k_max = (n_win - offset) / index_step;
+    if (n_in - n - 1 < k_max) k_max = n_in - n - 1;
+    for (int k = 0; k < k_max; ++k) {
+        const int o = offset + k * index_step;
+        const double weight = __dadd_rn(__ldg(win + o), __dmul_rn(eta, __ldg(delta + o)));
+        acc = (float)__dadd_rn((double)acc, __dmul_rn(weight, (double)__ldg(x + n + k + 1)));
+    }
+    y[t] = acc;
+}
+
 static int grid1d(size_t items, int block) {
     size_t blocks = (items + block - 1) / block;
     const size_t cap = 148u * 8u;
@@ -255,6 +311,40 @@ static int grid1d(size_t items, int block) {
 using namespace gance;
 
 extern "C" {
+
+int gance_pcm_to_float(const void* pcm, int bits, long long num_samples, float* out, void* stream) {
+    GANCE_REQUIRE(is_initialised(), GANCE_E_NOT_INIT, "gance_init() has not been called");
+    GANCE_REQUIRE(pcm && out, GANCE_E_NULL, "gance_pcm_to_float: NULL pointer");
+    GANCE_REQUIRE(num_samples > 0, GANCE_E_SHAPE, "gance_pcm_to_float: num_samples=%lld", num_samples);
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t n = (size_t)num_samples;
+    const int grid = grid1d(n, 256);
+    // input ranges of music.py:198-203 (the reference maps 8-bit PCM from (0, 255))
+    if (bits == 16) {
+        pcm_to_float_kernel<int16_t><<<grid, 256, 0, s>>>((const int16_t*)pcm, n, -32768.0, 2.0 / 65535.0, -1.0, out);
+    } else if (bits == 32) {
+        pcm_to_float_kernel<int32_t><<<grid, 256, 0, s>>>((const int32_t*)pcm, n, -2147483648.0, 2.0 / 4294967295.0,
+                                                          -1.0, out);
+    } else if (bits == 8) {
+        pcm_to_float_kernel<int8_t><<<grid, 256, 0, s>>>((const int8_t*)pcm, n, 0.0, 2.0 / 255.0, -1.0, out);
+    } else {
+        return fail(GANCE_E_DTYPE, "gance_pcm_to_float: %d-bit PCM is not supported", bits);
+    }
+    return check_launch("pcm_to_float_kernel");
+}
+
+int gance_sinc_resample(const float* x, int n_in, const double* times, int n_out, const double* interp_win,
+                        const double* interp_delta, int n_win, double scale, int num_table, float* y,
+                        void* stream) {
+    GANCE_REQUIRE(is_initialised(), GANCE_E_NOT_INIT, "gance_init() has not been called");
+    GANCE_REQUIRE(x && times && interp_win && interp_delta && y, GANCE_E_NULL, "gance_sinc_resample: NULL pointer");
+    const int index_step = (int)(scale * num_table);
+    GANCE_REQUIRE(n_in > 0 && n_out > 0 && n_win > 0 && num_table > 0 && scale > 0.0 && scale <= 1.0 && index_step > 0,
+                  GANCE_E_SHAPE, "gance_sinc_resample: n_in=%d n_out=%d n_win=%d scale=%g", n_in, n_out, n_win, scale);
+    sinc_resample_kernel<<<(n_out + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
+        x, n_in, times, n_out, interp_win, interp_delta, n_win, scale, num_table, index_step, y);
+    return check_launch("sinc_resample_kernel");
+}
 
 int gance_stft_mag(const float* audio, int num_frames, int vector_length, double* mag, double* global_max,
                    void* stream) {

@@ -23,7 +23,7 @@ import logging
 import typing
 from functools import wraps
 from pathlib import Path
-from typing import Callable, Dict, List, NamedTuple, Optional, Tuple, Union
+from typing import Callable, Dict, Iterable, Iterator, List, NamedTuple, Optional, Tuple, Union
 
 import numpy as np
 import pydantic
@@ -34,7 +34,7 @@ from typing_extensions import Protocol
 from gance_b200.gance_types import RGBInt8ImageType
 from gance_b200.logger_common import LOGGER
 from gance_b200.networks.container import NETWORK_SUFFIX, LoadedNetwork, read_network
-from gance_b200.synthesis import GeneratorOnDevice
+from gance_b200.synthesis import BatchRenderer, GeneratorOnDevice
 from gance_b200.vector_sources.vector_types import SingleMatrix, SingleVector, is_vector
 
 TRUNCATION_PSI = 1.2  # hard-wired in the reference (:124, :155)
@@ -63,8 +63,10 @@ class BatchImageFunction(Protocol):  # pylint: disable=too-few-public-methods
 class NetworkInterface(NamedTuple):
     """
     The only view of a network the rest of GANce uses. The first four fields are the reference's,
-    in the reference's order (:66-78); `create_images_batch` is an addition with a default so that
-    code constructing the tuple from the four original fields keeps working.
+    in the reference's order (:66-78). Two additions, with defaults so that code constructing the
+    tuple from the four original fields keeps working: `create_images_batch` renders many frames per
+    call, `render_batches` streams batches of host latents to host frames with the copies overlapped
+    (gance_b200.synthesis.BatchRenderer; each yielded array is valid until the next one is drawn).
     """
 
     expected_vector_length: int
@@ -72,6 +74,7 @@ class NetworkInterface(NamedTuple):
     create_image_matrix: ImageFunction
     create_image_generic: ImageFunction
     create_images_batch: Optional[BatchImageFunction] = None
+    render_batches: Optional[Callable[[Iterable[np.ndarray]], Iterator[np.ndarray]]] = None
 
 
 def fix_cuda_path() -> None:
@@ -95,9 +98,9 @@ def load_network_network(network_path: Path, call_init_function: bool) -> Loaded
     return read_network(Path(network_path))
 
 
-def wrap_loaded_network(network: LoadedNetwork, mode: str = DEFAULT_MODE) -> NetworkInterface:
+def wrap_loaded_network(network: LoadedNetwork, mode: Optional[str] = None) -> NetworkInterface:
     """Upload the weights and build the interface NT (reference :114-192)."""
-    generator = GeneratorOnDevice(network.spec, network.variables, _device(), mode=mode)
+    generator = GeneratorOnDevice(network.spec, network.variables, _device(), mode=mode or DEFAULT_MODE)
     return _wrap_generator(generator)
 
 
@@ -147,12 +150,22 @@ def _wrap_generator(generator: GeneratorOnDevice, alive: Optional[List[bool]] = 
             return to_host(matrices(array[None]))
         return to_host(matrices(array))
 
+    renderers: Dict[int, BatchRenderer] = {}
+
+    def render_batches(batches: Iterable[np.ndarray], max_batch: int = 32) -> Iterator[np.ndarray]:
+        check_alive()
+        renderer = renderers.get(max_batch)
+        if renderer is None:
+            renderer = renderers[max_batch] = BatchRenderer(generator, max_batch=max_batch, truncation_psi=TRUNCATION_PSI)
+        return renderer.render(batches)
+
     return NetworkInterface(
         expected_vector_length=512,
         create_image_vector=create_image_vector,
         create_image_matrix=create_image_matrix,
         create_image_generic=create_image_generic,
         create_images_batch=create_images_batch,
+        render_batches=render_batches,
     )
 
 
@@ -172,8 +185,9 @@ class NetworkInterfaceInProcess(NamedTuple):
 _RESIDENT: Dict[Tuple[str, str], GeneratorOnDevice] = {}
 
 
-def resident_generator(network_path: Path, mode: str = DEFAULT_MODE) -> GeneratorOnDevice:
+def resident_generator(network_path: Path, mode: Optional[str] = None) -> GeneratorOnDevice:
     """The GPU-resident generator for a network file, loading it on first use."""
+    mode = mode or DEFAULT_MODE
     key = (str(Path(network_path).resolve()), mode)
     generator = _RESIDENT.get(key)
     if generator is None:
@@ -190,7 +204,7 @@ def evict_resident_networks() -> None:
         torch.cuda.empty_cache()
 
 
-def create_network_interface_process(network_path: Path, mode: str = DEFAULT_MODE) -> NetworkInterfaceInProcess:
+def create_network_interface_process(network_path: Path, mode: Optional[str] = None) -> NetworkInterfaceInProcess:
     """
     Reference :232-340 spawns a TF worker and re-raises its start-up exception in the parent
     (:270-278). Here loading happens in-process, so a bad path / bad file / missing GPU raises
@@ -198,7 +212,7 @@ def create_network_interface_process(network_path: Path, mode: str = DEFAULT_MOD
     drops this interface's work buffers. The weights stay resident for fast switching; call
     `evict_resident_networks()` to free them.
     """
-    generator = resident_generator(network_path, mode)
+    generator = resident_generator(network_path, mode or DEFAULT_MODE)
     alive = [True]
 
     def stop_function() -> None:
@@ -296,6 +310,16 @@ class MultiNetwork:
             generic = self._currently_loaded_network.network_interface.create_image_generic
             return np.stack([generic(item) for item in data])
         return batch_function(data)
+
+    @_raise_exception_if_unloaded
+    def indexed_render_batches(self: "MultiNetwork", index: int, batches: Iterable[np.ndarray], max_batch: int = 32):
+        """Addition: stream batches of host latents of ONE network to host frames, copies overlapped."""
+        self._load_network_at_index(index)
+        render = self._currently_loaded_network.network_interface.render_batches
+        if render is None:
+            generic = self._currently_loaded_network.network_interface.create_image_generic
+            return (np.stack([generic(item) for item in batch]) for batch in batches)
+        return render(batches, max_batch)
 
     def load(self: "MultiNetwork") -> None:
         network_path = self._network_paths[self._currently_loaded_network_index]

@@ -18,7 +18,7 @@ Data flow per batch (NHWC activations, `mode` = "bf16" | "fp16" | "fp32"; DESIGN
       ToRGB + skip (+ uint8)        gance_torgb_skip
 """
 
-from typing import Dict, List, Optional, Sequence
+from typing import Dict, Iterable, Iterator, List, Optional, Sequence
 
 import numpy as np
 import torch
@@ -289,3 +289,85 @@ class GeneratorOnDevice:
     def run_matrices(self, wplus: torch.Tensor, **kwargs):
         """Batched `Gs.components.synthesis.run(w+, randomize_noise=False)` (network_functions.py:167-169)."""
         return self.synthesis(wplus, noise_mode="const", **kwargs)
+
+
+class BatchRenderer:
+    """
+    Host latents in, host frames out, with the three legs overlapped: while batch i is computed,
+    batch i-1's frames travel device -> host on a copy stream into pinned memory and batch i+1's
+    latents are staged. This is what replaces the reference's per-frame
+    `input_queue.put` / `output_queue.get` round trip through a TF child process
+    (network_functions.py:289-301), which pickles 3 MB per frame.
+
+    `render(batches)` yields one uint8 [n,R,R,3] array per input batch, in order. Each yielded
+    array is a view of a pinned ring buffer and stays valid until the next batch is drawn from the
+    iterator (copy it to keep it longer).
+    """
+
+    def __init__(self, generator: GeneratorOnDevice, max_batch: int = 32, depth: int = 2,
+                 truncation_psi: float = 1.2, noise_mode: Optional[str] = None) -> None:
+        self.generator = generator
+        self.max_batch = max_batch
+        self.depth = max(2, depth)
+        self.truncation_psi = truncation_psi
+        self.noise_mode = noise_mode
+        dev, res = generator.device, generator.resolution
+        self.copy_stream = torch.cuda.Stream(device=dev)
+        self.frames_dev = [torch.empty((max_batch, res, res, 3), dtype=torch.uint8, device=dev) for _ in range(self.depth)]
+        self.frames_host = [torch.empty((max_batch, res, res, 3), dtype=torch.uint8).pin_memory() for _ in range(self.depth)]
+        self.latents_host = [torch.empty((max_batch * generator.num_ws * 512,), dtype=torch.float32).pin_memory()
+                             for _ in range(self.depth)]
+        self.done = [torch.cuda.Event() for _ in range(self.depth)]
+        self.bytes_h2d = 0
+        self.bytes_d2h = 0
+
+    def _submit(self, slot: int, latents: np.ndarray) -> int:
+        gen = self.generator
+        array = np.asarray(latents, dtype=np.float32)
+        is_vectors = array.ndim == 2 and array.shape[-1] == 512 and array.shape[0] != gen.num_ws or array.ndim == 1
+        if array.ndim == 1:
+            array = array[None]
+        if not is_vectors and array.ndim == 2:
+            array = array[None]
+        n = array.shape[0]
+        if n > self.max_batch:
+            raise ValueError(f"batch of {n} exceeds max_batch {self.max_batch}")
+        if not is_vectors:
+            if array.shape[1] < gen.num_ws:
+                raise ValueError(f"latents have {array.shape[1]} rows, this network needs {gen.num_ws}")
+            array = array[:, : gen.num_ws]
+        stream = torch.cuda.current_stream(gen.device)
+        stream.wait_event(self.done[slot])  # the frames of the batch that last used this slot have left the device
+        staged = self.latents_host[slot][: array.size].view(array.shape)
+        staged.copy_(torch.from_numpy(np.ascontiguousarray(array)))
+        on_device = staged.to(gen.device, non_blocking=True)
+        self.bytes_h2d += array.size * 4
+        out = self.frames_dev[slot][:n]
+        if is_vectors:
+            gen.run_vectors(on_device, truncation_psi=self.truncation_psi, noise_mode=self.noise_mode or "random", out=out)
+        else:
+            gen.synthesis(on_device, noise_mode=self.noise_mode or "const", out=out)
+        computed = torch.cuda.Event()
+        computed.record(stream)
+        self.copy_stream.wait_event(computed)
+        with torch.cuda.stream(self.copy_stream):
+            self.frames_host[slot][:n].copy_(out, non_blocking=True)
+            self.done[slot].record(self.copy_stream)
+        self.bytes_d2h += n * out[0].numel()
+        return n
+
+    def render(self, batches: Iterable[np.ndarray]) -> Iterator[np.ndarray]:
+        pending: List[tuple] = []
+        index = 0
+        for latents in batches:
+            slot = index % self.depth
+            n = self._submit(slot, latents)
+            pending.append((slot, n))
+            index += 1
+            if len(pending) == self.depth:  # keep depth-1 batches in flight
+                ready_slot, ready_n = pending.pop(0)
+                self.done[ready_slot].synchronize()
+                yield self.frames_host[ready_slot][:ready_n].numpy()
+        for ready_slot, ready_n in pending:
+            self.done[ready_slot].synchronize()
+            yield self.frames_host[ready_slot][:ready_n].numpy()

@@ -134,6 +134,20 @@ int gance_torgb_skip(const void* x, int dtype, int batch, int h, int w, int chan
 /* Stand-alone convert_images_to_uint8 on a [B,H,W,4] f32 skip tensor -> [B,H,W,3] u8. */
 int gance_to_uint8_nhwc(const float* y, int batch, int h, int w, uint8_t* frames, void* stream);
 
+/* ---- audio: WAV samples -> float32 -> resampled so that one frame = vector_length samples --------
+ * gance_pcm_to_float: music.read_wav_file (gance/vector_sources/music.py:190-205) +
+ * remap_values_into_range (vector_sources_common.py:44-61): PCM of `bits` (16, 32, 8) mapped from
+ * its integer range onto [-1,1] in float64, stored float32. Bit-exact with the reference.
+ * gance_sinc_resample: resampy 0.2.2 resample(filter='kaiser_best') as called by
+ * _scale_wav_to_sample_rate (music.py:212-230). interp_win / interp_delta are the float64 half
+ * window (already multiplied by the ratio when down-sampling) and its first difference, n_win
+ * long; scale = min(1, ratio); times[t] is the float64 running sum of 1/ratio (host-built by
+ * sequential addition). y [n_out] f32. Same operation order and rounding as the numba loop. */
+int gance_pcm_to_float(const void* pcm, int bits, long long num_samples, float* out, void* stream);
+int gance_sinc_resample(const float* x, int n_in, const double* times, int n_out,
+                        const double* interp_win, const double* interp_delta, int n_win,
+                        double scale, int num_table, float* y, void* stream);
+
 /* ---- audio: windowed real DFT -> magnitude ------------------------------------------------------
  * apply_spectrogram.compute_spectrogram (apply_spectrogram.py:49-82) up to |X|: frames of
  * window = vector_length-2 samples at hop vector_length, periodic Hann np.hanning(window+1)[:-1],

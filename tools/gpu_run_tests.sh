@@ -10,6 +10,7 @@ run() { # name, pytest args...
   tail -n 3 gpurun_out/$name.log | tee -a gpurun_out/summary.txt
 }
 : > gpurun_out/summary.txt
+run audio tests/test_gpu_audio.py
 run kernels_small tests/test_gpu_kernels.py -k "not modconv3x3 and not up_convolution"
 run conv_fp32 tests/test_gpu_kernels.py -k "fp32 and (modconv3x3 or up_convolution)"
 run conv_tc tests/test_gpu_kernels.py -k "tcgen05 or ((bf16 or fp16) and up_convolution)"
