@@ -25,7 +25,13 @@ _SIGNATURES = {
         c_int,
         [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p],
     ),
+    "gance_styles_all": (
+        c_int,
+        [c_void_p, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int,
+         c_void_p, c_void_p],
+    ),
     "gance_const_input": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "gance_scale_channels": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "gance_modconv3x3": (
         c_int,
         [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_longlong,
@@ -36,6 +42,11 @@ _SIGNATURES = {
         c_int,
         [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_longlong,
          c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+    ),
+    "gance_modconv3x3_up2_folded": (
+        c_int,
+        [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_longlong, c_float,
+         c_void_p, c_void_p, c_void_p, c_void_p],
     ),
     "gance_torgb_skip": (
         c_int,

@@ -43,7 +43,9 @@ struct ConvParams {
     float noise_strength;
     const float* bias;
     const float* next_styles;
-    void* out;  // [B,h_out,w_out,c_out] bf16 or half
+    void* out;  // [B,h_out,w_out,c_out] bf16 or half; up: [B,2*h_out,2*w_out,c_real]
+    int up;      // 1: folded up-convolution, GEMM column n = phase*c_real + co, phase = py*2+px -> pixel (2h+py, 2w+px)
+    int c_real;  // channels of `out` (= c_out when !up, c_out/4 when up); demod/bias/next_styles are indexed by co
 };
 
 // ---- PTX wrappers --------------------------------------------------------------------------------
@@ -310,15 +312,9 @@ modconv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             const TileCoord t = decode_tile(p, tile, N_TILE);
             const int b = t.b0 + bl, h = t.h0 + hl, w = t.w0 + wl;
             const bool valid = b < p.batch && h < p.h_out && w < p.w_out;
-            float nz = 0.f;
-            if (valid && p.noise != nullptr)
-                nz = __ldg(p.noise + (size_t)b * p.noise_batch_stride + (size_t)h * p.w_out + w) * p.noise_strength;
-            const size_t bc = (size_t)(valid ? b : 0) * p.c_out + t.n0;
-            const float4* demod4 = reinterpret_cast<const float4*>(p.demod + bc);
-            const float4* bias4 = reinterpret_cast<const float4*>(p.bias + t.n0);
-            const float4* style4 = p.next_styles ? reinterpret_cast<const float4*>(p.next_styles + bc) : nullptr;
-            T* dst = reinterpret_cast<T*>(p.out) + (((size_t)(valid ? b : 0) * p.h_out + (valid ? h : 0)) * p.w_out +
-                                                    (valid ? w : 0)) * p.c_out + t.n0;
+            const int bv = valid ? b : 0, hv = valid ? h : 0, wv = valid ? w : 0;
+            const int out_h = p.up ? 2 * p.h_out : p.h_out, out_w = p.up ? 2 * p.w_out : p.w_out;
+            const float* noise_b = p.noise ? p.noise + (size_t)bv * p.noise_batch_stride : nullptr;
 
             mbar_wait(tmem_full_bar + acc, acc_phase);
             tcgen05_fence_after();
@@ -327,6 +323,17 @@ modconv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             for (int c0 = 0; c0 < N_TILE; c0 += 32) {
                 uint32_t r[32];
                 tmem_ld_32x32(taddr + (uint32_t)c0, r);
+                // column chunk -> (phase, first channel): a 32-column chunk never straddles a phase (c_real % 32 == 0)
+                const int n = t.n0 + c0;
+                const int phase = p.up ? n / p.c_real : 0;
+                const int co0 = n - phase * p.c_real;
+                const int oh = p.up ? 2 * hv + (phase >> 1) : hv, ow = p.up ? 2 * wv + (phase & 1) : wv;
+                const float nz = noise_b ? __ldg(noise_b + (size_t)oh * out_w + ow) * p.noise_strength : 0.f;
+                const size_t bc = (size_t)bv * p.c_real + co0;
+                const float4* demod4 = reinterpret_cast<const float4*>(p.demod + bc);
+                const float4* bias4 = reinterpret_cast<const float4*>(p.bias + co0);
+                const float4* style4 = p.next_styles ? reinterpret_cast<const float4*>(p.next_styles + bc) : nullptr;
+                T* dst = reinterpret_cast<T*>(p.out) + (((size_t)bv * out_h + oh) * out_w + ow) * p.c_real + co0;
                 tmem_ld_wait();
                 if (valid) {
 #pragma unroll
@@ -334,7 +341,7 @@ modconv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                         float v[8];
 #pragma unroll
                         for (int q = 0; q < 2; ++q) {
-                            const int idx = (c0 >> 2) + g * 2 + q;
+                            const int idx = g * 2 + q;
                             const float4 d = __ldg(demod4 + idx);
                             const float4 bs = __ldg(bias4 + idx);
                             float o0 = bias_lrelu(fmaf(__uint_as_float(r[g * 8 + q * 4 + 0]), d.x, nz + bs.x));
@@ -349,7 +356,7 @@ modconv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                         }
                         Vec<T> packed;
                         packed.from_float(v);
-                        packed.store(dst + c0 + g * 8);
+                        packed.store(dst + g * 8);
                     }
                 }
             }
@@ -473,38 +480,28 @@ int launch_modconv3x3_f32(const float* x, int batch, int h_out, int w_out, int c
 
 using namespace gance;
 
-extern "C" int gance_modconv3x3(const void* x, int dtype, int batch, int h_out, int w_out, int c_in, int c_out,
-                                int pad, const void* weight, const float* demod, const float* noise,
-                                long long noise_batch_stride, float noise_strength, const float* bias,
-                                const float* next_styles, void* out, void* stream) {
-    GANCE_REQUIRE(is_initialised(), GANCE_E_NOT_INIT, "gance_init() has not been called");
-    GANCE_REQUIRE(x && weight && demod && bias && out, GANCE_E_NULL, "gance_modconv3x3: NULL pointer");
-    GANCE_REQUIRE(batch > 0 && h_out > 0 && w_out > 0 && c_in > 0 && c_out > 0 && (pad == 0 || pad == 1),
-                  GANCE_E_SHAPE, "gance_modconv3x3: shape B=%d H=%d W=%d Cin=%d Cout=%d pad=%d", batch, h_out, w_out,
-                  c_in, c_out, pad);
-    cudaStream_t s = (cudaStream_t)stream;
-    if (dtype == GANCE_F32)
-        return launch_modconv3x3_f32((const float*)x, batch, h_out, w_out, c_in, c_out, pad, (const float*)weight,
-                                     demod, noise, noise_batch_stride, noise_strength, bias, next_styles,
-                                     (float*)out, s);
-    GANCE_REQUIRE(dtype == GANCE_BF16 || dtype == GANCE_F16, GANCE_E_DTYPE, "gance_modconv3x3: dtype %d", dtype);
+// Shared launcher of the tcgen05 path. `c_out` is the GEMM N (4 * c_real for a folded up-convolution).
+static int launch_tensor_core_conv(const char* who, const void* x, int dtype, int batch, int h_out, int w_out, int c_in,
+                                   int c_out, int pad, int up, int c_real, const void* weight, const float* demod,
+                                   const float* noise, long long noise_batch_stride, float noise_strength,
+                                   const float* bias, const float* next_styles, void* out, cudaStream_t s) {
+    GANCE_REQUIRE(dtype == GANCE_BF16 || dtype == GANCE_F16, GANCE_E_DTYPE, "%s: dtype %d", who, dtype);
     const bool half_operands = dtype == GANCE_F16;
-    GANCE_REQUIRE(c_in % 32 == 0 && c_out % 32 == 0, GANCE_E_SHAPE,
-                  "gance_modconv3x3: the tcgen05 path needs Cin %% 32 == 0 and Cout %% 32 == 0 (got %d, %d)", c_in,
-                  c_out);
+    GANCE_REQUIRE(c_in % 32 == 0 && c_real % 32 == 0, GANCE_E_SHAPE,
+                  "%s: the tcgen05 path needs Cin %% 32 == 0 and Cout %% 32 == 0 (got %d, %d)", who, c_in, c_real);
     GANCE_REQUIRE(aligned16(x) && aligned16(weight) && aligned16(out) && aligned16(demod) && aligned16(bias) &&
                       aligned16(next_styles),
-                  GANCE_E_ALIGN, "gance_modconv3x3: pointers must be 16-byte aligned");
+                  GANCE_E_ALIGN, "%s: pointers must be 16-byte aligned", who);
 
     tc::ConvParams p;
     p.batch = batch; p.h_out = h_out; p.w_out = w_out; p.c_in = c_in; p.c_out = c_out; p.pad = pad;
+    p.up = up; p.c_real = c_real;
     // 128 output pixels per tile: as wide as the image allows (<= 16), then rows, then samples.
     p.tile_w = w_out >= 16 ? 16 : w_out;
-    GANCE_REQUIRE((p.tile_w & (p.tile_w - 1)) == 0, GANCE_E_SHAPE, "gance_modconv3x3: W=%d (< 16) must be a power of two",
-                  w_out);
+    GANCE_REQUIRE((p.tile_w & (p.tile_w - 1)) == 0, GANCE_E_SHAPE, "%s: W=%d (< 16) must be a power of two", who, w_out);
     int rows = tc::kTileM / p.tile_w;
     p.tile_h = h_out >= rows ? rows : h_out;
-    GANCE_REQUIRE(rows % p.tile_h == 0, GANCE_E_SHAPE, "gance_modconv3x3: H=%d does not tile 128 pixels", h_out);
+    GANCE_REQUIRE(rows % p.tile_h == 0, GANCE_E_SHAPE, "%s: H=%d does not tile 128 pixels", who, h_out);
     p.tile_b = rows / p.tile_h;
     p.tiles_w = (w_out + p.tile_w - 1) / p.tile_w;
     p.tiles_h = (h_out + p.tile_h - 1) / p.tile_h;
@@ -515,7 +512,6 @@ extern "C" int gance_modconv3x3(const void* x, int dtype, int batch, int h_out, 
     const int m_tiles = p.tiles_w * p.tiles_h * p.tiles_b;
 
     if (c_in % 64 != 0) {  // Cin = 32 (1024^2 Conv1 in config-f): 64-byte rows, SWIZZLE_64B
-        GANCE_REQUIRE(c_out % 32 == 0, GANCE_E_SHAPE, "Cout %d", c_out);
         p.n_tiles = c_out / 32; p.k_chunks = c_in / 32;
         return tc::launch<32, 32, 8>(half_operands, p, x, weight, h_in, w_in, s);
     }
@@ -534,6 +530,37 @@ extern "C" int gance_modconv3x3(const void* x, int dtype, int batch, int h_out, 
     }
     p.n_tiles = c_out / 32;
     return tc::launch<32, 64, 8>(half_operands, p, x, weight, h_in, w_in, s);
+}
+
+extern "C" int gance_modconv3x3(const void* x, int dtype, int batch, int h_out, int w_out, int c_in, int c_out,
+                                int pad, const void* weight, const float* demod, const float* noise,
+                                long long noise_batch_stride, float noise_strength, const float* bias,
+                                const float* next_styles, void* out, void* stream) {
+    GANCE_REQUIRE(is_initialised(), GANCE_E_NOT_INIT, "gance_init() has not been called");
+    GANCE_REQUIRE(x && weight && demod && bias && out, GANCE_E_NULL, "gance_modconv3x3: NULL pointer");
+    GANCE_REQUIRE(batch > 0 && h_out > 0 && w_out > 0 && c_in > 0 && c_out > 0 && (pad == 0 || pad == 1),
+                  GANCE_E_SHAPE, "gance_modconv3x3: shape B=%d H=%d W=%d Cin=%d Cout=%d pad=%d", batch, h_out, w_out,
+                  c_in, c_out, pad);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (dtype == GANCE_F32)
+        return launch_modconv3x3_f32((const float*)x, batch, h_out, w_out, c_in, c_out, pad, (const float*)weight,
+                                     demod, noise, noise_batch_stride, noise_strength, bias, next_styles,
+                                     (float*)out, s);
+    return launch_tensor_core_conv("gance_modconv3x3", x, dtype, batch, h_out, w_out, c_in, c_out, pad, /*up=*/0, c_out,
+                                   weight, demod, noise, noise_batch_stride, noise_strength, bias, next_styles, out, s);
+}
+
+extern "C" int gance_modconv3x3_up2_folded(const void* x, int dtype, int batch, int h_in, int w_in, int c_in, int c_out,
+                                           const void* weight_folded, const float* demod, const float* noise,
+                                           long long noise_batch_stride, float noise_strength, const float* bias,
+                                           const float* next_styles, void* out, void* stream) {
+    GANCE_REQUIRE(is_initialised(), GANCE_E_NOT_INIT, "gance_init() has not been called");
+    GANCE_REQUIRE(x && weight_folded && demod && bias && out, GANCE_E_NULL, "gance_modconv3x3_up2_folded: NULL pointer");
+    GANCE_REQUIRE(batch > 0 && h_in > 0 && w_in > 0 && c_in > 0 && c_out > 0, GANCE_E_SHAPE,
+                  "gance_modconv3x3_up2_folded: shape B=%d H=%d W=%d Cin=%d Cout=%d", batch, h_in, w_in, c_in, c_out);
+    return launch_tensor_core_conv("gance_modconv3x3_up2_folded", x, dtype, batch, h_in, w_in, c_in, 4 * c_out, /*pad=*/1,
+                                   /*up=*/1, c_out, weight_folded, demod, noise, noise_batch_stride, noise_strength,
+                                   bias, next_styles, out, (cudaStream_t)stream);
 }
 
 extern "C" int gance_modconv3x3_up2_fir(const void* x, int dtype, int batch, int h_in, int w_in, int c_in,

@@ -96,6 +96,101 @@ __global__ void __launch_bounds__(256) style_demod_kernel(const float* __restric
 }
 
 // ------------------------------------------------------------------------------------------------
+// Styles and demodulation coefficients of EVERY layer of a generator in two launches.
+// The per-layer affine weights are concatenated column-wise into mod_weight_cat [512, total_cols];
+// a chunk = 32 consecutive columns of one layer. CTA = 32 columns x 4 slices of the 512-long (or
+// Cin-long) reduction, for 8 samples at a time (the w vectors / squared styles sit in shared memory).
+// Outputs are layer-major so each layer's [B, C] block is contiguous: block of layer L starts at
+// B * col0(L).
+// ------------------------------------------------------------------------------------------------
+constexpr int kStyleSamples = 8;
+
+__global__ void __launch_bounds__(128) styles_all_kernel(const float* __restrict__ wplus, int batch, int num_ws,
+                                                         const float* __restrict__ mod_weight_cat, int total_cols,
+                                                         const float* __restrict__ mod_bias_cat,
+                                                         const int4* __restrict__ chunks,
+                                                         float* __restrict__ styles_out) {
+    __shared__ float w[kStyleSamples][kLatent];
+    __shared__ float part[4][kStyleSamples][32];
+    const int4 chunk = chunks[blockIdx.x];  // x: w_index, y: first column of the layer, z: Cin, w: first column of the chunk inside the layer
+    const int b0 = blockIdx.y * kStyleSamples;
+    for (int i = threadIdx.x; i < kStyleSamples * kLatent; i += blockDim.x) {
+        const int sidx = i / kLatent, k = i % kLatent;
+        w[sidx][k] = b0 + sidx < batch ? wplus[((size_t)(b0 + sidx) * num_ws + chunk.x) * kLatent + k] : 0.f;
+    }
+    __syncthreads();
+    const int col = threadIdx.x & 31, slice = threadIdx.x >> 5;
+    const int gcol = chunk.y + chunk.w + col;
+    float acc[kStyleSamples];
+#pragma unroll
+    for (int i = 0; i < kStyleSamples; ++i) acc[i] = 0.f;
+    const float* m = mod_weight_cat + (size_t)(slice * (kLatent / 4)) * total_cols + gcol;
+#pragma unroll 4
+    for (int k = 0; k < kLatent / 4; ++k) {
+        const float mv = __ldg(m + (size_t)k * total_cols);
+#pragma unroll
+        for (int i = 0; i < kStyleSamples; ++i) acc[i] = fmaf(w[i][slice * (kLatent / 4) + k], mv, acc[i]);
+    }
+#pragma unroll
+    for (int i = 0; i < kStyleSamples; ++i) part[slice][i][col] = acc[i];
+    __syncthreads();
+    for (int i = threadIdx.x; i < kStyleSamples * 32; i += blockDim.x) {
+        const int sidx = i >> 5, c = i & 31;
+        if (b0 + sidx >= batch) continue;
+        const float v = (part[0][sidx][c] + part[1][sidx][c]) + (part[2][sidx][c] + part[3][sidx][c]);
+        styles_out[(size_t)batch * chunk.y + (size_t)(b0 + sidx) * chunk.z + chunk.w + c] =
+            v + mod_bias_cat[chunk.y + chunk.w + c] + 1.0f;
+    }
+}
+
+struct DemodChunk {
+    int wsq_offset;   // float offset of this layer's [Cin, Cout] sum-of-squared-weights matrix in wsq_cat
+    int c_in, c_out;
+    int style_col0;   // first column of the layer in the concatenated style space
+    int co0;          // first output channel of this chunk
+    int demod_col0;   // first column of the layer in the concatenated demod space
+};
+
+__global__ void __launch_bounds__(128) demod_all_kernel(const float* __restrict__ styles_all, int batch,
+                                                        const float* __restrict__ wsq_cat,
+                                                        const DemodChunk* __restrict__ chunks,
+                                                        float* __restrict__ demod_out) {
+    __shared__ float s2[kStyleSamples][kLatent];
+    __shared__ float part[4][kStyleSamples][32];
+    const DemodChunk chunk = chunks[blockIdx.x];
+    const int b0 = blockIdx.y * kStyleSamples;
+    for (int i = threadIdx.x; i < kStyleSamples * chunk.c_in; i += blockDim.x) {
+        const int sidx = i / chunk.c_in, ci = i % chunk.c_in;
+        float v = 0.f;
+        if (b0 + sidx < batch) v = styles_all[(size_t)batch * chunk.style_col0 + (size_t)(b0 + sidx) * chunk.c_in + ci];
+        s2[sidx][ci] = v * v;
+    }
+    __syncthreads();
+    const int col = threadIdx.x & 31, slice = threadIdx.x >> 5;
+    const int per_slice = chunk.c_in / 4;  // Cin is a multiple of 32
+    float acc[kStyleSamples];
+#pragma unroll
+    for (int i = 0; i < kStyleSamples; ++i) acc[i] = 0.f;
+    const float* m = wsq_cat + chunk.wsq_offset + (size_t)(slice * per_slice) * chunk.c_out + chunk.co0 + col;
+#pragma unroll 4
+    for (int k = 0; k < per_slice; ++k) {
+        const float mv = __ldg(m + (size_t)k * chunk.c_out);
+#pragma unroll
+        for (int i = 0; i < kStyleSamples; ++i) acc[i] = fmaf(s2[i][slice * per_slice + k], mv, acc[i]);
+    }
+#pragma unroll
+    for (int i = 0; i < kStyleSamples; ++i) part[slice][i][col] = acc[i];
+    __syncthreads();
+    for (int i = threadIdx.x; i < kStyleSamples * 32; i += blockDim.x) {
+        const int sidx = i >> 5, c = i & 31;
+        if (b0 + sidx >= batch) continue;
+        const float v = (part[0][sidx][c] + part[1][sidx][c]) + (part[2][sidx][c] + part[3][sidx][c]);
+        demod_out[(size_t)batch * chunk.demod_col0 + (size_t)(b0 + sidx) * chunk.c_out + chunk.co0 + c] =
+            rsqrtf(v + 1e-8f);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // const * style
 // ------------------------------------------------------------------------------------------------
 template <typename T>
@@ -186,6 +281,32 @@ __global__ void __launch_bounds__(256) upfir2x_pad_kernel(const T* __restrict__ 
 // reads 32 consecutive 16-byte vectors: fully coalesced. wmod[c][j] = styles[b,c]*weight[c,j]
 // sits in shared memory (one sample per CTA row of the grid).
 // ------------------------------------------------------------------------------------------------
+// ------------------------------------------------------------------------------------------------
+// x[b,h,w,c] * styles[b,c] -> out (the pre-scaling of a modulated convolution's input when the
+// producing kernel could not apply it in its epilogue). 16-byte vectors, grid-stride.
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) scale_channels_kernel(const T* __restrict__ x, size_t pixels_per_sample,
+                                                             int channels, size_t total_vecs,
+                                                             const float* __restrict__ styles, T* __restrict__ out) {
+    constexpr int V = Vec<T>::N;
+    const int vec_per_pixel = channels / V;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total_vecs;
+         i += (size_t)gridDim.x * blockDim.x) {
+        const int cv = (int)(i % vec_per_pixel);
+        const size_t b = i / ((size_t)vec_per_pixel * pixels_per_sample);
+        Vec<T> v;
+        v.load(x + i * V);
+        float f[V];
+        v.to_float(f);
+        const float* s = styles + b * channels + cv * V;
+#pragma unroll
+        for (int k = 0; k < V; ++k) f[k] *= __ldg(s + k);
+        v.from_float(f);
+        v.store(out + i * V);
+    }
+}
+
 __device__ __forceinline__ float4 upsample_tap(const float* __restrict__ y_prev, int b, int hp, int wp,
                                                int h, int w) {
     // upsample_2d(k=[1,3,3,1]): y[2a] = .25 p[a-1] + .75 p[a]; y[2a+1] = .75 p[a] + .25 p[a+1]
@@ -456,6 +577,29 @@ int gance_style_demod(const float* wplus, int batch, int num_ws, int w_index, co
     return check_launch("style_demod_kernel");
 }
 
+int gance_styles_all(const float* wplus, int batch, int num_ws, const float* mod_weight_cat, int total_cols,
+                     const float* mod_bias_cat, const int* style_chunks, int n_style_chunks, float* styles_out,
+                     const float* wsq_cat, const int* demod_chunks, int n_demod_chunks, float* demod_out,
+                     void* stream) {
+    GANCE_REQUIRE(is_initialised(), GANCE_E_NOT_INIT, "gance_init() has not been called");
+    GANCE_REQUIRE(wplus && mod_weight_cat && mod_bias_cat && style_chunks && styles_out, GANCE_E_NULL,
+                  "gance_styles_all: NULL pointer");
+    GANCE_REQUIRE(batch > 0 && num_ws > 0 && total_cols > 0 && n_style_chunks > 0 && n_demod_chunks >= 0, GANCE_E_SHAPE,
+                  "gance_styles_all: batch=%d num_ws=%d total_cols=%d chunks=%d/%d", batch, num_ws, total_cols,
+                  n_style_chunks, n_demod_chunks);
+    GANCE_REQUIRE(aligned16(style_chunks), GANCE_E_ALIGN, "gance_styles_all: style_chunks must be 16-byte aligned");
+    cudaStream_t s = (cudaStream_t)stream;
+    const int sample_groups = (batch + kStyleSamples - 1) / kStyleSamples;
+    styles_all_kernel<<<dim3(n_style_chunks, sample_groups), 128, 0, s>>>(
+        wplus, batch, num_ws, mod_weight_cat, total_cols, mod_bias_cat, (const int4*)style_chunks, styles_out);
+    int rc = check_launch("styles_all_kernel");
+    if (rc != GANCE_OK || n_demod_chunks == 0) return rc;
+    GANCE_REQUIRE(wsq_cat && demod_chunks && demod_out, GANCE_E_NULL, "gance_styles_all: NULL demod pointer");
+    demod_all_kernel<<<dim3(n_demod_chunks, sample_groups), 128, 0, s>>>(styles_out, batch, wsq_cat,
+                                                                        (const DemodChunk*)demod_chunks, demod_out);
+    return check_launch("demod_all_kernel");
+}
+
 int gance_const_input(const float* konst, const float* styles, int batch, int channels, int dtype, void* out,
                       void* stream) {
     GANCE_REQUIRE(is_initialised(), GANCE_E_NOT_INIT, "gance_init() has not been called");
@@ -477,6 +621,33 @@ int gance_const_input(const float* konst, const float* styles, int batch, int ch
         return fail(GANCE_E_DTYPE, "gance_const_input: dtype %d", dtype);
     }
     return check_launch("const_input_kernel");
+}
+
+int gance_scale_channels(const void* x, int dtype, int batch, int h, int w, int channels, const float* styles,
+                         void* out, void* stream) {
+    GANCE_REQUIRE(is_initialised(), GANCE_E_NOT_INIT, "gance_init() has not been called");
+    GANCE_REQUIRE(x && styles && out, GANCE_E_NULL, "gance_scale_channels: NULL pointer");
+    GANCE_REQUIRE(batch > 0 && h > 0 && w > 0 && channels > 0 && channels % 8 == 0, GANCE_E_SHAPE,
+                  "gance_scale_channels: shape [%d,%d,%d,%d]", batch, h, w, channels);
+    GANCE_REQUIRE(aligned16(x) && aligned16(out), GANCE_E_ALIGN, "gance_scale_channels: pointers must be 16-byte aligned");
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t pixels = (size_t)h * w;
+    if (dtype == GANCE_F32) {
+        const size_t vecs = (size_t)batch * pixels * channels / 4;
+        scale_channels_kernel<float><<<grid_for(vecs, 256), 256, 0, s>>>((const float*)x, pixels, channels, vecs, styles,
+                                                                          (float*)out);
+    } else if (dtype == GANCE_BF16) {
+        const size_t vecs = (size_t)batch * pixels * channels / 8;
+        scale_channels_kernel<__nv_bfloat16><<<grid_for(vecs, 256), 256, 0, s>>>((const __nv_bfloat16*)x, pixels, channels,
+                                                                                  vecs, styles, (__nv_bfloat16*)out);
+    } else if (dtype == GANCE_F16) {
+        const size_t vecs = (size_t)batch * pixels * channels / 8;
+        scale_channels_kernel<__half><<<grid_for(vecs, 256), 256, 0, s>>>((const __half*)x, pixels, channels, vecs, styles,
+                                                                           (__half*)out);
+    } else {
+        return fail(GANCE_E_DTYPE, "gance_scale_channels: dtype %d", dtype);
+    }
+    return check_launch("scale_channels_kernel");
 }
 
 int gance_upfir2x_pad(const void* x, int dtype, int batch, int h, int w, int channels, const float* styles,

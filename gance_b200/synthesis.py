@@ -39,6 +39,21 @@ MODES = {
 NOISE_MODES = ("const", "random", "provided", "none")
 
 
+def fold_up_weight(hwio: torch.Tensor) -> torch.Tensor:
+    """
+    [3,3,Cin,Cout] (runtime-scaled HWIO) -> [4*Cout,3,3,Cin]: the four phase weights of the folded
+    up-convolution (include/gance_b200.h, gance_modconv3x3_up2_folded), row n = (py*2+px)*Cout + co.
+    Folded in float64, rounded to the operand type once.
+    """
+    w = hwio.double()
+    taps = (
+        torch.tensor([[0.75, 0.25, 0.0], [0.25, 0.75, 0.75], [0.0, 0.0, 0.25]], dtype=torch.float64, device=w.device),
+        torch.tensor([[0.25, 0.0, 0.0], [0.75, 0.75, 0.25], [0.0, 0.25, 0.75]], dtype=torch.float64, device=w.device),
+    )
+    phases = [torch.einsum("yk,xl,klio->oyxi", taps[py], taps[px], w) for py in range(2) for px in range(2)]
+    return torch.cat(phases, dim=0).contiguous().float()
+
+
 def _ptr(tensor: Optional[torch.Tensor]) -> Optional[int]:
     return None if tensor is None else tensor.data_ptr()
 
@@ -91,6 +106,8 @@ class GeneratorOnDevice:
             self.conv_wsq.append((hwio * hwio).sum(dim=(0, 1)).contiguous())  # [Cin,Cout]
             if self.mode == "fp32":
                 self.conv_w.append(hwio.contiguous())  # [3,3,Cin,Cout]
+            elif conv.up:
+                self.conv_w.append(fold_up_weight(hwio).to(self.torch_dtype))  # [4*Cout,3,3,Cin]
             else:
                 self.conv_w.append(hwio.permute(3, 0, 1, 2).contiguous().to(self.torch_dtype))  # [Cout,3,3,Cin]
             self.conv_mod_w.append(f32(v[f"{conv.name}/mod_weight"] * (1.0 / np.sqrt(512.0))))
@@ -108,6 +125,34 @@ class GeneratorOnDevice:
             self.rgb_mod_w.append(f32(v[f"{rgb.name}/mod_weight"] * (1.0 / np.sqrt(512.0))))
             self.rgb_mod_b.append(f32(v[f"{rgb.name}/mod_bias"]))
             self.rgb_bias.append(f32(v[f"{rgb.name}/bias"]))
+
+        self._build_style_tables()
+
+    def _build_style_tables(self) -> None:
+        """Concatenated affine weights + chunk descriptors for gance_styles_all (include/gance_b200.h)."""
+        dev = self.device
+        layers = [(c.w_index, c.in_channels, self.conv_mod_w[i], self.conv_mod_b[i]) for i, c in enumerate(self.convs)]
+        layers += [(r.w_index, r.in_channels, self.rgb_mod_w[i], self.rgb_mod_b[i]) for i, r in enumerate(self.rgbs)]
+        self.style_col0: List[int] = []
+        style_chunks, col = [], 0
+        for w_index, channels, _, _ in layers:
+            self.style_col0.append(col)
+            style_chunks += [[w_index, col, channels, first] for first in range(0, channels, 32)]
+            col += channels
+        self.style_cols = col
+        self.mod_w_cat = torch.cat([w for _, _, w, _ in layers], dim=1).contiguous()  # [512, total]
+        self.mod_b_cat = torch.cat([b for _, _, _, b in layers]).contiguous()
+        self.style_chunks = torch.tensor(style_chunks, dtype=torch.int32).to(dev)
+        demod_chunks, self.demod_col0, dcol, offset = [], [], 0, 0
+        for i, conv in enumerate(self.convs):
+            self.demod_col0.append(dcol)
+            demod_chunks += [[offset, conv.in_channels, conv.out_channels, self.style_col0[i], first, dcol]
+                             for first in range(0, conv.out_channels, 32)]
+            dcol += conv.out_channels
+            offset += conv.in_channels * conv.out_channels
+        self.demod_cols = dcol
+        self.wsq_cat = torch.cat([w.reshape(-1) for w in self.conv_wsq]).contiguous()
+        self.demod_chunks = torch.tensor(demod_chunks, dtype=torch.int32).to(dev)
 
     def weight_bytes(self) -> int:
         tensors = [self.map_w, self.map_b, self.dlatent_avg, self.const]
@@ -178,29 +223,23 @@ class GeneratorOnDevice:
             raise ValueError("out must be a contiguous uint8 [B,R,R,3] tensor")
 
         # -- styles and demodulation coefficients of every layer
-        styles, demods = [], []
-        for i, conv in enumerate(self.convs):
-            s = self._buffer(f"style{i}", (batch, conv.in_channels), torch.float32)
-            d = self._buffer(f"demod{i}", (batch, conv.out_channels), torch.float32)
-            _lib.check(
-                lib.gance_style_demod(wplus.data_ptr(), batch, self.num_ws, conv.w_index,
-                                      self.conv_mod_w[i].data_ptr(), self.conv_mod_b[i].data_ptr(),
-                                      self.conv_wsq[i].data_ptr(), conv.in_channels, conv.out_channels,
-                                      s.data_ptr(), d.data_ptr(), stream),
-                "gance_style_demod",
-            )
-            styles.append(s)
-            demods.append(d)
-        rgb_styles = []
-        for i, rgb in enumerate(self.rgbs):
-            s = self._buffer(f"rgbstyle{i}", (batch, rgb.in_channels), torch.float32)
-            _lib.check(
-                lib.gance_style_demod(wplus.data_ptr(), batch, self.num_ws, rgb.w_index,
-                                      self.rgb_mod_w[i].data_ptr(), self.rgb_mod_b[i].data_ptr(), None,
-                                      rgb.in_channels, 3, s.data_ptr(), None, stream),
-                "gance_style_demod(torgb)",
-            )
-            rgb_styles.append(s)
+        styles_all = self._buffer("styles_all", (batch * self.style_cols,), torch.float32)
+        demod_all = self._buffer("demod_all", (batch * self.demod_cols,), torch.float32)
+        _lib.check(
+            lib.gance_styles_all(wplus.data_ptr(), batch, self.num_ws, self.mod_w_cat.data_ptr(), self.style_cols,
+                                 self.mod_b_cat.data_ptr(), self.style_chunks.data_ptr(), self.style_chunks.shape[0],
+                                 styles_all.data_ptr(), self.wsq_cat.data_ptr(), self.demod_chunks.data_ptr(),
+                                 self.demod_chunks.shape[0], demod_all.data_ptr(), stream),
+            "gance_styles_all",
+        )
+
+        def block(flat: torch.Tensor, col0: int, channels: int) -> torch.Tensor:
+            return flat[batch * col0: batch * (col0 + channels)].view(batch, channels)
+
+        styles = [block(styles_all, self.style_col0[i], c.in_channels) for i, c in enumerate(self.convs)]
+        demods = [block(demod_all, self.demod_col0[i], c.out_channels) for i, c in enumerate(self.convs)]
+        rgb_styles = [block(styles_all, self.style_col0[len(self.convs) + i], r.in_channels)
+                      for i, r in enumerate(self.rgbs)]
         self._mark("styles")
 
         def layer_noise(i: int, side: int):
@@ -243,18 +282,34 @@ class GeneratorOnDevice:
             up_i, conv_i = 2 * block - 1, 2 * block
             up, conv = self.convs[up_i], self.convs[conv_i]
             side_in, side = up.in_resolution, up.out_resolution
-            scratch = self._buffer("upfir", (batch, 2 * side_in + 2, 2 * side_in + 2, up.in_channels), dt)
             x_up = self._buffer(f"up{side}", (batch, side, side, up.out_channels), dt)
             nz, nz_stride = layer_noise(up_i, side)
-            _lib.check(
-                lib.gance_modconv3x3_up2_fir(x.data_ptr(), code, batch, side_in, side_in, up.in_channels,
-                                             up.out_channels, styles[up_i].data_ptr(),
-                                             self.conv_w[up_i].data_ptr(), demods[up_i].data_ptr(), _ptr(nz),
-                                             nz_stride, self.conv_strength[up_i],
-                                             self.conv_bias[up_i].data_ptr(), styles[conv_i].data_ptr(),
-                                             scratch.data_ptr(), x_up.data_ptr(), stream),
-                f"gance_modconv3x3_up2_fir({side})",
-            )
+            if self.mode == "fp32":  # validation mode: FIR-first form on CUDA cores
+                scratch = self._buffer("upfir", (batch, 2 * side_in + 2, 2 * side_in + 2, up.in_channels), dt)
+                _lib.check(
+                    lib.gance_modconv3x3_up2_fir(x.data_ptr(), code, batch, side_in, side_in, up.in_channels,
+                                                 up.out_channels, styles[up_i].data_ptr(),
+                                                 self.conv_w[up_i].data_ptr(), demods[up_i].data_ptr(), _ptr(nz),
+                                                 nz_stride, self.conv_strength[up_i],
+                                                 self.conv_bias[up_i].data_ptr(), styles[conv_i].data_ptr(),
+                                                 scratch.data_ptr(), x_up.data_ptr(), stream),
+                    f"gance_modconv3x3_up2_fir({side})",
+                )
+            else:  # folded up-convolution: one implicit GEMM at the input resolution, N = 4*Cout
+                x_scaled = self._buffer(f"scaled{side_in}", (batch, side_in, side_in, up.in_channels), dt)
+                _lib.check(
+                    lib.gance_scale_channels(x.data_ptr(), code, batch, side_in, side_in, up.in_channels,
+                                             styles[up_i].data_ptr(), x_scaled.data_ptr(), stream),
+                    f"gance_scale_channels({side_in})",
+                )
+                _lib.check(
+                    lib.gance_modconv3x3_up2_folded(x_scaled.data_ptr(), code, batch, side_in, side_in, up.in_channels,
+                                                    up.out_channels, self.conv_w[up_i].data_ptr(),
+                                                    demods[up_i].data_ptr(), _ptr(nz), nz_stride,
+                                                    self.conv_strength[up_i], self.conv_bias[up_i].data_ptr(),
+                                                    styles[conv_i].data_ptr(), x_up.data_ptr(), stream),
+                    f"gance_modconv3x3_up2_folded({side})",
+                )
             self._mark(f"{side}/conv0_up")
             x = self._buffer(f"act{side}", (batch, side, side, conv.out_channels), dt)
             nz, nz_stride = layer_noise(conv_i, side)

@@ -82,10 +82,30 @@ int gance_style_demod(const float* wplus, int batch, int num_ws, int w_index,
                       const float* mod_weight, const float* mod_bias, const float* wsq, int c_in,
                       int c_out, float* styles, float* demod, void* stream);
 
+/* ---- styles + demodulation coefficients of every layer at once ---------------------------------
+ * The same arithmetic as gance_style_demod for ALL modulated layers of a generator in two launches
+ * (the per-layer entry costs one launch per layer: 26 at 1024^2). mod_weight_cat [512,total_cols] is
+ * the column-wise concatenation of the layers' (pre-scaled) affine weights, mod_bias_cat
+ * [total_cols]. style_chunks [n][4] int32, one row per 32 columns: {w_index, first column of the
+ * layer, Cin of the layer, first column of the chunk inside the layer}. demod_chunks [n][6] int32,
+ * one row per 32 output channels of a demodulated layer: {float offset of the layer's wsq [Cin,Cout]
+ * in wsq_cat, Cin, Cout, first style column of the layer, first output channel of the chunk, first
+ * demod column of the layer}. Outputs are layer-major: layer L's [B,C] block starts at B*col0(L). */
+int gance_styles_all(const float* wplus, int batch, int num_ws, const float* mod_weight_cat,
+                     int total_cols, const float* mod_bias_cat, const int* style_chunks,
+                     int n_style_chunks, float* styles_out, const float* wsq_cat,
+                     const int* demod_chunks, int n_demod_chunks, float* demod_out, void* stream);
+
 /* ---- learned constant input ------------------------------------------------------------------
  * tile(const, B) * styles: out[b,h,w,c] = konst[h,w,c] * styles[b,c]; konst is [4,4,C] f32. */
 int gance_const_input(const float* konst, const float* styles, int batch, int channels, int dtype,
                       void* out, void* stream);
+
+/* ---- per-sample channel scaling -----------------------------------------------------------------
+ * out[b,h,w,c] = x[b,h,w,c] * styles[b,c]: the `ww = w * s` modulation of modulated_conv2d_layer moved
+ * onto the activations, for inputs whose producer could not pre-scale them in its epilogue. */
+int gance_scale_channels(const void* x, int dtype, int batch, int h, int w, int channels,
+                         const float* styles, void* out, void* stream);
 
 /* ---- 3x3 modulated convolution with fused epilogue ---------------------------------------------
  * modulated_conv2d_layer(kernel=3, demodulate=True) + noise + fused_bias_act('lrelu'), computed
@@ -121,6 +141,23 @@ int gance_modconv3x3_up2_fir(const void* x, int dtype, int batch, int h_in, int 
                              const float* demod, const float* noise,
                              long long noise_batch_stride, float noise_strength, const float* bias,
                              const float* next_styles, void* scratch, void* out, void* stream);
+
+/* ---- up-convolution as ONE implicit GEMM at the input resolution ("folded") -----------------------
+ * modulated_conv2d_layer(up=True) = conv2d_transpose(stride 2) -> upfirdn_2d([1,3,3,1]) is linear in x,
+ * so each of the 4 output phases (py,px) is a SAME 3x3 convolution of x with its own 3x3 weight
+ *   Wf[py,px][dy][dx] = sum_{ky,kx} A_py[dy][ky] A_px[dx][kx] w[ky][kx],
+ *   A_0 = [[.75,.25,0],[.25,.75,.75],[0,0,.25]], A_1 = [[.25,0,0],[.75,.75,.25],[0,.25,.75]]
+ * (tests/test_oracle_stylegan2.py proves the identity against the transposed-conv + upfirdn form).
+ * One GEMM with N = 4*Cout computes all phases from the same A tiles; the epilogue scatters column
+ * n = (py*2+px)*Cout + co to pixel (2h+py, 2w+px). No (2H+2)^2 intermediate ever reaches HBM.
+ *   x [B,H,W,Cin] ALREADY multiplied by this layer's styles; weight_folded [4*Cout][3][3][Cin]
+ *   (GANCE_BF16 / GANCE_F16 only; the fp32 validation mode uses gance_modconv3x3_up2_fir)
+ *   noise [2H,2W] or [B,2H,2W]; out [B,2H,2W,Cout]. */
+int gance_modconv3x3_up2_folded(const void* x, int dtype, int batch, int h_in, int w_in, int c_in,
+                                int c_out, const void* weight_folded, const float* demod,
+                                const float* noise, long long noise_batch_stride,
+                                float noise_strength, const float* bias, const float* next_styles,
+                                void* out, void* stream);
 
 /* ---- ToRGB + skip accumulation (+ uint8 conversion) ---------------------------------------------
  * torgb(): modulated 1x1 conv without demodulation + bias, y = upsample_2d(y_prev) + t, and on

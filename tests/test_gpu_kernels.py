@@ -293,3 +293,41 @@ def test_up_convolution_matches_oracle(lib, mode):
     # 16-bit modes: weights, upsampled activations and output are all rounded
     tol = {"fp32": 5e-5, "bf16": 2.0 ** -5, "fp16": 2.0 ** -8}[mode]
     assert rel_err(out.permute(0, 3, 1, 2), want) < tol
+
+
+@pytest.mark.parametrize("mode", ["bf16", "fp16"])
+@pytest.mark.parametrize("cin,cout,side,batch", [(64, 32, 16, 2), (512, 512, 4, 3), (128, 64, 32, 1), (256, 128, 8, 5)])
+def test_folded_up_convolution_matches_oracle(lib, mode, cin, cout, side, batch):
+    """gance_scale_channels + gance_modconv3x3_up2_folded against the transposed-conv + upfirdn oracle."""
+    from gance_b200.synthesis import fold_up_weight
+
+    code, dt = MODE_CODES[mode]
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(batch, cin, side, side, dtype=F64, generator=g)
+    wplus, weight, mod_w, mod_b = _style_case(cin, cout, batch, 12)
+    bias = torch.randn(cout, dtype=F64, generator=g) * 0.1
+    noise = torch.randn(batch, 2 * side, 2 * side, dtype=F64, generator=g)
+    nxt = torch.randn(batch, cout, dtype=F64, generator=g)
+    strength = 0.05
+    x_dev = dev(x.permute(0, 2, 3, 1), dt)
+    x_used = x_dev.double().cpu().permute(0, 3, 1, 2)
+    s, d = run_style_demod(lib, wplus, 1, weight, mod_w, mod_b)
+    want = ref.modulated_conv2d_layer(x_used, wplus[:, 1], weight, mod_w, mod_b, up=True)
+    want = want + noise.float().double()[:, None] * np.float32(strength)
+    want = ref.apply_bias_act(want, bias, act="lrelu") * nxt.float().double()[:, :, None, None]
+    w_fold = dev(fold_up_weight(ref.get_weight(weight).float()), dt)
+    assert w_fold.shape == (4 * cout, 3, 3, cin)
+    x_scaled = torch.empty_like(x_dev)
+    _lib.check(lib.gance_scale_channels(x_dev.data_ptr(), code, batch, side, side, cin, s.data_ptr(),
+                                        x_scaled.data_ptr(), stream()), "gance_scale_channels")
+    out = torch.full((batch, 2 * side, 2 * side, cout), float("nan"), device="cuda", dtype=dt)
+    _lib.check(
+        lib.gance_modconv3x3_up2_folded(x_scaled.data_ptr(), code, batch, side, side, cin, cout, w_fold.data_ptr(),
+                                        d.data_ptr(), dev(noise).data_ptr(), 4 * side * side, strength,
+                                        dev(bias).data_ptr(), dev(nxt).data_ptr(), out.data_ptr(), stream()),
+        "gance_modconv3x3_up2_folded",
+    )
+    torch.cuda.synchronize()
+    assert not torch.isnan(out.float()).any(), "kernel left output unwritten"
+    tol = {"bf16": 2.0 ** -5, "fp16": 2.0 ** -8}[mode]  # weights, scaled activations and output are each rounded once
+    assert rel_err(out.permute(0, 3, 1, 2), want) < tol
