@@ -17,157 +17,13 @@
 //              leaky-ReLU * sqrt(2) -> (* next layer's style) -> bf16 -> 16-byte NHWC stores
 // Accumulators are double-buffered in TMEM (2 x N_TILE columns) so the epilogue of tile i
 // overlaps the MMAs of tile i+1.
-#include <cuda.h>
+#include <cstdlib>
 
-#include <type_traits>
-
-#include "common.cuh"
+#include "tc_ptx.cuh"
 
 namespace gance {
 
 namespace tc {
-
-constexpr int kTileM = 128;
-constexpr int kThreads = 192;
-constexpr int kUmmaK = 16;  // bf16
-
-struct ConvParams {
-    int batch, h_out, w_out, c_in, c_out, pad;
-    int tile_w, tile_h, tile_b;      // tile_w * tile_h * tile_b == 128 output pixels
-    int tiles_w, tiles_h, tiles_b;   // m-tiles per dimension
-    int n_tiles;                     // c_out / N_TILE
-    int k_chunks;                    // c_in / BLOCK_K
-    const float* demod;
-    const float* noise;
-    long long noise_batch_stride;
-    float noise_strength;
-    const float* bias;
-    const float* next_styles;
-    void* out;  // [B,h_out,w_out,c_out] bf16 or half; up: [B,2*h_out,2*w_out,c_real]
-    int up;      // 1: folded up-convolution, GEMM column n = phase*c_real + co, phase = py*2+px -> pixel (2h+py, 2w+px)
-    int c_real;  // channels of `out` (= c_out when !up, c_out/4 when up); demod/bias/next_styles are indexed by co
-};
-
-// ---- PTX wrappers --------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
-                 : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    const uint32_t addr = smem_u32(bar);
-    uint32_t done;
-    long long start = 0;
-    for (;;) {  // try_wait suspends the thread in hardware until the phase flips or a time-out elapses
-        asm volatile(
-            "{\n\t"
-            ".reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t"
-            "}"
-            : "=r"(done)
-            : "r"(addr), "r"(parity)
-            : "memory");
-        if (done) break;
-        // A pipeline bug must surface as a launch error, never as a hung GPU: give up after ~2 s.
-        if (start == 0) start = clock64();
-        else if (clock64() - start > 4000000000ll) __trap();
-    }
-}
-__device__ __forceinline__ void fence_barrier_init() {
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void tcgen05_fence_before() {
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-}
-__device__ __forceinline__ void tcgen05_fence_after() {
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-}
-__device__ __forceinline__ void prefetch_tmap(const CUtensorMap* m) {
-    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
-}
-__device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1,
-                                            int c2, int c3) {
-    asm volatile(
-        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes"
-        " [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(smem_u32(dst)),
-        "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
-        : "memory");
-}
-__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
-        " [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(dst)),
-        "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
-        : "memory");
-}
-__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t cols) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)),
-                 "r"(cols)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
-}
-// D[tmem] (+)= A[smem] * B[smem]^T ; both operands K-major, bf16 or half, fp32 accumulate.
-__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
-                                          uint32_t accumulate) {
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
-        "}" ::"r"(d_tmem),
-        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-// Arrive on an mbarrier once every previously issued tcgen05.mma of this thread has completed.
-__device__ __forceinline__ void umma_commit(uint64_t* bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
-                 : "memory");
-}
-// 32 lanes x 32 columns of fp32 accumulator -> 32 registers per thread (thread i = TMEM lane base+i).
-__device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32]) {
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
-          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]),
-          "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]),
-          "=r"(r[30]), "=r"(r[31])
-        : "r"(taddr)
-        : "memory");
-}
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-// UMMA shared-memory descriptor for a K-major tile whose rows are SWIZZLE_BYTES wide
-// (cute::UMMA::SmemDescriptor, mma_sm100_desc.hpp): start address >> 4 in bits [0,14),
-// LBO (ignored for swizzled K-major, canonical value 1) in [16,30), SBO = 8 rows * row bytes >> 4
-// in [32,46), version = 1 in [46,48), layout type in [61,64): 2 = SWIZZLE_128B, 4 = SWIZZLE_64B.
-template <int SWIZZLE_BYTES>
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
-    constexpr uint64_t layout = SWIZZLE_BYTES == 128 ? 2ull : (SWIZZLE_BYTES == 64 ? 4ull : 6ull);
-    constexpr uint64_t sbo = (8ull * SWIZZLE_BYTES) >> 4;
-    return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | (1ull << 16) | (sbo << 32) | (1ull << 46) | (layout << 61);
-}
-
-// tcgen05 instruction descriptor (cute::UMMA::InstrDescriptor): c_format F32 = 1 @ [4,6),
-// a_format / b_format BF16 = 1 @ [7,10) / [10,13), a_major = b_major = K (0) @ 15 / 16,
-// N >> 3 @ [17,23), M >> 4 @ [24,29).
-__host__ __device__ constexpr uint32_t make_instr_desc(int m, int n, bool half_operands) {
-    const uint32_t fmt = half_operands ? 0u : 1u;  // F16 = 0, BF16 = 1
-    return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
-}
 
 template <int N_TILE, int BLOCK_K, int STAGES>
 struct SmemLayout {
@@ -195,6 +51,79 @@ __device__ __forceinline__ TileCoord decode_tile(const ConvParams& p, int tile, 
     t.h0 = th * p.tile_h;
     t.b0 = tb * p.tile_b;
     return t;
+}
+
+// Epilogue shared by both kernels: warps 2-5, TMEM lane quarter = warp % 4, one accumulator row (= one
+// output pixel of the tile) per thread.
+template <typename T, int N_TILE>
+__device__ __forceinline__ void conv_epilogue(const ConvParams& p, int warp, int lane, int total_tiles,
+                                              uint32_t tmem_base, uint64_t* tmem_full_bar, uint64_t* tmem_empty_bar) {
+        // ===== epilogue warps: TMEM lane quarter = warp % 4 =====
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;
+    const int wl = row % p.tile_w;
+    const int hl = (row / p.tile_w) % p.tile_h;
+    const int bl = row / (p.tile_w * p.tile_h);
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const TileCoord t = decode_tile(p, tile, N_TILE);
+        const int b = t.b0 + bl, h = t.h0 + hl, w = t.w0 + wl;
+        const bool valid = b < p.batch && h < p.h_out && w < p.w_out;
+        const int bv = valid ? b : 0, hv = valid ? h : 0, wv = valid ? w : 0;
+        const int out_h = p.up ? 2 * p.h_out : p.h_out, out_w = p.up ? 2 * p.w_out : p.w_out;
+        const float* noise_b = p.noise ? p.noise + (size_t)bv * p.noise_batch_stride : nullptr;
+
+        mbar_wait(tmem_full_bar + acc, acc_phase);
+        tcgen05_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * N_TILE);
+#pragma unroll 1
+        for (int c0 = 0; c0 < N_TILE; c0 += 32) {
+            uint32_t r[32];
+            tmem_ld_32x32(taddr + (uint32_t)c0, r);
+            // column chunk -> (phase, first channel): a 32-column chunk never straddles a phase (c_real % 32 == 0)
+            const int n = t.n0 + c0;
+            const int phase = p.up ? n / p.c_real : 0;
+            const int co0 = n - phase * p.c_real;
+            const int oh = p.up ? 2 * hv + (phase >> 1) : hv, ow = p.up ? 2 * wv + (phase & 1) : wv;
+            const float nz = noise_b ? __ldg(noise_b + (size_t)oh * out_w + ow) * p.noise_strength : 0.f;
+            const size_t bc = (size_t)bv * p.c_real + co0;
+            const float4* demod4 = reinterpret_cast<const float4*>(p.demod + bc);
+            const float4* bias4 = reinterpret_cast<const float4*>(p.bias + co0);
+            const float4* style4 = p.next_styles ? reinterpret_cast<const float4*>(p.next_styles + bc) : nullptr;
+            T* dst = reinterpret_cast<T*>(p.out) + (((size_t)bv * out_h + oh) * out_w + ow) * p.c_real + co0;
+            tmem_ld_wait();
+            if (valid) {
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {  // 8 channels -> one 16-byte store
+                    float v[8];
+#pragma unroll
+                    for (int q = 0; q < 2; ++q) {
+                        const int idx = g * 2 + q;
+                        const float4 d = __ldg(demod4 + idx);
+                        const float4 bs = __ldg(bias4 + idx);
+                        float o0 = bias_lrelu(fmaf(__uint_as_float(r[g * 8 + q * 4 + 0]), d.x, nz + bs.x));
+                        float o1 = bias_lrelu(fmaf(__uint_as_float(r[g * 8 + q * 4 + 1]), d.y, nz + bs.y));
+                        float o2 = bias_lrelu(fmaf(__uint_as_float(r[g * 8 + q * 4 + 2]), d.z, nz + bs.z));
+                        float o3 = bias_lrelu(fmaf(__uint_as_float(r[g * 8 + q * 4 + 3]), d.w, nz + bs.w));
+                        if (style4 != nullptr) {
+                            const float4 s = __ldg(style4 + idx);
+                            o0 *= s.x; o1 *= s.y; o2 *= s.z; o3 *= s.w;
+                        }
+                        v[q * 4 + 0] = o0; v[q * 4 + 1] = o1; v[q * 4 + 2] = o2; v[q * 4 + 3] = o3;
+                    }
+                    Vec<T> packed;
+                    packed.from_float(v);
+                    packed.store(dst + g * 8);
+                }
+            }
+        }
+        tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tmem_empty_bar + acc);
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1u;
+    }
 }
 
 template <typename T, int N_TILE, int BLOCK_K, int STAGES>
@@ -300,72 +229,150 @@ modconv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             }
         }
     } else {
-        // ===== epilogue warps: TMEM lane quarter = warp % 4 =====
-        const int quarter = warp & 3;
-        const int row = quarter * 32 + lane;
-        const int wl = row % p.tile_w;
-        const int hl = (row / p.tile_w) % p.tile_h;
-        const int bl = row / (p.tile_w * p.tile_h);
-        int acc = 0;
-        uint32_t acc_phase = 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-            const TileCoord t = decode_tile(p, tile, N_TILE);
-            const int b = t.b0 + bl, h = t.h0 + hl, w = t.w0 + wl;
-            const bool valid = b < p.batch && h < p.h_out && w < p.w_out;
-            const int bv = valid ? b : 0, hv = valid ? h : 0, wv = valid ? w : 0;
-            const int out_h = p.up ? 2 * p.h_out : p.h_out, out_w = p.up ? 2 * p.w_out : p.w_out;
-            const float* noise_b = p.noise ? p.noise + (size_t)bv * p.noise_batch_stride : nullptr;
+        conv_epilogue<T, N_TILE>(p, warp, lane, total_tiles, tmem_base, tmem_full_bar, tmem_empty_bar);
+    }
 
-            mbar_wait(tmem_full_bar + acc, acc_phase);
-            tcgen05_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * N_TILE);
-#pragma unroll 1
-            for (int c0 = 0; c0 < N_TILE; c0 += 32) {
-                uint32_t r[32];
-                tmem_ld_32x32(taddr + (uint32_t)c0, r);
-                // column chunk -> (phase, first channel): a 32-column chunk never straddles a phase (c_real % 32 == 0)
-                const int n = t.n0 + c0;
-                const int phase = p.up ? n / p.c_real : 0;
-                const int co0 = n - phase * p.c_real;
-                const int oh = p.up ? 2 * hv + (phase >> 1) : hv, ow = p.up ? 2 * wv + (phase & 1) : wv;
-                const float nz = noise_b ? __ldg(noise_b + (size_t)oh * out_w + ow) * p.noise_strength : 0.f;
-                const size_t bc = (size_t)bv * p.c_real + co0;
-                const float4* demod4 = reinterpret_cast<const float4*>(p.demod + bc);
-                const float4* bias4 = reinterpret_cast<const float4*>(p.bias + co0);
-                const float4* style4 = p.next_styles ? reinterpret_cast<const float4*>(p.next_styles + bc) : nullptr;
-                T* dst = reinterpret_cast<T*>(p.out) + (((size_t)bv * out_h + oh) * out_w + ow) * p.c_real + co0;
-                tmem_ld_wait();
-                if (valid) {
-#pragma unroll
-                    for (int g = 0; g < 4; ++g) {  // 8 channels -> one 16-byte store
-                        float v[8];
-#pragma unroll
-                        for (int q = 0; q < 2; ++q) {
-                            const int idx = g * 2 + q;
-                            const float4 d = __ldg(demod4 + idx);
-                            const float4 bs = __ldg(bias4 + idx);
-                            float o0 = bias_lrelu(fmaf(__uint_as_float(r[g * 8 + q * 4 + 0]), d.x, nz + bs.x));
-                            float o1 = bias_lrelu(fmaf(__uint_as_float(r[g * 8 + q * 4 + 1]), d.y, nz + bs.y));
-                            float o2 = bias_lrelu(fmaf(__uint_as_float(r[g * 8 + q * 4 + 2]), d.z, nz + bs.z));
-                            float o3 = bias_lrelu(fmaf(__uint_as_float(r[g * 8 + q * 4 + 3]), d.w, nz + bs.w));
-                            if (style4 != nullptr) {
-                                const float4 s = __ldg(style4 + idx);
-                                o0 *= s.x; o1 *= s.y; o2 *= s.z; o3 *= s.w;
-                            }
-                            v[q * 4 + 0] = o0; v[q * 4 + 1] = o1; v[q * 4 + 2] = o2; v[q * 4 + 3] = o3;
-                        }
-                        Vec<T> packed;
-                        packed.from_float(v);
-                        packed.store(dst + g * 8);
-                    }
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tcgen05_fence_after();
+        tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
+// ====================================================================================================
+// Halo variant for the narrow layers (Cin = 32 or 64, SAME padding): the layers of 512^2 and 1024^2.
+//
+// The kernel above re-fetches the activation tile once per filter tap (9x the input through L2) and the
+// weight tile once per work item; with 32-64 channels that makes those layers L2-bound at ~1/8 of the
+// tensor rate. Here
+//   * the WHOLE weight matrix [9 taps][N][Cin] is loaded into shared memory once per CTA, and
+//   * ONE TMA box per tile brings the (16+2) x (8+2)-pixel halo of a 16-row x 8-column output tile;
+//     the A operand of tap (ky,kx) is the same buffer read through a shifted descriptor:
+//     start += (ky*10 + kx) pixels, 8-row groups (= 8 consecutive pixels of one image row) spaced by the
+//     halo pitch (SBO = 10 pixels). The swizzle XOR is a function of the shared-memory address bits for
+//     both the TMA write and the UMMA read, so a start shifted by whole pixel rows stays consistent.
+// L2 -> SM traffic per 128 output pixels drops from 9*128 to 180 pixel rows (6.4x) + no weight re-reads.
+// ====================================================================================================
+constexpr int kHaloTileW = 8, kHaloTileH = 16;
+constexpr int kHaloW = kHaloTileW + 2, kHaloH = kHaloTileH + 2;
+
+template <int N_GEMM, int CIN, int STAGES>
+struct HaloSmem {
+    static constexpr int kRowBytes = CIN * 2;
+    static constexpr int kWeightBytes = 9 * N_GEMM * kRowBytes;
+    static constexpr int kHaloBytes = kHaloH * kHaloW * kRowBytes;
+    static constexpr int kHaloStride = (kHaloBytes + 1023) / 1024 * 1024;
+    static constexpr int kBarrierOffset = kWeightBytes + STAGES * kHaloStride;
+    static constexpr int kBytes = kBarrierOffset + (2 * STAGES + 5) * 8 + 16 + 1024;
+};
+
+template <int SWIZZLE_BYTES>
+__device__ __forceinline__ uint64_t make_smem_desc_sbo(uint32_t smem_addr, uint32_t sbo_bytes) {
+    constexpr uint64_t layout = SWIZZLE_BYTES == 128 ? 2ull : (SWIZZLE_BYTES == 64 ? 4ull : 6ull);
+    return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(sbo_bytes >> 4) << 32) | (1ull << 46) |
+           (layout << 61);
+}
+
+template <typename T, int N_GEMM, int CIN, int STAGES>
+__global__ void __launch_bounds__(kThreads, 1)
+modconv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
+                       const ConvParams p) {
+    using L = HaloSmem<N_GEMM, CIN, STAGES>;
+    constexpr int kSwizzle = CIN * 2;  // 128 or 64 bytes per pixel row
+    constexpr uint32_t kTmemCols = 2 * N_GEMM < 32 ? 32 : 2 * N_GEMM;
+    static_assert((kTmemCols & (kTmemCols - 1)) == 0 && kTmemCols <= 512, "TMEM columns must be a power of two");
+    static_assert(CIN == 32 || CIN == 64, "one swizzled row per pixel");
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem_w = smem;
+    uint8_t* smem_halo = smem + L::kWeightBytes;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarrierOffset);
+    uint64_t* empty_bar = full_bar + STAGES;
+    uint64_t* tmem_full_bar = empty_bar + STAGES;
+    uint64_t* tmem_empty_bar = tmem_full_bar + 2;
+    uint64_t* weight_bar = tmem_empty_bar + 2;
+    uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(weight_bar + 1);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmap_x);
+        prefetch_tmap(&tmap_w);
+        for (int i = 0; i < STAGES; ++i) {
+            mbar_init(full_bar + i, 1);
+            mbar_init(empty_bar + i, 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(tmem_full_bar + i, 1);
+            mbar_init(tmem_empty_bar + i, 4);
+        }
+        mbar_init(weight_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_base_slot, kTmemCols);
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_base_slot;
+    const int total_tiles = p.tiles_b * p.tiles_h * p.tiles_w;  // n_tiles == 1: every CTA computes all N_GEMM columns
+
+    if (warp == 0) {
+        if (lane == 0) {
+            mbar_expect_tx(weight_bar, L::kWeightBytes);
+            for (int tap = 0; tap < 9; ++tap)
+                tma_load_2d(smem_w + tap * N_GEMM * L::kRowBytes, &tmap_w, weight_bar, tap * CIN, 0);
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+                const TileCoord t = decode_tile(p, tile, N_GEMM);
+                mbar_wait(empty_bar + stage, phase ^ 1u);
+                mbar_expect_tx(full_bar + stage, L::kHaloBytes);
+                tma_load_4d(smem_halo + stage * L::kHaloStride, &tmap_x, full_bar + stage, 0, t.w0 - 1, t.h0 - 1, t.b0);
+                if (++stage == STAGES) {
+                    stage = 0;
+                    phase ^= 1u;
                 }
             }
-            tcgen05_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(tmem_empty_bar + acc);
-            acc ^= 1;
-            if (acc == 0) acc_phase ^= 1u;
         }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_instr_desc(kTileM, N_GEMM, sizeof(T) == 2 && !std::is_same<T, __nv_bfloat16>::value);
+            mbar_wait(weight_bar, 0);
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            const uint32_t w_addr = smem_u32(smem_w);
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+                mbar_wait(tmem_empty_bar + acc, acc_phase ^ 1u);
+                mbar_wait(full_bar + stage, phase);
+                tcgen05_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * N_GEMM);
+                const uint32_t halo_addr = smem_u32(smem_halo + stage * L::kHaloStride);
+#pragma unroll
+                for (int tap = 0; tap < 9; ++tap) {
+                    const uint32_t a_addr = halo_addr + (uint32_t)(((tap / 3) * kHaloW + (tap % 3)) * L::kRowBytes);
+                    const uint64_t a_desc = make_smem_desc_sbo<kSwizzle>(a_addr, kHaloW * L::kRowBytes);
+                    const uint64_t b_desc = make_smem_desc<kSwizzle>(w_addr + (uint32_t)(tap * N_GEMM * L::kRowBytes));
+#pragma unroll
+                    for (int k = 0; k < CIN / kUmmaK; ++k)
+                        umma_bf16(d_tmem, a_desc + (uint64_t)(k * 2), b_desc + (uint64_t)(k * 2), idesc,
+                                  (tap | k) != 0 ? 1u : 0u);
+                }
+                umma_commit(empty_bar + stage);
+                umma_commit(tmem_full_bar + acc);
+                if (++stage == STAGES) {
+                    stage = 0;
+                    phase ^= 1u;
+                }
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1u;
+            }
+        }
+    } else {
+        conv_epilogue<T, N_GEMM>(p, warp, lane, total_tiles, tmem_base, tmem_full_bar, tmem_empty_bar);
     }
 
     tcgen05_fence_before();
@@ -449,6 +456,53 @@ static int launch(bool half_operands, const ConvParams& p, const void* x, const 
     return launch_typed<__nv_bfloat16, N_TILE, BLOCK_K, STAGES>(p, x, weight, h_in, w_in, stream);
 }
 
+template <typename T, int N_GEMM, int CIN, int STAGES>
+static int launch_halo_typed(const ConvParams& p, const void* x, const void* weight, cudaStream_t stream) {
+    using L = HaloSmem<N_GEMM, CIN, STAGES>;
+    constexpr bool kHalf = std::is_same<T, __half>::value;
+    CUtensorMap tmap_x, tmap_w;
+    {
+        cuuint64_t dims[4] = {(cuuint64_t)CIN, (cuuint64_t)p.w_out, (cuuint64_t)p.h_out, (cuuint64_t)p.batch};
+        cuuint64_t strides[3] = {(cuuint64_t)CIN * 2, (cuuint64_t)p.w_out * CIN * 2, (cuuint64_t)p.h_out * p.w_out * CIN * 2};
+        cuuint32_t box[4] = {(cuuint32_t)CIN, (cuuint32_t)kHaloW, (cuuint32_t)kHaloH, 1u};
+        int rc = make_tmap(&tmap_x, x, kHalf, 4, dims, strides, box, CIN * 2);
+        if (rc != GANCE_OK) return rc;
+    }
+    {
+        cuuint64_t dims[2] = {(cuuint64_t)9 * CIN, (cuuint64_t)N_GEMM};
+        cuuint64_t strides[1] = {(cuuint64_t)9 * CIN * 2};
+        cuuint32_t box[2] = {(cuuint32_t)CIN, (cuuint32_t)N_GEMM};
+        int rc = make_tmap(&tmap_w, weight, kHalf, 2, dims, strides, box, CIN * 2);
+        if (rc != GANCE_OK) return rc;
+    }
+    const int total_tiles = p.tiles_b * p.tiles_h * p.tiles_w;
+    const int grid = total_tiles < g_num_sms ? total_tiles : g_num_sms;
+    modconv3x3_halo_kernel<T, N_GEMM, CIN, STAGES><<<grid, kThreads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
+    return check_launch("modconv3x3_halo_kernel");
+}
+
+template <int N_GEMM, int CIN, int STAGES>
+static int launch_halo(bool half_operands, const ConvParams& p, const void* x, const void* weight, cudaStream_t stream) {
+    if (half_operands) return launch_halo_typed<__half, N_GEMM, CIN, STAGES>(p, x, weight, stream);
+    return launch_halo_typed<__nv_bfloat16, N_GEMM, CIN, STAGES>(p, x, weight, stream);
+}
+
+template <int N_GEMM, int CIN, int STAGES>
+static int configure_halo() {
+    using L = HaloSmem<N_GEMM, CIN, STAGES>;
+    cudaError_t err = cudaFuncSetAttribute(modconv3x3_halo_kernel<__nv_bfloat16, N_GEMM, CIN, STAGES>,
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes);
+    if (err == cudaSuccess)
+        err = cudaFuncSetAttribute(modconv3x3_halo_kernel<__half, N_GEMM, CIN, STAGES>,
+                                   cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes);
+    if (err != cudaSuccess)
+        return fail(-(int)err, "cudaFuncSetAttribute(modconv3x3_halo<%d,%d,%d>, %d B): %s", N_GEMM, CIN, STAGES, L::kBytes,
+                    cudaGetErrorString(err));
+    return GANCE_OK;
+}
+
+static bool g_use_halo = true;
+
 }  // namespace tc
 
 int init_tensor_core_path() {
@@ -468,6 +522,11 @@ int init_tensor_core_path() {
     if ((rc = tc::configure<64, 64, 8>()) != GANCE_OK) return rc;
     if ((rc = tc::configure<32, 64, 8>()) != GANCE_OK) return rc;
     if ((rc = tc::configure<32, 32, 8>()) != GANCE_OK) return rc;
+    if ((rc = tc::configure_halo<128, 64, 2>()) != GANCE_OK) return rc;
+    if ((rc = tc::configure_halo<64, 64, 3>()) != GANCE_OK) return rc;
+    if ((rc = tc::configure_halo<32, 32, 4>()) != GANCE_OK) return rc;
+    const char* halo = getenv("GANCE_HALO");  // GANCE_HALO=0 forces the per-tap kernel (A/B measurements)
+    tc::g_use_halo = !(halo != nullptr && halo[0] == '0');
     return GANCE_OK;
 }
 
@@ -511,6 +570,16 @@ static int launch_tensor_core_conv(const char* who, const void* x, int dtype, in
     const int h_in = h_out + 2 - 2 * pad, w_in = w_out + 2 - 2 * pad;
     const int m_tiles = p.tiles_w * p.tiles_h * p.tiles_b;
 
+    // Narrow layers (512^2 / 1024^2): halo kernel, whole weight resident, one activation fetch per tile.
+    if (tc::g_use_halo && pad == 1 && w_out % tc::kHaloTileW == 0 && h_out % tc::kHaloTileH == 0 &&
+        ((c_in == 64 && (c_out == 128 || c_out == 64)) || (c_in == 32 && c_out == 32))) {
+        p.tile_w = tc::kHaloTileW; p.tile_h = tc::kHaloTileH; p.tile_b = 1;
+        p.tiles_w = w_out / p.tile_w; p.tiles_h = h_out / p.tile_h; p.tiles_b = batch;
+        p.n_tiles = 1; p.k_chunks = 1;
+        if (c_in == 32) return tc::launch_halo<32, 32, 4>(half_operands, p, x, weight, s);
+        if (c_out == 128) return tc::launch_halo<128, 64, 2>(half_operands, p, x, weight, s);
+        return tc::launch_halo<64, 64, 3>(half_operands, p, x, weight, s);
+    }
     if (c_in % 64 != 0) {  // Cin = 32 (1024^2 Conv1 in config-f): 64-byte rows, SWIZZLE_64B
         p.n_tiles = c_out / 32; p.k_chunks = c_in / 32;
         return tc::launch<32, 32, 8>(half_operands, p, x, weight, h_in, w_in, s);

@@ -196,6 +196,9 @@ CONV_CASES = [
     (128, 64, 32, 2, 1, "N=64"),
     (64, 32, 32, 2, 1, "N=32 K=64"),
     (32, 32, 64, 2, 1, "Cin=32: SWIZZLE_64B"),
+    (64, 64, 32, 3, 1, "halo kernel N=64 (512^2 Conv1 shape)"),
+    (64, 128, 16, 2, 1, "halo kernel N=128"),
+    (64, 64, 48, 1, 1, "halo kernel, 3x6 tiles"),
     (64, 64, 32, 2, 0, "VALID (up-conv second half)"),
     (512, 512, 8, 2, 0, "VALID 8x8"),
 ]
