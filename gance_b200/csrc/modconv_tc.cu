@@ -25,13 +25,19 @@ namespace gance {
 
 namespace tc {
 
+constexpr int kEpilogueThreads = 128;
+constexpr int kCacheFloatsPerChannel = 6;  // demod, bias, next style, rgb weight x3
+constexpr int kCacheMaxChannels = 512;
+constexpr int kCacheBytes = kCacheFloatsPerChannel * kCacheMaxChannels * 4;
+
 template <int N_TILE, int BLOCK_K, int STAGES>
 struct SmemLayout {
     static constexpr int kABytes = kTileM * BLOCK_K * 2;
     static constexpr int kBBytes = N_TILE * BLOCK_K * 2;
     static constexpr int kStageBytes = kABytes + kBBytes;
     static constexpr int kBarrierOffset = STAGES * kStageBytes;
-    static constexpr int kBytes = kBarrierOffset + (2 * STAGES + 4) * 8 + 16 + 1024;  // + alignment slack
+    static constexpr int kCacheOffset = kBarrierOffset + (2 * STAGES + 4) * 8 + 16;
+    static constexpr int kBytes = kCacheOffset + kCacheBytes + 1024;  // + alignment slack
 };
 
 struct TileCoord {
@@ -54,16 +60,34 @@ __device__ __forceinline__ TileCoord decode_tile(const ConvParams& p, int tile, 
 }
 
 // Epilogue shared by both kernels: warps 2-5, TMEM lane quarter = warp % 4, one accumulator row (= one
-// output pixel of the tile) per thread.
+// output pixel of the tile) per thread:
+//   v = lrelu(acc * demod[b,co] + noise * strength + bias[co]) * sqrt(2)
+//   fused ToRGB (p.rgb_weight): rgb += v * (rgb_styles[b,co] * rgb_weight[co,:]) in fp32, then
+//       y = upsample_2d(y_prev) + rgb + rgb_bias -> y_out (fp32) and/or uint8 frames
+//   x_out = v * next_styles[b,co] (the next convolution's modulation) -> 16-bit NHWC store (skipped if out == NULL)
+// When a tile holds pixels of ONE sample (tile_b == 1) the per-(sample, channel) coefficients are staged in
+// shared memory once per sample instead of being fetched from L2 by every thread for every tile.
+
+__device__ __forceinline__ void epilogue_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
 template <typename T, int N_TILE>
 __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int warp, int lane, int total_tiles,
-                                              uint32_t tmem_base, uint64_t* tmem_full_bar, uint64_t* tmem_empty_bar) {
-        // ===== epilogue warps: TMEM lane quarter = warp % 4 =====
+                                              uint32_t tmem_base, uint64_t* tmem_full_bar, uint64_t* tmem_empty_bar,
+                                              float* cache) {
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
     const int wl = row % p.tile_w;
     const int hl = (row / p.tile_w) % p.tile_h;
     const int bl = row / (p.tile_w * p.tile_h);
+    const int C = p.c_real;
+    const bool use_cache = p.tile_b == 1 && C <= kCacheMaxChannels;
+    const bool fuse_rgb = p.rgb_weight != nullptr;
+    const int out_h = p.up ? 2 * p.h_out : p.h_out, out_w = p.up ? 2 * p.w_out : p.w_out;
+    float* c_demod = cache;
+    float* c_bias = cache + C;
+    float* c_style = cache + 2 * C;
+    float* c_rgb = cache + 3 * C;
+    int cached_b = -1;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -71,8 +95,31 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int warp, int
         const int b = t.b0 + bl, h = t.h0 + hl, w = t.w0 + wl;
         const bool valid = b < p.batch && h < p.h_out && w < p.w_out;
         const int bv = valid ? b : 0, hv = valid ? h : 0, wv = valid ? w : 0;
-        const int out_h = p.up ? 2 * p.h_out : p.h_out, out_w = p.up ? 2 * p.w_out : p.w_out;
+        if (use_cache && t.b0 != cached_b) {  // CTA-uniform: all four epilogue warps work on the same tile
+            epilogue_bar_sync();              // everyone is done reading the previous sample's coefficients
+            const int tid = (warp - 2) * 32 + lane;
+            for (int i = tid; i < C; i += kEpilogueThreads) {
+                const size_t bc = (size_t)t.b0 * C + i;
+                c_demod[i] = __ldg(p.demod + bc);
+                c_bias[i] = __ldg(p.bias + i);
+                c_style[i] = p.next_styles ? __ldg(p.next_styles + bc) : 1.0f;
+                if (fuse_rgb) {
+                    const float s = __ldg(p.rgb_styles + bc);
+                    c_rgb[3 * i + 0] = s * __ldg(p.rgb_weight + 3 * i + 0);
+                    c_rgb[3 * i + 1] = s * __ldg(p.rgb_weight + 3 * i + 1);
+                    c_rgb[3 * i + 2] = s * __ldg(p.rgb_weight + 3 * i + 2);
+                }
+            }
+            epilogue_bar_sync();
+            cached_b = t.b0;
+        }
         const float* noise_b = p.noise ? p.noise + (size_t)bv * p.noise_batch_stride : nullptr;
+        // the skip-connection taps do not depend on the accumulator: fetch them while the MMAs run
+        float4 skip = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (fuse_rgb && valid && p.y_prev != nullptr) skip = upsample_tap(p.y_prev, bv, p.h_out >> 1, p.w_out >> 1, hv, wv);
+        float nz_same = 0.f;
+        if (!p.up && noise_b != nullptr) nz_same = __ldg(noise_b + (size_t)hv * out_w + wv) * p.noise_strength;
+        float red = 0.f, green = 0.f, blue = 0.f;
 
         mbar_wait(tmem_full_bar + acc, acc_phase);
         tcgen05_fence_after();
@@ -83,44 +130,63 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int warp, int
             tmem_ld_32x32(taddr + (uint32_t)c0, r);
             // column chunk -> (phase, first channel): a 32-column chunk never straddles a phase (c_real % 32 == 0)
             const int n = t.n0 + c0;
-            const int phase = p.up ? n / p.c_real : 0;
-            const int co0 = n - phase * p.c_real;
+            const int phase = p.up ? n / C : 0;
+            const int co0 = n - phase * C;
             const int oh = p.up ? 2 * hv + (phase >> 1) : hv, ow = p.up ? 2 * wv + (phase & 1) : wv;
-            const float nz = noise_b ? __ldg(noise_b + (size_t)oh * out_w + ow) * p.noise_strength : 0.f;
-            const size_t bc = (size_t)bv * p.c_real + co0;
-            const float4* demod4 = reinterpret_cast<const float4*>(p.demod + bc);
-            const float4* bias4 = reinterpret_cast<const float4*>(p.bias + co0);
-            const float4* style4 = p.next_styles ? reinterpret_cast<const float4*>(p.next_styles + bc) : nullptr;
-            T* dst = reinterpret_cast<T*>(p.out) + (((size_t)bv * out_h + oh) * out_w + ow) * p.c_real + co0;
+            float nz = nz_same;
+            if (p.up && noise_b != nullptr) nz = __ldg(noise_b + (size_t)oh * out_w + ow) * p.noise_strength;
+            T* dst = p.out ? reinterpret_cast<T*>(p.out) + (((size_t)bv * out_h + oh) * out_w + ow) * C + co0 : nullptr;
+            const size_t bc = (size_t)bv * C + co0;
             tmem_ld_wait();
             if (valid) {
 #pragma unroll
                 for (int g = 0; g < 4; ++g) {  // 8 channels -> one 16-byte store
                     float v[8];
 #pragma unroll
-                    for (int q = 0; q < 2; ++q) {
-                        const int idx = g * 2 + q;
-                        const float4 d = __ldg(demod4 + idx);
-                        const float4 bs = __ldg(bias4 + idx);
-                        float o0 = bias_lrelu(fmaf(__uint_as_float(r[g * 8 + q * 4 + 0]), d.x, nz + bs.x));
-                        float o1 = bias_lrelu(fmaf(__uint_as_float(r[g * 8 + q * 4 + 1]), d.y, nz + bs.y));
-                        float o2 = bias_lrelu(fmaf(__uint_as_float(r[g * 8 + q * 4 + 2]), d.z, nz + bs.z));
-                        float o3 = bias_lrelu(fmaf(__uint_as_float(r[g * 8 + q * 4 + 3]), d.w, nz + bs.w));
-                        if (style4 != nullptr) {
-                            const float4 s = __ldg(style4 + idx);
-                            o0 *= s.x; o1 *= s.y; o2 *= s.z; o3 *= s.w;
+                    for (int q = 0; q < 8; ++q) {
+                        const int c = co0 + g * 8 + q;
+                        float d, bs, st;
+                        if (use_cache) {
+                            d = c_demod[c]; bs = c_bias[c]; st = c_style[c];
+                        } else {
+                            d = __ldg(p.demod + bc + g * 8 + q);
+                            bs = __ldg(p.bias + c);
+                            st = p.next_styles ? __ldg(p.next_styles + bc + g * 8 + q) : 1.0f;
                         }
-                        v[q * 4 + 0] = o0; v[q * 4 + 1] = o1; v[q * 4 + 2] = o2; v[q * 4 + 3] = o3;
+                        const float o = bias_lrelu(fmaf(__uint_as_float(r[g * 8 + q]), d, nz + bs));
+                        if (fuse_rgb) {
+                            float w0, w1, w2;
+                            if (use_cache) {
+                                w0 = c_rgb[3 * c]; w1 = c_rgb[3 * c + 1]; w2 = c_rgb[3 * c + 2];
+                            } else {
+                                const float s = __ldg(p.rgb_styles + bc + g * 8 + q);
+                                w0 = s * __ldg(p.rgb_weight + 3 * c); w1 = s * __ldg(p.rgb_weight + 3 * c + 1);
+                                w2 = s * __ldg(p.rgb_weight + 3 * c + 2);
+                            }
+                            red = fmaf(o, w0, red); green = fmaf(o, w1, green); blue = fmaf(o, w2, blue);
+                        }
+                        v[q] = o * st;
                     }
-                    Vec<T> packed;
-                    packed.from_float(v);
-                    packed.store(dst + g * 8);
+                    if (dst != nullptr) {
+                        Vec<T> packed;
+                        packed.from_float(v);
+                        packed.store(dst + g * 8);
+                    }
                 }
             }
         }
         tcgen05_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(tmem_empty_bar + acc);
+        if (lane == 0) mbar_arrive(tmem_empty_bar + acc);  // accumulator drained: the MMAs of tile+2 may start
+        if (fuse_rgb && valid) {
+            red += __ldg(p.rgb_bias) + skip.x; green += __ldg(p.rgb_bias + 1) + skip.y; blue += __ldg(p.rgb_bias + 2) + skip.z;
+            const size_t pixel = ((size_t)bv * p.h_out + hv) * p.w_out + wv;
+            if (p.y_out != nullptr) reinterpret_cast<float4*>(p.y_out)[pixel] = make_float4(red, green, blue, 0.f);
+            if (p.frames != nullptr) {
+                uint8_t* f = p.frames + pixel * 3;
+                f[0] = to_u8(red); f[1] = to_u8(green); f[2] = to_u8(blue);
+            }
+        }
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1u;
     }
@@ -229,7 +295,8 @@ modconv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             }
         }
     } else {
-        conv_epilogue<T, N_TILE>(p, warp, lane, total_tiles, tmem_base, tmem_full_bar, tmem_empty_bar);
+        conv_epilogue<T, N_TILE>(p, warp, lane, total_tiles, tmem_base, tmem_full_bar, tmem_empty_bar,
+                                 reinterpret_cast<float*>(smem + L::kCacheOffset));
     }
 
     tcgen05_fence_before();
@@ -264,7 +331,8 @@ struct HaloSmem {
     static constexpr int kHaloBytes = kHaloH * kHaloW * kRowBytes;
     static constexpr int kHaloStride = (kHaloBytes + 1023) / 1024 * 1024;
     static constexpr int kBarrierOffset = kWeightBytes + STAGES * kHaloStride;
-    static constexpr int kBytes = kBarrierOffset + (2 * STAGES + 5) * 8 + 16 + 1024;
+    static constexpr int kCacheOffset = kBarrierOffset + (2 * STAGES + 5) * 8 + 16;
+    static constexpr int kBytes = kCacheOffset + kCacheBytes + 1024;
 };
 
 template <int SWIZZLE_BYTES>
@@ -372,7 +440,8 @@ modconv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_
             }
         }
     } else {
-        conv_epilogue<T, N_GEMM>(p, warp, lane, total_tiles, tmem_base, tmem_full_bar, tmem_empty_bar);
+        conv_epilogue<T, N_GEMM>(p, warp, lane, total_tiles, tmem_base, tmem_full_bar, tmem_empty_bar,
+                                 reinterpret_cast<float*>(smem + L::kCacheOffset));
     }
 
     tcgen05_fence_before();
@@ -539,11 +608,21 @@ int launch_modconv3x3_f32(const float* x, int batch, int h_out, int w_out, int c
 
 using namespace gance;
 
+struct RgbFusion {
+    const float* styles;
+    const float* weight;
+    const float* bias;
+    const float* y_prev;
+    float* y_out;
+    uint8_t* frames;
+};
+
 // Shared launcher of the tcgen05 path. `c_out` is the GEMM N (4 * c_real for a folded up-convolution).
 static int launch_tensor_core_conv(const char* who, const void* x, int dtype, int batch, int h_out, int w_out, int c_in,
                                    int c_out, int pad, int up, int c_real, const void* weight, const float* demod,
                                    const float* noise, long long noise_batch_stride, float noise_strength,
-                                   const float* bias, const float* next_styles, void* out, cudaStream_t s) {
+                                   const float* bias, const float* next_styles, void* out, cudaStream_t s,
+                                   const RgbFusion* rgb = nullptr) {
     GANCE_REQUIRE(dtype == GANCE_BF16 || dtype == GANCE_F16, GANCE_E_DTYPE, "%s: dtype %d", who, dtype);
     const bool half_operands = dtype == GANCE_F16;
     GANCE_REQUIRE(c_in % 32 == 0 && c_real % 32 == 0, GANCE_E_SHAPE,
@@ -567,6 +646,12 @@ static int launch_tensor_core_conv(const char* who, const void* x, int dtype, in
     p.tiles_b = (batch + p.tile_b - 1) / p.tile_b;
     p.demod = demod; p.noise = noise; p.noise_batch_stride = noise_batch_stride; p.noise_strength = noise_strength;
     p.bias = bias; p.next_styles = next_styles; p.out = out;
+    p.rgb_styles = rgb ? rgb->styles : nullptr; p.rgb_weight = rgb ? rgb->weight : nullptr;
+    p.rgb_bias = rgb ? rgb->bias : nullptr; p.y_prev = rgb ? rgb->y_prev : nullptr;
+    p.y_out = rgb ? rgb->y_out : nullptr; p.frames = rgb ? rgb->frames : nullptr;
+    const bool one_n_tile = rgb != nullptr;  // the fused ToRGB needs every channel of a pixel in one tile
+    GANCE_REQUIRE(!one_n_tile || (up == 0 && (c_out == 256 || c_out == 128 || c_out == 64 || c_out == 32)), GANCE_E_SHAPE,
+                  "%s: fused ToRGB needs Cout in {32,64,128,256} (got %d)", who, c_out);
     const int h_in = h_out + 2 - 2 * pad, w_in = w_out + 2 - 2 * pad;
     const int m_tiles = p.tiles_w * p.tiles_h * p.tiles_b;
 
@@ -585,15 +670,15 @@ static int launch_tensor_core_conv(const char* who, const void* x, int dtype, in
         return tc::launch<32, 32, 8>(half_operands, p, x, weight, h_in, w_in, s);
     }
     p.k_chunks = c_in / 64;
-    if (c_out % 256 == 0 && m_tiles >= 148) {
+    if (c_out % 256 == 0 && (m_tiles >= 148 || one_n_tile)) {
         p.n_tiles = c_out / 256;
         return tc::launch<256, 64, 4>(half_operands, p, x, weight, h_in, w_in, s);
     }
-    if (c_out % 128 == 0) {
+    if (c_out % 128 == 0 && !(one_n_tile && c_out != 128)) {
         p.n_tiles = c_out / 128;
         return tc::launch<128, 64, 6>(half_operands, p, x, weight, h_in, w_in, s);
     }
-    if (c_out % 64 == 0) {
+    if (c_out % 64 == 0 && !(one_n_tile && c_out != 64)) {
         p.n_tiles = c_out / 64;
         return tc::launch<64, 64, 8>(half_operands, p, x, weight, h_in, w_in, s);
     }
@@ -617,6 +702,27 @@ extern "C" int gance_modconv3x3(const void* x, int dtype, int batch, int h_out, 
                                      (float*)out, s);
     return launch_tensor_core_conv("gance_modconv3x3", x, dtype, batch, h_out, w_out, c_in, c_out, pad, /*up=*/0, c_out,
                                    weight, demod, noise, noise_batch_stride, noise_strength, bias, next_styles, out, s);
+}
+
+extern "C" int gance_modconv3x3_torgb(const void* x, int dtype, int batch, int h, int w, int c_in, int c_out,
+                                      const void* weight, const float* demod, const float* noise,
+                                      long long noise_batch_stride, float noise_strength, const float* bias,
+                                      const float* next_styles, void* out, const float* rgb_styles,
+                                      const float* rgb_weight, const float* rgb_bias, const float* y_prev, float* y_out,
+                                      uint8_t* frames, void* stream) {
+    GANCE_REQUIRE(is_initialised(), GANCE_E_NOT_INIT, "gance_init() has not been called");
+    GANCE_REQUIRE(x && weight && demod && bias && rgb_styles && rgb_weight && rgb_bias, GANCE_E_NULL,
+                  "gance_modconv3x3_torgb: NULL pointer");
+    GANCE_REQUIRE(y_out || frames, GANCE_E_NULL, "gance_modconv3x3_torgb: neither y_out nor frames given");
+    GANCE_REQUIRE(batch > 0 && h > 0 && w > 0 && c_in > 0 && c_out > 0, GANCE_E_SHAPE,
+                  "gance_modconv3x3_torgb: shape B=%d H=%d W=%d Cin=%d Cout=%d", batch, h, w, c_in, c_out);
+    GANCE_REQUIRE(y_prev == nullptr || (h % 2 == 0 && w % 2 == 0), GANCE_E_SHAPE,
+                  "gance_modconv3x3_torgb: skip input needs even h,w");
+    GANCE_REQUIRE(aligned16(y_prev) && aligned16(y_out), GANCE_E_ALIGN, "gance_modconv3x3_torgb: y pointers must be 16-byte aligned");
+    const RgbFusion rgb{rgb_styles, rgb_weight, rgb_bias, y_prev, y_out, frames};
+    return launch_tensor_core_conv("gance_modconv3x3_torgb", x, dtype, batch, h, w, c_in, c_out, /*pad=*/1, /*up=*/0, c_out,
+                                   weight, demod, noise, noise_batch_stride, noise_strength, bias, next_styles, out,
+                                   (cudaStream_t)stream, &rgb);
 }
 
 extern "C" int gance_modconv3x3_up2_folded(const void* x, int dtype, int batch, int h_in, int w_in, int c_in, int c_out,

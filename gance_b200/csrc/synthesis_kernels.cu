@@ -307,37 +307,6 @@ __global__ void __launch_bounds__(256) scale_channels_kernel(const T* __restrict
     }
 }
 
-__device__ __forceinline__ float4 upsample_tap(const float* __restrict__ y_prev, int b, int hp, int wp,
-                                               int h, int w) {
-    // upsample_2d(k=[1,3,3,1]): y[2a] = .25 p[a-1] + .75 p[a]; y[2a+1] = .75 p[a] + .25 p[a+1]
-    const int a = h >> 1, c = w >> 1;
-    const int a2 = (h & 1) ? a + 1 : a - 1, c2 = (w & 1) ? c + 1 : c - 1;
-    const float4* base = reinterpret_cast<const float4*>(y_prev) + (size_t)b * hp * wp;
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    const float4 p00 = __ldg(base + (size_t)a * wp + c);
-    acc.x = 0.5625f * p00.x; acc.y = 0.5625f * p00.y; acc.z = 0.5625f * p00.z;
-    if (c2 >= 0 && c2 < wp) {
-        const float4 p = __ldg(base + (size_t)a * wp + c2);
-        acc.x += 0.1875f * p.x; acc.y += 0.1875f * p.y; acc.z += 0.1875f * p.z;
-    }
-    if (a2 >= 0 && a2 < hp) {
-        const float4 p = __ldg(base + (size_t)a2 * wp + c);
-        acc.x += 0.1875f * p.x; acc.y += 0.1875f * p.y; acc.z += 0.1875f * p.z;
-        if (c2 >= 0 && c2 < wp) {
-            const float4 q = __ldg(base + (size_t)a2 * wp + c2);
-            acc.x += 0.0625f * q.x; acc.y += 0.0625f * q.y; acc.z += 0.0625f * q.z;
-        }
-    }
-    return acc;
-}
-
-__device__ __forceinline__ uint8_t to_u8(float v) {
-    // convert_images_to_uint8: v*127.5 + 128, saturate_cast<uint8> = clamp then truncate
-    float s = fmaf(v, 127.5f, 128.0f);
-    s = fminf(fmaxf(s, 0.0f), 255.0f);
-    return (uint8_t)(int)s;
-}
-
 template <typename T, int LANES>
 __global__ void __launch_bounds__(256) torgb_skip_kernel(const T* __restrict__ x, int h, int w, int channels,
                                                          const float* __restrict__ styles,

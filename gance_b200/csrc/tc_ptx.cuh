@@ -28,6 +28,13 @@ struct ConvParams {
     const float* next_styles;
     void* out;  // [B,h_out,w_out,c_out] bf16 or half; up: [B,2*h_out,2*w_out,c_real]
     int up;      // 1: folded up-convolution, GEMM column n = phase*c_real + co, phase = py*2+px -> pixel (2h+py, 2w+px)
+    // fused ToRGB + skip (+ uint8), conv1 layers whose channels fit one N tile; all NULL otherwise
+    const float* rgb_styles;  // [B, c_real]
+    const float* rgb_weight;  // [c_real, 3], pre-multiplied by 1/sqrt(c_real)
+    const float* rgb_bias;    // [3]
+    const float* y_prev;      // [B, H/2, W/2, 4] f32 or NULL
+    float* y_out;             // [B, H, W, 4] f32 or NULL
+    uint8_t* frames;          // [B, H, W, 3] u8 or NULL
     int c_real;  // channels of `out` (= c_out when !up, c_out/4 when up); demod/bias/next_styles are indexed by co
 };
 

@@ -278,6 +278,7 @@ class GeneratorOnDevice:
         self._mark("4/torgb")
 
         # -- one block per resolution
+        x_prescaled = False  # True when `x` already carries the next up-convolution's styles
         for block in range(1, len(self.rgbs)):
             up_i, conv_i = 2 * block - 1, 2 * block
             up, conv = self.convs[up_i], self.convs[conv_i]
@@ -296,12 +297,14 @@ class GeneratorOnDevice:
                     f"gance_modconv3x3_up2_fir({side})",
                 )
             else:  # folded up-convolution: one implicit GEMM at the input resolution, N = 4*Cout
-                x_scaled = self._buffer(f"scaled{side_in}", (batch, side_in, side_in, up.in_channels), dt)
-                _lib.check(
-                    lib.gance_scale_channels(x.data_ptr(), code, batch, side_in, side_in, up.in_channels,
-                                             styles[up_i].data_ptr(), x_scaled.data_ptr(), stream),
-                    f"gance_scale_channels({side_in})",
-                )
+                x_scaled = x
+                if not x_prescaled:
+                    x_scaled = self._buffer(f"scaled{side_in}", (batch, side_in, side_in, up.in_channels), dt)
+                    _lib.check(
+                        lib.gance_scale_channels(x.data_ptr(), code, batch, side_in, side_in, up.in_channels,
+                                                 styles[up_i].data_ptr(), x_scaled.data_ptr(), stream),
+                        f"gance_scale_channels({side_in})",
+                    )
                 _lib.check(
                     lib.gance_modconv3x3_up2_folded(x_scaled.data_ptr(), code, batch, side_in, side_in, up.in_channels,
                                                     up.out_channels, self.conv_w[up_i].data_ptr(),
@@ -311,27 +314,46 @@ class GeneratorOnDevice:
                     f"gance_modconv3x3_up2_folded({side})",
                 )
             self._mark(f"{side}/conv0_up")
-            x = self._buffer(f"act{side}", (batch, side, side, conv.out_channels), dt)
             nz, nz_stride = layer_noise(conv_i, side)
-            _lib.check(
-                lib.gance_modconv3x3(x_up.data_ptr(), code, batch, side, side, conv.in_channels,
-                                     conv.out_channels, 1, self.conv_w[conv_i].data_ptr(),
-                                     demods[conv_i].data_ptr(), _ptr(nz), nz_stride, self.conv_strength[conv_i],
-                                     self.conv_bias[conv_i].data_ptr(), None, x.data_ptr(), stream),
-                f"gance_modconv3x3({side})",
-            )
-            self._mark(f"{side}/conv1")
             is_last = block == last
             want_float = return_float_image or not is_last
             y_out = self._buffer(f"skip{side}", (batch, side, side, 4), torch.float32) if want_float else None
-            _lib.check(
-                lib.gance_torgb_skip(x.data_ptr(), code, batch, side, side, conv.out_channels,
-                                     rgb_styles[block].data_ptr(), self.rgb_w[block].data_ptr(),
-                                     self.rgb_bias[block].data_ptr(), _ptr(y), _ptr(y_out),
-                                     frames.data_ptr() if is_last else None, stream),
-                f"gance_torgb_skip({side})",
-            )
-            self._mark(f"{side}/torgb")
+            if self.mode != "fp32" and conv.out_channels <= 256:
+                # Conv1 + ToRGB + skip (+ uint8) in one kernel; its activation output is pre-multiplied by the
+                # NEXT up-convolution's styles, and not written at all on the last block (nothing reads it).
+                x = None if is_last else self._buffer(f"act{side}", (batch, side, side, conv.out_channels), dt)
+                next_style = None if is_last else styles[conv_i + 1]
+                _lib.check(
+                    lib.gance_modconv3x3_torgb(x_up.data_ptr(), code, batch, side, side, conv.in_channels,
+                                               conv.out_channels, self.conv_w[conv_i].data_ptr(),
+                                               demods[conv_i].data_ptr(), _ptr(nz), nz_stride,
+                                               self.conv_strength[conv_i], self.conv_bias[conv_i].data_ptr(),
+                                               _ptr(next_style), _ptr(x), rgb_styles[block].data_ptr(),
+                                               self.rgb_w[block].data_ptr(), self.rgb_bias[block].data_ptr(), _ptr(y),
+                                               _ptr(y_out), frames.data_ptr() if is_last else None, stream),
+                    f"gance_modconv3x3_torgb({side})",
+                )
+                x_prescaled = True
+                self._mark(f"{side}/conv1")
+            else:
+                x = self._buffer(f"act{side}", (batch, side, side, conv.out_channels), dt)
+                _lib.check(
+                    lib.gance_modconv3x3(x_up.data_ptr(), code, batch, side, side, conv.in_channels,
+                                         conv.out_channels, 1, self.conv_w[conv_i].data_ptr(),
+                                         demods[conv_i].data_ptr(), _ptr(nz), nz_stride, self.conv_strength[conv_i],
+                                         self.conv_bias[conv_i].data_ptr(), None, x.data_ptr(), stream),
+                    f"gance_modconv3x3({side})",
+                )
+                x_prescaled = False
+                self._mark(f"{side}/conv1")
+                _lib.check(
+                    lib.gance_torgb_skip(x.data_ptr(), code, batch, side, side, conv.out_channels,
+                                         rgb_styles[block].data_ptr(), self.rgb_w[block].data_ptr(),
+                                         self.rgb_bias[block].data_ptr(), _ptr(y), _ptr(y_out),
+                                         frames.data_ptr() if is_last else None, stream),
+                    f"gance_torgb_skip({side})",
+                )
+                self._mark(f"{side}/torgb")
             y = y_out
         if return_float_image:
             return frames, y

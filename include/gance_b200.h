@@ -159,6 +159,20 @@ int gance_modconv3x3_up2_folded(const void* x, int dtype, int batch, int h_in, i
                                 float noise_strength, const float* bias, const float* next_styles,
                                 void* out, void* stream);
 
+/* ---- Conv1 + ToRGB + skip (+ uint8) in one kernel ------------------------------------------------
+ * gance_modconv3x3 (SAME) whose epilogue also evaluates torgb() on the fp32 activations it has in
+ * registers: rgb = sum_co v[co] * rgb_styles[b,co] * rgb_weight[co,:] + rgb_bias, y = upsample_2d(y_prev)
+ * + rgb -> y_out [B,H,W,4] f32 and/or convert_images_to_uint8 -> frames [B,H,W,3]. The activation
+ * tensor is never re-read (gance_torgb_skip would) and `out` may be NULL on the last block, where nothing
+ * consumes it. next_styles (the NEXT up-convolution's styles) is applied to `out` only.
+ * GANCE_BF16 / GANCE_F16; Cout in {32,64,128,256} (all channels of a pixel in one accumulator tile). */
+int gance_modconv3x3_torgb(const void* x, int dtype, int batch, int h, int w, int c_in, int c_out,
+                           const void* weight, const float* demod, const float* noise,
+                           long long noise_batch_stride, float noise_strength, const float* bias,
+                           const float* next_styles, void* out, const float* rgb_styles,
+                           const float* rgb_weight, const float* rgb_bias, const float* y_prev,
+                           float* y_out, uint8_t* frames, void* stream);
+
 /* ---- ToRGB + skip accumulation (+ uint8 conversion) ---------------------------------------------
  * torgb(): modulated 1x1 conv without demodulation + bias, y = upsample_2d(y_prev) + t, and on
  * the last block tflib.convert_images_to_uint8(nchw_to_nhwc=True): trunc(clamp(y*127.5+128)).

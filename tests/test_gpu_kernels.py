@@ -334,3 +334,56 @@ def test_folded_up_convolution_matches_oracle(lib, mode, cin, cout, side, batch)
     assert not torch.isnan(out.float()).any(), "kernel left output unwritten"
     tol = {"bf16": 2.0 ** -5, "fp16": 2.0 ** -8}[mode]  # weights, scaled activations and output are each rounded once
     assert rel_err(out.permute(0, 3, 1, 2), want) < tol
+
+
+@pytest.mark.parametrize("mode", ["bf16", "fp16"])
+@pytest.mark.parametrize("cin,cout,side,batch,last", [(64, 64, 32, 2, False), (32, 32, 32, 3, True), (128, 128, 16, 2, False),
+                                                     (256, 256, 16, 1, False), (64, 32, 16, 2, True)])
+def test_fused_conv_torgb_matches_oracle(lib, mode, cin, cout, side, batch, last):
+    """gance_modconv3x3_torgb: Conv1 epilogue + ToRGB + skip upsample (+ uint8) against float64 arithmetic."""
+    code, dt = MODE_CODES[mode]
+    g = torch.Generator().manual_seed(21)
+    x = torch.randn(batch, cin, side, side, dtype=F64, generator=g)
+    weight = torch.randn(3, 3, cin, cout, dtype=F64, generator=g) / np.sqrt(9 * cin)
+    demod = torch.rand(batch, cout, dtype=F64, generator=g) + 0.5
+    noise = torch.randn(side, side, dtype=F64, generator=g)
+    bias = torch.randn(cout, dtype=F64, generator=g) * 0.1
+    nxt = torch.randn(batch, cout, dtype=F64, generator=g)
+    rgb_s = torch.randn(batch, cout, dtype=F64, generator=g)
+    rgb_w = torch.randn(cout, 3, dtype=F64, generator=g) / np.sqrt(cout)
+    rgb_b = torch.randn(3, dtype=F64, generator=g) * 0.1
+    y_prev = torch.randn(batch, 3, side // 2, side // 2, dtype=F64, generator=g)
+    strength = 0.07
+    x_dev = dev(x.permute(0, 2, 3, 1), dt)
+    w_dev = dev(weight.permute(3, 0, 1, 2), dt)
+    x_used = x_dev.double().cpu().permute(0, 3, 1, 2)
+    w_used = w_dev.double().cpu().permute(1, 2, 3, 0)
+    f32 = lambda t: t.float().double()  # noqa: E731
+    act = F.conv2d(x_used, w_used.permute(3, 2, 0, 1), padding=1) * f32(demod)[:, :, None, None]
+    act = act + f32(noise)[None, None] * np.float32(strength) + f32(bias)[None, :, None, None]
+    act = F.leaky_relu(act, 0.2) * np.sqrt(2.0)
+    rgb = torch.einsum("bchw,bc,cj->bjhw", act, f32(rgb_s), f32(rgb_w)) + f32(rgb_b)[None, :, None, None]
+    want_y = ref.upsample_2d(f32(y_prev)) + rgb
+    want_x = act * f32(nxt)[:, :, None, None]
+    y_prev_dev = torch.zeros(batch, side // 2, side // 2, 4, device="cuda")
+    y_prev_dev[..., :3] = dev(y_prev.permute(0, 2, 3, 1))
+    y_out = torch.full((batch, side, side, 4), float("nan"), device="cuda")
+    frames = torch.zeros(batch, side, side, 3, device="cuda", dtype=torch.uint8)
+    out = None if last else torch.full((batch, side, side, cout), float("nan"), device="cuda", dtype=dt)
+    _lib.check(
+        lib.gance_modconv3x3_torgb(x_dev.data_ptr(), code, batch, side, side, cin, cout, w_dev.data_ptr(),
+                                   dev(demod).data_ptr(), dev(noise).data_ptr(), 0, strength, dev(bias).data_ptr(),
+                                   None if last else dev(nxt).data_ptr(), None if last else out.data_ptr(),
+                                   dev(rgb_s).data_ptr(), dev(rgb_w).data_ptr(), dev(rgb_b).data_ptr(),
+                                   y_prev_dev.data_ptr(), y_out.data_ptr(), frames.data_ptr() if last else None, stream()),
+        "gance_modconv3x3_torgb",
+    )
+    torch.cuda.synchronize()
+    assert rel_err(y_out[..., :3].permute(0, 3, 1, 2), want_y) < 2e-5  # fp32 epilogue on the un-rounded activations
+    assert float(y_out[..., 3].abs().max()) == 0.0
+    if last:
+        want_u8 = ref.convert_images_to_uint8(y_out[..., :3].permute(0, 3, 1, 2).cpu())
+        assert np.array_equal(frames.cpu().numpy(), want_u8)
+    else:
+        ulp = 2.0 ** -8 if mode == "bf16" else 2.0 ** -11
+        assert rel_err(out.permute(0, 3, 1, 2), want_x) < 2 * ulp
