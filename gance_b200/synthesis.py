@@ -61,7 +61,7 @@ def _ptr(tensor: Optional[torch.Tensor]) -> Optional[int]:
 class GeneratorOnDevice:
     """One generator's weights resident in HBM in kernel layout, plus per-batch work buffers."""
 
-    def __init__(self, spec: GeneratorSpec, variables: Dict[str, np.ndarray], device: torch.device, mode: str = "bf16") -> None:
+    def __init__(self, spec: GeneratorSpec, variables: Dict[str, np.ndarray], device: torch.device, mode: str = "fp16") -> None:
         if mode not in MODES:
             raise ValueError(f"mode must be one of {sorted(MODES)}, got {mode!r}")
         if device.type != "cuda":
