@@ -25,10 +25,12 @@ namespace gance {
 
 namespace tc {
 
-constexpr int kEpilogueThreads = 128;
-constexpr int kCacheFloatsPerChannel = 6;  // demod, bias, next style, rgb weight x3
-constexpr int kCacheMaxChannels = 512;
-constexpr int kCacheBytes = kCacheFloatsPerChannel * kCacheMaxChannels * 4;
+// Per-(sample, channel) epilogue coefficients, staged in shared memory once per sample and per epilogue
+// group as float4 {demod, bias, sqrt(2) * next style, -} and, for the fused ToRGB,
+// float4 {sqrt(2) * rgb_style * rgb_weight[.,0..2], -}: one broadcast LDS.128 per channel (and one more for RGB).
+// Up to 512 channels without ToRGB, 256 with it: 8 KB per group.
+constexpr int kCacheFloat4PerGroup = 512;
+constexpr int kCacheBytes = kEpilogueGroups * kCacheFloat4PerGroup * 16;
 
 template <int N_TILE, int BLOCK_K, int STAGES>
 struct SmemLayout {
@@ -51,92 +53,106 @@ __device__ __forceinline__ TileCoord decode_tile(const ConvParams& p, int tile, 
     int tw = m % p.tiles_w;
     m /= p.tiles_w;
     int th = m % p.tiles_h;
-    int tb = m / p.tiles_h;
+    t.b0 = m / p.tiles_h;  // tile_b == 1
     t.n0 = nt * n_tile_size;
-    t.w0 = tw * p.tile_w;
+    t.w0 = tw << p.tile_w_log2;
     t.h0 = th * p.tile_h;
-    t.b0 = tb * p.tile_b;
     return t;
 }
 
-// Epilogue shared by both kernels: warps 2-5, TMEM lane quarter = warp % 4, one accumulator row (= one
-// output pixel of the tile) per thread:
-//   v = lrelu(acc * demod[b,co] + noise * strength + bias[co]) * sqrt(2)
-//   fused ToRGB (p.rgb_weight): rgb += v * (rgb_styles[b,co] * rgb_weight[co,:]) in fp32, then
+// Epilogue shared by both kernels. Two groups of four warps; group g drains TMEM accumulator buffer g, i.e. the
+// CTA's tiles g, g+2, g+4, ... (the MMA issuer alternates buffers), so the epilogue of one tile overlaps both the
+// MMAs and the epilogue of the next. Inside a group warp w owns TMEM lane quarter w % 4 and every thread one
+// accumulator row = one output pixel of the tile:
+//   v = lrelu(acc * demod[b,co] + noise * strength + bias[co])              (gain sqrt(2) folded into the consumers)
+//   fused ToRGB (RGB): rgb += v * sqrt(2) * rgb_styles[b,co] * rgb_weight[co,:] in fp32, then
 //       y = upsample_2d(y_prev) + rgb + rgb_bias -> y_out (fp32) and/or uint8 frames
-//   x_out = v * next_styles[b,co] (the next convolution's modulation) -> 16-bit NHWC store (skipped if out == NULL)
-// When a tile holds pixels of ONE sample (tile_b == 1) the per-(sample, channel) coefficients are staged in
-// shared memory once per sample instead of being fetched from L2 by every thread for every tile.
+//   x_out = v * sqrt(2) * next_styles[b,co] (the next convolution's modulation) -> 16-bit NHWC store (skipped if
+//   out == NULL)
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
 
-__device__ __forceinline__ void epilogue_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ void epilogue_bar_sync(int group) {
+    asm volatile("bar.sync %0, 128;" ::"r"(group + 1) : "memory");
+}
 
-template <typename T, int N_TILE>
-__device__ __forceinline__ void conv_epilogue(const ConvParams& p, int warp, int lane, int total_tiles,
+template <typename T, int N_TILE, bool UP, bool RGB>
+__device__ __forceinline__ void conv_epilogue(const ConvParams& p, int group, int warp, int lane, int total_tiles,
                                               uint32_t tmem_base, uint64_t* tmem_full_bar, uint64_t* tmem_empty_bar,
-                                              float* cache) {
+                                              float4* cache_all) {
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
-    const int wl = row % p.tile_w;
-    const int hl = (row / p.tile_w) % p.tile_h;
-    const int bl = row / (p.tile_w * p.tile_h);
+    const int wl = row & (p.tile_w - 1);
+    const int hl = row >> p.tile_w_log2;  // >= tile_h for the unused rows of a small-resolution tile
     const int C = p.c_real;
-    const bool use_cache = p.tile_b == 1 && C <= kCacheMaxChannels;
-    const bool fuse_rgb = p.rgb_weight != nullptr;
-    const int out_h = p.up ? 2 * p.h_out : p.h_out, out_w = p.up ? 2 * p.w_out : p.w_out;
-    float* c_demod = cache;
-    float* c_bias = cache + C;
-    float* c_style = cache + 2 * C;
-    float* c_rgb = cache + 3 * C;
+    const int out_w = UP ? 2 * p.w_out : p.w_out;
+    float4* coef_a = cache_all + group * kCacheFloat4PerGroup;
+    float4* coef_b = coef_a + C;
+    const uint32_t coef_a_addr = smem_u32(coef_a);
+    const int tid = quarter * 32 + lane;
     int cached_b = -1;
-    int acc = 0;
-    uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    uint32_t full_phase = 0;
+    float3 rgb_bias = make_float3(0.f, 0.f, 0.f);
+    if (RGB) rgb_bias = make_float3(__ldg(p.rgb_bias), __ldg(p.rgb_bias + 1), __ldg(p.rgb_bias + 2));
+    const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(group * N_TILE);
+
+    for (int tile = blockIdx.x + group * gridDim.x; tile < total_tiles; tile += kEpilogueGroups * gridDim.x) {
         const TileCoord t = decode_tile(p, tile, N_TILE);
-        const int b = t.b0 + bl, h = t.h0 + hl, w = t.w0 + wl;
-        const bool valid = b < p.batch && h < p.h_out && w < p.w_out;
-        const int bv = valid ? b : 0, hv = valid ? h : 0, wv = valid ? w : 0;
-        if (use_cache && t.b0 != cached_b) {  // CTA-uniform: all four epilogue warps work on the same tile
-            epilogue_bar_sync();              // everyone is done reading the previous sample's coefficients
-            const int tid = (warp - 2) * 32 + lane;
+        const int b = t.b0, h = t.h0 + hl, w = t.w0 + wl;
+        const bool valid = hl < p.tile_h && h < p.h_out && w < p.w_out;
+        const int hv = valid ? h : 0, wv = valid ? w : 0;
+        if (b != cached_b) {      // group-uniform
+            epilogue_bar_sync(group);  // everyone is done reading the previous sample's coefficients
             for (int i = tid; i < C; i += kEpilogueThreads) {
-                const size_t bc = (size_t)t.b0 * C + i;
-                c_demod[i] = __ldg(p.demod + bc);
-                c_bias[i] = __ldg(p.bias + i);
-                c_style[i] = p.next_styles ? __ldg(p.next_styles + bc) : 1.0f;
-                if (fuse_rgb) {
-                    const float s = __ldg(p.rgb_styles + bc);
-                    c_rgb[3 * i + 0] = s * __ldg(p.rgb_weight + 3 * i + 0);
-                    c_rgb[3 * i + 1] = s * __ldg(p.rgb_weight + 3 * i + 1);
-                    c_rgb[3 * i + 2] = s * __ldg(p.rgb_weight + 3 * i + 2);
+                const size_t bc = (size_t)b * C + i;
+                const float st = p.next_styles ? __ldg(p.next_styles + bc) : 1.0f;
+                coef_a[i] = make_float4(__ldg(p.demod + bc), __ldg(p.bias + i), st * kLreluGain, 0.f);
+                if (RGB) {
+                    const float s = __ldg(p.rgb_styles + bc) * kLreluGain;
+                    coef_b[i] = make_float4(s * __ldg(p.rgb_weight + 3 * i), s * __ldg(p.rgb_weight + 3 * i + 1),
+                                            s * __ldg(p.rgb_weight + 3 * i + 2), 0.f);
                 }
             }
-            epilogue_bar_sync();
-            cached_b = t.b0;
+            epilogue_bar_sync(group);
+            cached_b = b;
         }
-        const float* noise_b = p.noise ? p.noise + (size_t)bv * p.noise_batch_stride : nullptr;
-        // the skip-connection taps do not depend on the accumulator: fetch them while the MMAs run
+        const float* noise_b = p.noise ? p.noise + (size_t)b * p.noise_batch_stride : nullptr;
+        // everything that does not depend on the accumulator is fetched while the MMAs run
         float4 skip = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (fuse_rgb && valid && p.y_prev != nullptr) skip = upsample_tap(p.y_prev, bv, p.h_out >> 1, p.w_out >> 1, hv, wv);
-        float nz_same = 0.f;
-        if (!p.up && noise_b != nullptr) nz_same = __ldg(noise_b + (size_t)hv * out_w + wv) * p.noise_strength;
+        if (RGB && valid && p.y_prev != nullptr) skip = upsample_tap(p.y_prev, b, p.h_out >> 1, p.w_out >> 1, hv, wv);
+        float nz4[4] = {0.f, 0.f, 0.f, 0.f};
+        if (noise_b != nullptr) {
+            if (UP) {
+                const float2 top = __ldg(reinterpret_cast<const float2*>(noise_b + (size_t)(2 * hv) * out_w + 2 * wv));
+                const float2 bot = __ldg(reinterpret_cast<const float2*>(noise_b + (size_t)(2 * hv + 1) * out_w + 2 * wv));
+                nz4[0] = top.x * p.noise_strength; nz4[1] = top.y * p.noise_strength;
+                nz4[2] = bot.x * p.noise_strength; nz4[3] = bot.y * p.noise_strength;
+            } else {
+                nz4[0] = __ldg(noise_b + (size_t)hv * out_w + wv) * p.noise_strength;
+            }
+        }
         float red = 0.f, green = 0.f, blue = 0.f;
 
-        mbar_wait(tmem_full_bar + acc, acc_phase);
+        mbar_wait(tmem_full_bar + group, full_phase);
+        full_phase ^= 1u;
         tcgen05_fence_after();
-        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * N_TILE);
 #pragma unroll 1
         for (int c0 = 0; c0 < N_TILE; c0 += 32) {
             uint32_t r[32];
             tmem_ld_32x32(taddr + (uint32_t)c0, r);
             // column chunk -> (phase, first channel): a 32-column chunk never straddles a phase (c_real % 32 == 0)
             const int n = t.n0 + c0;
-            const int phase = p.up ? n / C : 0;
-            const int co0 = n - phase * C;
-            const int oh = p.up ? 2 * hv + (phase >> 1) : hv, ow = p.up ? 2 * wv + (phase & 1) : wv;
-            float nz = nz_same;
-            if (p.up && noise_b != nullptr) nz = __ldg(noise_b + (size_t)oh * out_w + ow) * p.noise_strength;
-            T* dst = p.out ? reinterpret_cast<T*>(p.out) + (((size_t)bv * out_h + oh) * out_w + ow) * C + co0 : nullptr;
-            const size_t bc = (size_t)bv * C + co0;
+            const int phase = UP ? n >> p.c_log2 : 0;
+            const int co0 = UP ? n & (C - 1) : n;
+            const int oh = UP ? 2 * hv + (phase >> 1) : hv, ow = UP ? 2 * wv + (phase & 1) : wv;
+            const float nz = UP ? nz4[phase] : nz4[0];
+            T* dst = nullptr;
+            if (p.out != nullptr)
+                dst = reinterpret_cast<T*>(p.out) + (((size_t)b * (UP ? 2 * p.h_out : p.h_out) + oh) * out_w + ow) * C + co0;
+            const uint32_t ca = coef_a_addr + (uint32_t)co0 * 16u, cb = ca + (uint32_t)C * 16u;
             tmem_ld_wait();
             if (valid) {
 #pragma unroll
@@ -144,28 +160,14 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int warp, int
                     float v[8];
 #pragma unroll
                     for (int q = 0; q < 8; ++q) {
-                        const int c = co0 + g * 8 + q;
-                        float d, bs, st;
-                        if (use_cache) {
-                            d = c_demod[c]; bs = c_bias[c]; st = c_style[c];
-                        } else {
-                            d = __ldg(p.demod + bc + g * 8 + q);
-                            bs = __ldg(p.bias + c);
-                            st = p.next_styles ? __ldg(p.next_styles + bc + g * 8 + q) : 1.0f;
+                        const float4 a = lds128(ca + (uint32_t)(g * 8 + q) * 16u);
+                        float o = fmaf(__uint_as_float(r[g * 8 + q]), a.x, nz + a.y);
+                        o = fmaxf(o, o * kLreluAlpha);
+                        if (RGB) {
+                            const float4 wv4 = lds128(cb + (uint32_t)(g * 8 + q) * 16u);
+                            red = fmaf(o, wv4.x, red); green = fmaf(o, wv4.y, green); blue = fmaf(o, wv4.z, blue);
                         }
-                        const float o = bias_lrelu(fmaf(__uint_as_float(r[g * 8 + q]), d, nz + bs));
-                        if (fuse_rgb) {
-                            float w0, w1, w2;
-                            if (use_cache) {
-                                w0 = c_rgb[3 * c]; w1 = c_rgb[3 * c + 1]; w2 = c_rgb[3 * c + 2];
-                            } else {
-                                const float s = __ldg(p.rgb_styles + bc + g * 8 + q);
-                                w0 = s * __ldg(p.rgb_weight + 3 * c); w1 = s * __ldg(p.rgb_weight + 3 * c + 1);
-                                w2 = s * __ldg(p.rgb_weight + 3 * c + 2);
-                            }
-                            red = fmaf(o, w0, red); green = fmaf(o, w1, green); blue = fmaf(o, w2, blue);
-                        }
-                        v[q] = o * st;
+                        v[q] = o * a.z;
                     }
                     if (dst != nullptr) {
                         Vec<T> packed;
@@ -177,22 +179,20 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int warp, int
         }
         tcgen05_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(tmem_empty_bar + acc);  // accumulator drained: the MMAs of tile+2 may start
-        if (fuse_rgb && valid) {
-            red += __ldg(p.rgb_bias) + skip.x; green += __ldg(p.rgb_bias + 1) + skip.y; blue += __ldg(p.rgb_bias + 2) + skip.z;
-            const size_t pixel = ((size_t)bv * p.h_out + hv) * p.w_out + wv;
+        if (lane == 0) mbar_arrive(tmem_empty_bar + group);  // accumulator drained: the MMAs of tile+2 may start
+        if (RGB && valid) {
+            red += rgb_bias.x + skip.x; green += rgb_bias.y + skip.y; blue += rgb_bias.z + skip.z;
+            const size_t pixel = ((size_t)b * p.h_out + hv) * p.w_out + wv;
             if (p.y_out != nullptr) reinterpret_cast<float4*>(p.y_out)[pixel] = make_float4(red, green, blue, 0.f);
             if (p.frames != nullptr) {
                 uint8_t* f = p.frames + pixel * 3;
                 f[0] = to_u8(red); f[1] = to_u8(green); f[2] = to_u8(blue);
             }
         }
-        acc ^= 1;
-        if (acc == 0) acc_phase ^= 1u;
     }
 }
 
-template <typename T, int N_TILE, int BLOCK_K, int STAGES>
+template <typename T, int N_TILE, int BLOCK_K, int STAGES, bool UP, bool RGB>
 __global__ void __launch_bounds__(kThreads, 1)
 modconv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
                      const ConvParams p) {
@@ -248,7 +248,7 @@ modconv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                         mbar_wait(empty_bar + stage, phase ^ 1u);
                         uint8_t* a_dst = smem + stage * L::kStageBytes;
                         uint8_t* b_dst = a_dst + L::kABytes;
-                        mbar_expect_tx(full_bar + stage, L::kStageBytes);
+                        mbar_expect_tx(full_bar + stage, (uint32_t)p.a_tx_bytes + L::kBBytes);
                         tma_load_4d(a_dst, &tmap_x, full_bar + stage, kc * BLOCK_K, t.w0 + dx, t.h0 + dy, t.b0);
                         tma_load_2d(b_dst, &tmap_w, full_bar + stage, tap * p.c_in + kc * BLOCK_K, t.n0);
                         if (++stage == STAGES) {
@@ -295,8 +295,8 @@ modconv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             }
         }
     } else {
-        conv_epilogue<T, N_TILE>(p, warp, lane, total_tiles, tmem_base, tmem_full_bar, tmem_empty_bar,
-                                 reinterpret_cast<float*>(smem + L::kCacheOffset));
+        conv_epilogue<T, N_TILE, UP, RGB>(p, (warp - 2) >> 2, warp, lane, total_tiles, tmem_base, tmem_full_bar,
+                                          tmem_empty_bar, reinterpret_cast<float4*>(smem + L::kCacheOffset));
     }
 
     tcgen05_fence_before();
@@ -331,7 +331,7 @@ struct HaloSmem {
     static constexpr int kHaloBytes = kHaloH * kHaloW * kRowBytes;
     static constexpr int kHaloStride = (kHaloBytes + 1023) / 1024 * 1024;
     static constexpr int kBarrierOffset = kWeightBytes + STAGES * kHaloStride;
-    static constexpr int kCacheOffset = kBarrierOffset + (2 * STAGES + 5) * 8 + 16;
+    static constexpr int kCacheOffset = kBarrierOffset + ((2 * STAGES + 5) * 8 + 16 + 15) / 16 * 16;
     static constexpr int kBytes = kCacheOffset + kCacheBytes + 1024;
 };
 
@@ -342,7 +342,7 @@ __device__ __forceinline__ uint64_t make_smem_desc_sbo(uint32_t smem_addr, uint3
            (layout << 61);
 }
 
-template <typename T, int N_GEMM, int CIN, int STAGES>
+template <typename T, int N_GEMM, int CIN, int STAGES, bool UP, bool RGB>
 __global__ void __launch_bounds__(kThreads, 1)
 modconv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
                        const ConvParams p) {
@@ -440,8 +440,8 @@ modconv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_
             }
         }
     } else {
-        conv_epilogue<T, N_GEMM>(p, warp, lane, total_tiles, tmem_base, tmem_full_bar, tmem_empty_bar,
-                                 reinterpret_cast<float*>(smem + L::kCacheOffset));
+        conv_epilogue<T, N_GEMM, UP, RGB>(p, (warp - 2) >> 2, warp, lane, total_tiles, tmem_base, tmem_full_bar,
+                                          tmem_empty_bar, reinterpret_cast<float4*>(smem + L::kCacheOffset));
     }
 
     tcgen05_fence_before();
@@ -459,22 +459,25 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
 static EncodeTiledFn g_encode_tiled = nullptr;
 static int g_num_sms = 148;
 
-template <typename T, int N_TILE, int BLOCK_K, int STAGES>
-static int configure_one() {
-    using L = SmemLayout<N_TILE, BLOCK_K, STAGES>;
-    cudaError_t err = cudaFuncSetAttribute(modconv3x3_tc_kernel<T, N_TILE, BLOCK_K, STAGES>,
-                                           cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes);
+template <typename K>
+static int raise_smem_limit(K kernel, int bytes, const char* what) {
+    cudaError_t err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
     if (err != cudaSuccess)
-        return fail(-(int)err, "cudaFuncSetAttribute(modconv3x3_tc<%d,%d,%d>, %d B): %s", N_TILE, BLOCK_K, STAGES,
-                    L::kBytes, cudaGetErrorString(err));
+        return fail(-(int)err, "cudaFuncSetAttribute(%s, %d B): %s", what, bytes, cudaGetErrorString(err));
     return GANCE_OK;
 }
 
+// Every (operand type, epilogue flavour) instance of one tile configuration: plain, folded up-convolution, fused ToRGB.
 template <int N_TILE, int BLOCK_K, int STAGES>
 static int configure() {
-    int rc = configure_one<__nv_bfloat16, N_TILE, BLOCK_K, STAGES>();
-    if (rc != GANCE_OK) return rc;
-    return configure_one<__half, N_TILE, BLOCK_K, STAGES>();
+    using L = SmemLayout<N_TILE, BLOCK_K, STAGES>;
+    int rc;
+    if ((rc = raise_smem_limit(modconv3x3_tc_kernel<__nv_bfloat16, N_TILE, BLOCK_K, STAGES, false, false>, L::kBytes, "modconv3x3_tc")) != GANCE_OK) return rc;
+    if ((rc = raise_smem_limit(modconv3x3_tc_kernel<__half, N_TILE, BLOCK_K, STAGES, false, false>, L::kBytes, "modconv3x3_tc")) != GANCE_OK) return rc;
+    if ((rc = raise_smem_limit(modconv3x3_tc_kernel<__nv_bfloat16, N_TILE, BLOCK_K, STAGES, true, false>, L::kBytes, "modconv3x3_tc<up>")) != GANCE_OK) return rc;
+    if ((rc = raise_smem_limit(modconv3x3_tc_kernel<__half, N_TILE, BLOCK_K, STAGES, true, false>, L::kBytes, "modconv3x3_tc<up>")) != GANCE_OK) return rc;
+    if ((rc = raise_smem_limit(modconv3x3_tc_kernel<__nv_bfloat16, N_TILE, BLOCK_K, STAGES, false, true>, L::kBytes, "modconv3x3_tc<rgb>")) != GANCE_OK) return rc;
+    return raise_smem_limit(modconv3x3_tc_kernel<__half, N_TILE, BLOCK_K, STAGES, false, true>, L::kBytes, "modconv3x3_tc<rgb>");
 }
 
 static int make_tmap(CUtensorMap* map, const void* base, bool half_operands, int rank, const cuuint64_t* dims,
@@ -501,7 +504,7 @@ static int launch_typed(const ConvParams& p, const void* x, const void* weight, 
         cuuint64_t dims[4] = {(cuuint64_t)p.c_in, (cuuint64_t)w_in, (cuuint64_t)h_in, (cuuint64_t)p.batch};
         cuuint64_t strides[3] = {(cuuint64_t)p.c_in * 2, (cuuint64_t)w_in * p.c_in * 2,
                                  (cuuint64_t)h_in * w_in * p.c_in * 2};
-        cuuint32_t box[4] = {(cuuint32_t)BLOCK_K, (cuuint32_t)p.tile_w, (cuuint32_t)p.tile_h, (cuuint32_t)p.tile_b};
+        cuuint32_t box[4] = {(cuuint32_t)BLOCK_K, (cuuint32_t)p.tile_w, (cuuint32_t)p.tile_h, 1u};
         int rc = make_tmap(&tmap_x, x, kHalf, 4, dims, strides, box, BLOCK_K * 2);
         if (rc != GANCE_OK) return rc;
     }
@@ -512,9 +515,16 @@ static int launch_typed(const ConvParams& p, const void* x, const void* weight, 
         int rc = make_tmap(&tmap_w, weight, kHalf, 2, dims, strides, box, BLOCK_K * 2);
         if (rc != GANCE_OK) return rc;
     }
+    ConvParams q = p;
+    q.a_tx_bytes = p.tile_w * p.tile_h * BLOCK_K * 2;
     const int total_tiles = p.tiles_b * p.tiles_h * p.tiles_w * p.n_tiles;
     const int grid = total_tiles < g_num_sms ? total_tiles : g_num_sms;
-    modconv3x3_tc_kernel<T, N_TILE, BLOCK_K, STAGES><<<grid, kThreads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
+    if (p.rgb_weight != nullptr)
+        modconv3x3_tc_kernel<T, N_TILE, BLOCK_K, STAGES, false, true><<<grid, kThreads, L::kBytes, stream>>>(tmap_x, tmap_w, q);
+    else if (p.up)
+        modconv3x3_tc_kernel<T, N_TILE, BLOCK_K, STAGES, true, false><<<grid, kThreads, L::kBytes, stream>>>(tmap_x, tmap_w, q);
+    else
+        modconv3x3_tc_kernel<T, N_TILE, BLOCK_K, STAGES, false, false><<<grid, kThreads, L::kBytes, stream>>>(tmap_x, tmap_w, q);
     return check_launch("modconv3x3_tc_kernel");
 }
 
@@ -525,6 +535,8 @@ static int launch(bool half_operands, const ConvParams& p, const void* x, const 
     return launch_typed<__nv_bfloat16, N_TILE, BLOCK_K, STAGES>(p, x, weight, h_in, w_in, stream);
 }
 
+// The halo instances that exist: <N_GEMM, CIN> = <128,64> is the folded 1024^2 up-convolution (and plain 64->128),
+// <64,64> the 512^2 Conv1 (plain / fused ToRGB), <32,32> the 1024^2 Conv1 (plain / fused ToRGB).
 template <typename T, int N_GEMM, int CIN, int STAGES>
 static int launch_halo_typed(const ConvParams& p, const void* x, const void* weight, cudaStream_t stream) {
     using L = HaloSmem<N_GEMM, CIN, STAGES>;
@@ -546,7 +558,12 @@ static int launch_halo_typed(const ConvParams& p, const void* x, const void* wei
     }
     const int total_tiles = p.tiles_b * p.tiles_h * p.tiles_w;
     const int grid = total_tiles < g_num_sms ? total_tiles : g_num_sms;
-    modconv3x3_halo_kernel<T, N_GEMM, CIN, STAGES><<<grid, kThreads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
+    if (p.rgb_weight != nullptr)
+        modconv3x3_halo_kernel<T, N_GEMM, CIN, STAGES, false, true><<<grid, kThreads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
+    else if (p.up)
+        modconv3x3_halo_kernel<T, N_GEMM, CIN, STAGES, true, false><<<grid, kThreads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
+    else
+        modconv3x3_halo_kernel<T, N_GEMM, CIN, STAGES, false, false><<<grid, kThreads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
     return check_launch("modconv3x3_halo_kernel");
 }
 
@@ -559,15 +576,13 @@ static int launch_halo(bool half_operands, const ConvParams& p, const void* x, c
 template <int N_GEMM, int CIN, int STAGES>
 static int configure_halo() {
     using L = HaloSmem<N_GEMM, CIN, STAGES>;
-    cudaError_t err = cudaFuncSetAttribute(modconv3x3_halo_kernel<__nv_bfloat16, N_GEMM, CIN, STAGES>,
-                                           cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes);
-    if (err == cudaSuccess)
-        err = cudaFuncSetAttribute(modconv3x3_halo_kernel<__half, N_GEMM, CIN, STAGES>,
-                                   cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes);
-    if (err != cudaSuccess)
-        return fail(-(int)err, "cudaFuncSetAttribute(modconv3x3_halo<%d,%d,%d>, %d B): %s", N_GEMM, CIN, STAGES, L::kBytes,
-                    cudaGetErrorString(err));
-    return GANCE_OK;
+    int rc;
+    if ((rc = raise_smem_limit(modconv3x3_halo_kernel<__nv_bfloat16, N_GEMM, CIN, STAGES, false, false>, L::kBytes, "modconv3x3_halo")) != GANCE_OK) return rc;
+    if ((rc = raise_smem_limit(modconv3x3_halo_kernel<__half, N_GEMM, CIN, STAGES, false, false>, L::kBytes, "modconv3x3_halo")) != GANCE_OK) return rc;
+    if ((rc = raise_smem_limit(modconv3x3_halo_kernel<__nv_bfloat16, N_GEMM, CIN, STAGES, true, false>, L::kBytes, "modconv3x3_halo<up>")) != GANCE_OK) return rc;
+    if ((rc = raise_smem_limit(modconv3x3_halo_kernel<__half, N_GEMM, CIN, STAGES, true, false>, L::kBytes, "modconv3x3_halo<up>")) != GANCE_OK) return rc;
+    if ((rc = raise_smem_limit(modconv3x3_halo_kernel<__nv_bfloat16, N_GEMM, CIN, STAGES, false, true>, L::kBytes, "modconv3x3_halo<rgb>")) != GANCE_OK) return rc;
+    return raise_smem_limit(modconv3x3_halo_kernel<__half, N_GEMM, CIN, STAGES, false, true>, L::kBytes, "modconv3x3_halo<rgb>");
 }
 
 static bool g_use_halo = true;
@@ -634,16 +649,24 @@ static int launch_tensor_core_conv(const char* who, const void* x, int dtype, in
     tc::ConvParams p;
     p.batch = batch; p.h_out = h_out; p.w_out = w_out; p.c_in = c_in; p.c_out = c_out; p.pad = pad;
     p.up = up; p.c_real = c_real;
-    // 128 output pixels per tile: as wide as the image allows (<= 16), then rows, then samples.
+    // One tile = up to 128 output pixels of ONE sample: as wide as the image allows (<= 16), then rows. Resolutions
+    // below 16x8 leave accumulator rows unused (4x4: 16 of 128) - those layers are a rounding error of the frame time,
+    // and one sample per tile is what lets the epilogue stage its coefficients in shared memory.
+    auto is_pow2 = [](int v) { return v > 0 && (v & (v - 1)) == 0; };
+    auto ilog2 = [](int v) { int l = 0; while ((1 << l) < v) ++l; return l; };
     p.tile_w = w_out >= 16 ? 16 : w_out;
-    GANCE_REQUIRE((p.tile_w & (p.tile_w - 1)) == 0, GANCE_E_SHAPE, "%s: W=%d (< 16) must be a power of two", who, w_out);
-    int rows = tc::kTileM / p.tile_w;
+    GANCE_REQUIRE(is_pow2(p.tile_w), GANCE_E_SHAPE, "%s: W=%d (< 16) must be a power of two", who, w_out);
+    const int rows = tc::kTileM / p.tile_w;
     p.tile_h = h_out >= rows ? rows : h_out;
-    GANCE_REQUIRE(rows % p.tile_h == 0, GANCE_E_SHAPE, "%s: H=%d does not tile 128 pixels", who, h_out);
-    p.tile_b = rows / p.tile_h;
+    GANCE_REQUIRE(is_pow2(p.tile_h), GANCE_E_SHAPE, "%s: H=%d (< %d) must be a power of two", who, h_out, rows);
+    GANCE_REQUIRE(is_pow2(c_real) && c_real <= tc::kCacheFloat4PerGroup / (rgb ? 2 : 1), GANCE_E_SHAPE,
+                  "%s: Cout=%d must be a power of two <= %d", who, c_real, tc::kCacheFloat4PerGroup / (rgb ? 2 : 1));
+    p.tile_b = 1;
     p.tiles_w = (w_out + p.tile_w - 1) / p.tile_w;
     p.tiles_h = (h_out + p.tile_h - 1) / p.tile_h;
-    p.tiles_b = (batch + p.tile_b - 1) / p.tile_b;
+    p.tiles_b = batch;
+    p.tile_w_log2 = ilog2(p.tile_w); p.tile_hw_log2 = ilog2(p.tile_w * p.tile_h); p.c_log2 = ilog2(c_real);
+    p.a_tx_bytes = 0;  // set per instantiation (depends on BLOCK_K)
     p.demod = demod; p.noise = noise; p.noise_batch_stride = noise_batch_stride; p.noise_strength = noise_strength;
     p.bias = bias; p.next_styles = next_styles; p.out = out;
     p.rgb_styles = rgb ? rgb->styles : nullptr; p.rgb_weight = rgb ? rgb->weight : nullptr;
@@ -659,6 +682,7 @@ static int launch_tensor_core_conv(const char* who, const void* x, int dtype, in
     if (tc::g_use_halo && pad == 1 && w_out % tc::kHaloTileW == 0 && h_out % tc::kHaloTileH == 0 &&
         ((c_in == 64 && (c_out == 128 || c_out == 64)) || (c_in == 32 && c_out == 32))) {
         p.tile_w = tc::kHaloTileW; p.tile_h = tc::kHaloTileH; p.tile_b = 1;
+        p.tile_w_log2 = ilog2(p.tile_w); p.tile_hw_log2 = ilog2(p.tile_w * p.tile_h);
         p.tiles_w = w_out / p.tile_w; p.tiles_h = h_out / p.tile_h; p.tiles_b = batch;
         p.n_tiles = 1; p.k_chunks = 1;
         if (c_in == 32) return tc::launch_halo<32, 32, 4>(half_operands, p, x, weight, s);

@@ -11,12 +11,17 @@ namespace gance {
 namespace tc {
 
 constexpr int kTileM = 128;
-constexpr int kThreads = 192;
+constexpr int kEpilogueGroups = 2;     // two epilogue warpgroups, one per TMEM accumulator buffer
+constexpr int kEpilogueThreads = 128;  // per group: one thread per accumulator row
+constexpr int kThreads = 64 + kEpilogueGroups * kEpilogueThreads;  // + TMA producer warp + MMA issuer warp
 constexpr int kUmmaK = 16;  // bf16
 
 struct ConvParams {
     int batch, h_out, w_out, c_in, c_out, pad;
-    int tile_w, tile_h, tile_b;      // tile_w * tile_h * tile_b == 128 output pixels
+    int tile_w, tile_h, tile_b;      // powers of two; tile_b == 1; tile_w * tile_h <= 128 accumulator rows are valid
+    int tile_w_log2, tile_hw_log2;   // log2(tile_w), log2(tile_w * tile_h)
+    int c_log2;                      // log2(c_real)
+    int a_tx_bytes;                  // bytes one A-tile TMA box delivers (tile_w * tile_h * BLOCK_K * 2)
     int tiles_w, tiles_h, tiles_b;   // m-tiles per dimension
     int n_tiles;                     // c_out / N_TILE
     int k_chunks;                    // c_in / BLOCK_K
