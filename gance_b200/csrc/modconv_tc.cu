@@ -79,7 +79,7 @@ __device__ __forceinline__ void epilogue_bar_sync(int group) {
     asm volatile("bar.sync %0, 128;" ::"r"(group + 1) : "memory");
 }
 
-template <typename T, int N_TILE, bool UP, bool RGB>
+template <typename T, int N_TILE, bool UP, bool RGB, int GROUPS, int CACHE_F4>
 __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int group, int warp, int lane, int total_tiles,
                                               uint32_t tmem_base, uint64_t* tmem_full_bar, uint64_t* tmem_empty_bar,
                                               float4* cache_all) {
@@ -89,7 +89,7 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int group, in
     const int hl = row >> p.tile_w_log2;  // >= tile_h for the unused rows of a small-resolution tile
     const int C = p.c_real;
     const int out_w = UP ? 2 * p.w_out : p.w_out;
-    float4* coef_a = cache_all + group * kCacheFloat4PerGroup;
+    float4* coef_a = cache_all + group * CACHE_F4;
     float4* coef_b = coef_a + C;
     const uint32_t coef_a_addr = smem_u32(coef_a);
     const int tid = quarter * 32 + lane;
@@ -99,7 +99,7 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int group, in
     if (RGB) rgb_bias = make_float3(__ldg(p.rgb_bias), __ldg(p.rgb_bias + 1), __ldg(p.rgb_bias + 2));
     const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(group * N_TILE);
 
-    for (int tile = blockIdx.x + group * gridDim.x; tile < total_tiles; tile += kEpilogueGroups * gridDim.x) {
+    for (int tile = blockIdx.x + group * gridDim.x; tile < total_tiles; tile += GROUPS * gridDim.x) {
         const TileCoord t = decode_tile(p, tile, N_TILE);
         const int b = t.b0, h = t.h0 + hl, w = t.w0 + wl;
         const bool valid = hl < p.tile_h && h < p.h_out && w < p.w_out;
@@ -192,6 +192,176 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int group, in
     }
 }
 
+__device__ __forceinline__ void store_pair(__half* dst, float a, float b) {
+    *reinterpret_cast<__half2*>(dst) = __floats2half2_rn(a, b);
+}
+__device__ __forceinline__ void store_pair(__nv_bfloat16* dst, float a, float b) {
+    *reinterpret_cast<__nv_bfloat162*>(dst) = __floats2bfloat162_rn(a, b);
+}
+
+// ---- epilogue of the halo kernels: accumulators read in the mma-fragment layout ------------------------------------
+// With one accumulator row per thread (conv_epilogue above) every coefficient is a warp-wide broadcast load from
+// shared memory; at 32-64 channels a tile is only 18-36 tensor-core instructions long and those broadcasts (4 LSU
+// wavefronts per LDS.128) outlast the MMAs several times over (ncu, round 1: 1017 wavefronts per 288-cycle tile).
+// tcgen05.ld.16x256b hands each thread 4 pixels x C/4 channels instead, so a thread needs the coefficients of only
+// C/4 <= 16 channels and keeps them in REGISTERS for as long as the CTA stays on one sample: the inner loop has no
+// memory instruction at all. Thread t of warp quarter Q owns
+//   rows   Q*32 + 16*h2 + 8*s + t/4          (h2, s in {0,1}; "rr" = 2*h2 + s)
+//   channels 32*chunk + 8*j + 2*(t%4) + e    (j in 0..3, e in {0,1})
+// The ToRGB sum over channels is finished with a two-step reduce-scatter over the four lanes that share a row
+// (9 shuffles), which leaves row rr on lane t%4 == rr: every lane then adds the skip connection for ONE pixel.
+template <typename T, int N_TILE, int C, bool UP, bool RGB, int GROUPS>
+__device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int group, int warp, int lane, int total_tiles,
+                                                   uint32_t tmem_base, uint64_t* tmem_full_bar,
+                                                   uint64_t* tmem_empty_bar) {
+    static_assert(C % 32 == 0 && C <= 64, "register-resident coefficients: at most 16 channels per thread");
+    static_assert(N_TILE == (UP ? 4 * C : C), "GEMM columns = channels (x 4 phases for the folded up-convolution)");
+    constexpr int CPT = C / 4;           // channels per thread
+    constexpr int CHUNKS = N_TILE / 32;  // 32-column accumulator chunks per tile
+    const int quarter = warp & 3;
+    const int q4 = lane & 3, r8 = lane >> 2;
+    const int out_w = UP ? 2 * p.w_out : p.w_out, out_h = UP ? 2 * p.h_out : p.h_out;
+    const bool has_out = p.out != nullptr;
+
+    float cd[CPT], cb[CPT], cs[CPT], cw0[CPT], cw1[CPT], cw2[CPT];
+    float3 rgb_bias = make_float3(0.f, 0.f, 0.f);
+    if (RGB) rgb_bias = make_float3(__ldg(p.rgb_bias), __ldg(p.rgb_bias + 1), __ldg(p.rgb_bias + 2));
+    // tile-local pixel of each of this thread's rows (the tile is tile_w x tile_h pixels, w fastest)
+    int wl[4], hl[4];
+#pragma unroll
+    for (int rr = 0; rr < 4; ++rr) {
+        const int row = quarter * 32 + 16 * (rr >> 1) + 8 * (rr & 1) + r8;
+        wl[rr] = row & (p.tile_w - 1);
+        hl[rr] = row >> p.tile_w_log2;
+    }
+    int cached_b = -1;
+    uint32_t full_phase = 0;
+
+    for (int tile = blockIdx.x + group * gridDim.x; tile < total_tiles; tile += GROUPS * gridDim.x) {
+        const TileCoord t = decode_tile(p, tile, N_TILE);
+        const int b = t.b0;
+        if (b != cached_b) {  // per-sample coefficients of this thread's channels -> registers
+#pragma unroll
+            for (int k = 0; k < CPT; ++k) {
+                const int ch = (k >> 3) * 32 + ((k >> 1) & 3) * 8 + 2 * q4 + (k & 1);
+                const size_t bc = (size_t)b * C + ch;
+                cd[k] = __ldg(p.demod + bc);
+                cb[k] = __ldg(p.bias + ch);
+                cs[k] = (p.next_styles ? __ldg(p.next_styles + bc) : 1.0f) * kLreluGain;
+                if (RGB) {
+                    const float s = __ldg(p.rgb_styles + bc) * kLreluGain;
+                    cw0[k] = s * __ldg(p.rgb_weight + 3 * ch);
+                    cw1[k] = s * __ldg(p.rgb_weight + 3 * ch + 1);
+                    cw2[k] = s * __ldg(p.rgb_weight + 3 * ch + 2);
+                }
+            }
+            cached_b = b;
+        }
+        // everything that does not depend on the accumulator is fetched while the MMAs run
+        const float* noise_b = p.noise ? p.noise + (size_t)b * p.noise_batch_stride : nullptr;
+        constexpr int NP = UP ? 4 : 1;  // noise values per input pixel
+        float nz[4][NP];
+#pragma unroll
+        for (int rr = 0; rr < 4; ++rr) {
+            const int h = t.h0 + hl[rr], w = t.w0 + wl[rr];
+            if (UP) {
+                float2 top = make_float2(0.f, 0.f), bot = top;
+                if (noise_b != nullptr) {
+                    top = __ldg(reinterpret_cast<const float2*>(noise_b + (size_t)(2 * h) * out_w + 2 * w));
+                    bot = __ldg(reinterpret_cast<const float2*>(noise_b + (size_t)(2 * h + 1) * out_w + 2 * w));
+                }
+                nz[rr][0] = top.x * p.noise_strength; nz[rr][1 % NP] = top.y * p.noise_strength;
+                nz[rr][2 % NP] = bot.x * p.noise_strength; nz[rr][3 % NP] = bot.y * p.noise_strength;
+            } else {
+                nz[rr][0] = noise_b ? __ldg(noise_b + (size_t)h * out_w + w) * p.noise_strength : 0.f;
+            }
+        }
+        float4 skip = make_float4(0.f, 0.f, 0.f, 0.f);
+        int own_h = 0, own_wp = 0;
+        if (RGB) {  // this lane finishes the pixel of row rr == q4
+            own_h = t.h0 + (q4 == 0 ? hl[0] : q4 == 1 ? hl[1] : q4 == 2 ? hl[2] : hl[3]);
+            own_wp = t.w0 + (q4 == 0 ? wl[0] : q4 == 1 ? wl[1] : q4 == 2 ? wl[2] : wl[3]);
+            if (p.y_prev != nullptr) skip = upsample_tap(p.y_prev, b, p.h_out >> 1, p.w_out >> 1, own_h, own_wp);
+        }
+        float rgb[4][3];
+#pragma unroll
+        for (int rr = 0; rr < 4; ++rr) rgb[rr][0] = rgb[rr][1] = rgb[rr][2] = 0.f;
+
+        mbar_wait(tmem_full_bar + group, full_phase);
+        full_phase ^= 1u;
+        tcgen05_fence_after();
+#pragma unroll
+        for (int chunk = 0; chunk < CHUNKS; ++chunk) {
+            const int phase = UP ? (chunk * 32) / C : 0;
+            const int kbase = ((chunk * 32) % C) / 4;  // first of this thread's channels inside the chunk
+#pragma unroll
+            for (int h2 = 0; h2 < 2; ++h2) {
+                uint32_t r[16];
+                tmem_ld_16x256b_x4(tmem_base + ((uint32_t)(quarter * 32 + 16 * h2) << 16) +
+                                       (uint32_t)(group * N_TILE + chunk * 32), r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int s = 0; s < 2; ++s) {
+                    const int rr = 2 * h2 + s;
+                    const float nzv = nz[rr][UP ? phase : 0];
+                    float v[8];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            const int k = kbase + 2 * j + e;
+                            float o = fmaf(__uint_as_float(r[4 * j + 2 * s + e]), cd[k], nzv + cb[k]);
+                            o = fmaxf(o, o * kLreluAlpha);
+                            if (RGB) {
+                                rgb[rr][0] = fmaf(o, cw0[k], rgb[rr][0]);
+                                rgb[rr][1] = fmaf(o, cw1[k], rgb[rr][1]);
+                                rgb[rr][2] = fmaf(o, cw2[k], rgb[rr][2]);
+                            }
+                            v[2 * j + e] = o * cs[k];
+                        }
+                    }
+                    if (has_out) {
+                        const int h = t.h0 + hl[rr], w = t.w0 + wl[rr];
+                        const int oh = UP ? 2 * h + (phase >> 1) : h, ow = UP ? 2 * w + (phase & 1) : w;
+                        T* dst = reinterpret_cast<T*>(p.out) + (((size_t)b * out_h + oh) * out_w + ow) * C +
+                                 ((chunk * 32) % C) + 2 * q4;
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) store_pair(dst + 8 * j, v[2 * j], v[2 * j + 1]);
+                    }
+                }
+            }
+        }
+        tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tmem_empty_bar + group);  // accumulator drained
+        if (RGB) {
+            // reduce-scatter over the 4 lanes of a row group: xor 1 settles s, xor 2 settles h2
+            float keep[2][3], mine[3];
+            const bool s_own = (q4 & 1) != 0, h_own = (q4 & 2) != 0;
+#pragma unroll
+            for (int h2 = 0; h2 < 2; ++h2)
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    const float send = s_own ? rgb[2 * h2][c] : rgb[2 * h2 + 1][c];
+                    keep[h2][c] = (s_own ? rgb[2 * h2 + 1][c] : rgb[2 * h2][c]) + __shfl_xor_sync(0xffffffffu, send, 1);
+                }
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                const float send = h_own ? keep[0][c] : keep[1][c];
+                mine[c] = (h_own ? keep[1][c] : keep[0][c]) + __shfl_xor_sync(0xffffffffu, send, 2);
+            }
+            const float red = mine[0] + rgb_bias.x + skip.x, green = mine[1] + rgb_bias.y + skip.y,
+                        blue = mine[2] + rgb_bias.z + skip.z;
+            const size_t pixel = ((size_t)b * p.h_out + own_h) * p.w_out + own_wp;
+            if (p.y_out != nullptr) reinterpret_cast<float4*>(p.y_out)[pixel] = make_float4(red, green, blue, 0.f);
+            if (p.frames != nullptr) {
+                uint8_t* f = p.frames + pixel * 3;
+                f[0] = to_u8(red); f[1] = to_u8(green); f[2] = to_u8(blue);
+            }
+        }
+    }
+}
+
 template <typename T, int N_TILE, int BLOCK_K, int STAGES, bool UP, bool RGB>
 __global__ void __launch_bounds__(kThreads, 1)
 modconv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
@@ -210,7 +380,7 @@ modconv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
     uint64_t* tmem_empty_bar = tmem_full_bar + 2;
     uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
 
-    const int warp = threadIdx.x >> 5;
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // shfl result = provably warp-uniform
     const int lane = threadIdx.x & 31;
 
     if (warp == 0 && lane == 0) {
@@ -230,13 +400,17 @@ modconv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
     tcgen05_fence_before();
     __syncthreads();
     tcgen05_fence_after();
-    const uint32_t tmem_base = *tmem_base_slot;
+    const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_base_slot, 0);
 
     const int total_tiles = p.tiles_b * p.tiles_h * p.tiles_w * p.n_tiles;
     const int k_iters = 9 * p.k_chunks;
 
+    // Producer and MMA warps run their loops with all 32 lanes converged and elect one lane only around the
+    // asynchronous instructions: every operand is then warp-uniform for the compiler (uniform registers, no
+    // per-instruction R2UR "waterfall" loop - which cost ~130 cycles per tcgen05.mma in the first version).
     if (warp == 0) {
-        if (lane == 0) {
+        const bool leader = elect_one_sync();
+        {
             // ===== TMA producer =====
             int stage = 0;
             uint32_t phase = 0;
@@ -248,9 +422,12 @@ modconv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                         mbar_wait(empty_bar + stage, phase ^ 1u);
                         uint8_t* a_dst = smem + stage * L::kStageBytes;
                         uint8_t* b_dst = a_dst + L::kABytes;
-                        mbar_expect_tx(full_bar + stage, (uint32_t)p.a_tx_bytes + L::kBBytes);
-                        tma_load_4d(a_dst, &tmap_x, full_bar + stage, kc * BLOCK_K, t.w0 + dx, t.h0 + dy, t.b0);
-                        tma_load_2d(b_dst, &tmap_w, full_bar + stage, tap * p.c_in + kc * BLOCK_K, t.n0);
+                        if (leader) {
+                            mbar_expect_tx(full_bar + stage, (uint32_t)p.a_tx_bytes + L::kBBytes);
+                            tma_load_4d(a_dst, &tmap_x, full_bar + stage, kc * BLOCK_K, t.w0 + dx, t.h0 + dy, t.b0);
+                            tma_load_2d(b_dst, &tmap_w, full_bar + stage, tap * p.c_in + kc * BLOCK_K, t.n0);
+                        }
+                        __syncwarp();
                         if (++stage == STAGES) {
                             stage = 0;
                             phase ^= 1u;
@@ -260,13 +437,15 @@ modconv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        const bool leader = elect_one_sync();
+        {
             // ===== MMA issuer =====
             constexpr uint32_t idesc = make_instr_desc(kTileM, N_TILE, sizeof(T) == 2 && !std::is_same<T, __nv_bfloat16>::value);
             int stage = 0;
             uint32_t phase = 0;
             int acc = 0;
             uint32_t acc_phase = 0;
+            const uint32_t smem_base = smem_u32(smem);
             for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
                 mbar_wait(tmem_empty_bar + acc, acc_phase ^ 1u);  // epilogue has drained this accumulator
                 tcgen05_fence_after();
@@ -274,17 +453,20 @@ modconv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                 for (int it = 0; it < k_iters; ++it) {
                     mbar_wait(full_bar + stage, phase);  // TMA bytes have landed
                     tcgen05_fence_after();
-                    const uint32_t a_addr = smem_u32(smem + stage * L::kStageBytes);
+                    const uint32_t a_addr = smem_base + (uint32_t)(stage * L::kStageBytes);
                     const uint64_t a_desc = make_smem_desc<kSwizzle>(a_addr);
-                    const uint64_t b_desc = make_smem_desc<kSwizzle>(a_addr + L::kABytes);
+                    const uint64_t b_desc = a_desc + (uint64_t)(L::kABytes >> 4);
+                    if (leader) {
 #pragma unroll
-                    for (int k = 0; k < BLOCK_K / kUmmaK; ++k) {
-                        // advance along K inside the swizzle atom: +32 bytes = +2 in the >>4 address field
-                        umma_bf16(d_tmem, a_desc + (uint64_t)(k * 2), b_desc + (uint64_t)(k * 2), idesc,
-                                  (it | k) != 0 ? 1u : 0u);
+                        for (int k = 0; k < BLOCK_K / kUmmaK; ++k) {
+                            // advance along K inside the swizzle atom: +32 bytes = +2 in the >>4 address field
+                            umma_bf16(d_tmem, a_desc + (uint64_t)(k * 2), b_desc + (uint64_t)(k * 2), idesc,
+                                      (it | k) != 0 ? 1u : 0u);
+                        }
+                        umma_commit(empty_bar + stage);  // frees the smem slot when these MMAs retire
+                        if (it == k_iters - 1) umma_commit(tmem_full_bar + acc);
                     }
-                    umma_commit(empty_bar + stage);  // frees the smem slot when these MMAs retire
-                    if (it == k_iters - 1) umma_commit(tmem_full_bar + acc);
+                    __syncwarp();
                     if (++stage == STAGES) {
                         stage = 0;
                         phase ^= 1u;
@@ -295,7 +477,7 @@ modconv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             }
         }
     } else {
-        conv_epilogue<T, N_TILE, UP, RGB>(p, (warp - 2) >> 2, warp, lane, total_tiles, tmem_base, tmem_full_bar,
+        conv_epilogue<T, N_TILE, UP, RGB, kEpilogueGroups, kCacheFloat4PerGroup>(p, (warp - 2) >> 2, warp, lane, total_tiles, tmem_base, tmem_full_bar,
                                           tmem_empty_bar, reinterpret_cast<float4*>(smem + L::kCacheOffset));
     }
 
@@ -323,6 +505,11 @@ modconv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
 // ====================================================================================================
 constexpr int kHaloTileW = 8, kHaloTileH = 16;
 constexpr int kHaloW = kHaloTileW + 2, kHaloH = kHaloTileH + 2;
+// A tile of these layers is 18-36 tensor-core instructions: four epilogue groups (= four TMEM accumulator buffers,
+// four tiles in flight) hide the global-memory latency of the noise / skip-connection fetches behind one another.
+constexpr int kHaloGroups = 2;
+constexpr int kHaloThreads = 64 + kHaloGroups * kEpilogueThreads;
+constexpr int kHaloCacheFloat4 = 256;  // per group: up to 128 channels with ToRGB coefficients
 
 template <int N_GEMM, int CIN, int STAGES>
 struct HaloSmem {
@@ -331,8 +518,8 @@ struct HaloSmem {
     static constexpr int kHaloBytes = kHaloH * kHaloW * kRowBytes;
     static constexpr int kHaloStride = (kHaloBytes + 1023) / 1024 * 1024;
     static constexpr int kBarrierOffset = kWeightBytes + STAGES * kHaloStride;
-    static constexpr int kCacheOffset = kBarrierOffset + ((2 * STAGES + 5) * 8 + 16 + 15) / 16 * 16;
-    static constexpr int kBytes = kCacheOffset + kCacheBytes + 1024;
+    static constexpr int kCacheOffset = kBarrierOffset + ((2 * STAGES + 2 * kHaloGroups + 1) * 8 + 16 + 15) / 16 * 16;
+    static constexpr int kBytes = kCacheOffset + kHaloGroups * kHaloCacheFloat4 * 16 + 1024;
 };
 
 template <int SWIZZLE_BYTES>
@@ -343,12 +530,12 @@ __device__ __forceinline__ uint64_t make_smem_desc_sbo(uint32_t smem_addr, uint3
 }
 
 template <typename T, int N_GEMM, int CIN, int STAGES, bool UP, bool RGB>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kHaloThreads, 1)
 modconv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
                        const ConvParams p) {
     using L = HaloSmem<N_GEMM, CIN, STAGES>;
     constexpr int kSwizzle = CIN * 2;  // 128 or 64 bytes per pixel row
-    constexpr uint32_t kTmemCols = 2 * N_GEMM < 32 ? 32 : 2 * N_GEMM;
+    constexpr uint32_t kTmemCols = kHaloGroups * N_GEMM;
     static_assert((kTmemCols & (kTmemCols - 1)) == 0 && kTmemCols <= 512, "TMEM columns must be a power of two");
     static_assert(CIN == 32 || CIN == 64, "one swizzled row per pixel");
 
@@ -359,11 +546,11 @@ modconv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarrierOffset);
     uint64_t* empty_bar = full_bar + STAGES;
     uint64_t* tmem_full_bar = empty_bar + STAGES;
-    uint64_t* tmem_empty_bar = tmem_full_bar + 2;
-    uint64_t* weight_bar = tmem_empty_bar + 2;
+    uint64_t* tmem_empty_bar = tmem_full_bar + kHaloGroups;
+    uint64_t* weight_bar = tmem_empty_bar + kHaloGroups;
     uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(weight_bar + 1);
 
-    const int warp = threadIdx.x >> 5;
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // shfl result = provably warp-uniform
     const int lane = threadIdx.x & 31;
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tmap_x);
@@ -372,7 +559,7 @@ modconv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_
             mbar_init(full_bar + i, 1);
             mbar_init(empty_bar + i, 1);
         }
-        for (int i = 0; i < 2; ++i) {
+        for (int i = 0; i < kHaloGroups; ++i) {
             mbar_init(tmem_full_bar + i, 1);
             mbar_init(tmem_empty_bar + i, 4);
         }
@@ -383,21 +570,28 @@ modconv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_
     tcgen05_fence_before();
     __syncthreads();
     tcgen05_fence_after();
-    const uint32_t tmem_base = *tmem_base_slot;
+    const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_base_slot, 0);
     const int total_tiles = p.tiles_b * p.tiles_h * p.tiles_w;  // n_tiles == 1: every CTA computes all N_GEMM columns
 
     if (warp == 0) {
-        if (lane == 0) {
-            mbar_expect_tx(weight_bar, L::kWeightBytes);
-            for (int tap = 0; tap < 9; ++tap)
-                tma_load_2d(smem_w + tap * N_GEMM * L::kRowBytes, &tmap_w, weight_bar, tap * CIN, 0);
+        const bool leader = elect_one_sync();
+        {
+            if (leader) {
+                mbar_expect_tx(weight_bar, L::kWeightBytes);
+                for (int tap = 0; tap < 9; ++tap)
+                    tma_load_2d(smem_w + tap * N_GEMM * L::kRowBytes, &tmap_w, weight_bar, tap * CIN, 0);
+            }
+            __syncwarp();
             int stage = 0;
             uint32_t phase = 0;
             for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
                 const TileCoord t = decode_tile(p, tile, N_GEMM);
                 mbar_wait(empty_bar + stage, phase ^ 1u);
-                mbar_expect_tx(full_bar + stage, L::kHaloBytes);
-                tma_load_4d(smem_halo + stage * L::kHaloStride, &tmap_x, full_bar + stage, 0, t.w0 - 1, t.h0 - 1, t.b0);
+                if (leader) {
+                    mbar_expect_tx(full_bar + stage, L::kHaloBytes);
+                    tma_load_4d(smem_halo + stage * L::kHaloStride, &tmap_x, full_bar + stage, 0, t.w0 - 1, t.h0 - 1, t.b0);
+                }
+                __syncwarp();
                 if (++stage == STAGES) {
                     stage = 0;
                     phase ^= 1u;
@@ -405,7 +599,8 @@ modconv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        const bool leader = elect_one_sync();
+        {
             constexpr uint32_t idesc = make_instr_desc(kTileM, N_GEMM, sizeof(T) == 2 && !std::is_same<T, __nv_bfloat16>::value);
             mbar_wait(weight_bar, 0);
             int stage = 0;
@@ -413,35 +608,42 @@ modconv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_
             int acc = 0;
             uint32_t acc_phase = 0;
             const uint32_t w_addr = smem_u32(smem_w);
+            const uint64_t b_desc0 = make_smem_desc<kSwizzle>(w_addr);
             for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
                 mbar_wait(tmem_empty_bar + acc, acc_phase ^ 1u);
                 mbar_wait(full_bar + stage, phase);
                 tcgen05_fence_after();
                 const uint32_t d_tmem = tmem_base + (uint32_t)(acc * N_GEMM);
-                const uint32_t halo_addr = smem_u32(smem_halo + stage * L::kHaloStride);
+                // descriptors differ from these two only by constants: tap shift / K step, in 16-byte units
+                const uint64_t a_desc0 = make_smem_desc_sbo<kSwizzle>(w_addr + (uint32_t)(L::kWeightBytes + stage * L::kHaloStride),
+                                                                      kHaloW * L::kRowBytes);
+                if (leader) {
 #pragma unroll
-                for (int tap = 0; tap < 9; ++tap) {
-                    const uint32_t a_addr = halo_addr + (uint32_t)(((tap / 3) * kHaloW + (tap % 3)) * L::kRowBytes);
-                    const uint64_t a_desc = make_smem_desc_sbo<kSwizzle>(a_addr, kHaloW * L::kRowBytes);
-                    const uint64_t b_desc = make_smem_desc<kSwizzle>(w_addr + (uint32_t)(tap * N_GEMM * L::kRowBytes));
+                    for (int tap = 0; tap < 9; ++tap) {
+                        const uint64_t a_desc = a_desc0 + (uint64_t)((((tap / 3) * kHaloW + (tap % 3)) * L::kRowBytes) >> 4);
+                        const uint64_t b_desc = b_desc0 + (uint64_t)((tap * N_GEMM * L::kRowBytes) >> 4);
 #pragma unroll
-                    for (int k = 0; k < CIN / kUmmaK; ++k)
-                        umma_bf16(d_tmem, a_desc + (uint64_t)(k * 2), b_desc + (uint64_t)(k * 2), idesc,
-                                  (tap | k) != 0 ? 1u : 0u);
+                        for (int k = 0; k < CIN / kUmmaK; ++k)
+                            umma_bf16(d_tmem, a_desc + (uint64_t)(k * 2), b_desc + (uint64_t)(k * 2), idesc,
+                                      (tap | k) != 0 ? 1u : 0u);
+                    }
+                    umma_commit(empty_bar + stage);
+                    umma_commit(tmem_full_bar + acc);
                 }
-                umma_commit(empty_bar + stage);
-                umma_commit(tmem_full_bar + acc);
+                __syncwarp();
                 if (++stage == STAGES) {
                     stage = 0;
                     phase ^= 1u;
                 }
-                acc ^= 1;
-                if (acc == 0) acc_phase ^= 1u;
+                if (++acc == kHaloGroups) {
+                    acc = 0;
+                    acc_phase ^= 1u;
+                }
             }
         }
     } else {
-        conv_epilogue<T, N_GEMM, UP, RGB>(p, (warp - 2) >> 2, warp, lane, total_tiles, tmem_base, tmem_full_bar,
-                                          tmem_empty_bar, reinterpret_cast<float4*>(smem + L::kCacheOffset));
+        conv_epilogue_frag<T, N_GEMM, (UP ? N_GEMM / 4 : N_GEMM), UP, RGB, kHaloGroups>(
+            p, (warp - 2) >> 2, warp, lane, total_tiles, tmem_base, tmem_full_bar, tmem_empty_bar);
     }
 
     tcgen05_fence_before();
@@ -558,12 +760,13 @@ static int launch_halo_typed(const ConvParams& p, const void* x, const void* wei
     }
     const int total_tiles = p.tiles_b * p.tiles_h * p.tiles_w;
     const int grid = total_tiles < g_num_sms ? total_tiles : g_num_sms;
-    if (p.rgb_weight != nullptr)
-        modconv3x3_halo_kernel<T, N_GEMM, CIN, STAGES, false, true><<<grid, kThreads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
-    else if (p.up)
-        modconv3x3_halo_kernel<T, N_GEMM, CIN, STAGES, true, false><<<grid, kThreads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
-    else
-        modconv3x3_halo_kernel<T, N_GEMM, CIN, STAGES, false, false><<<grid, kThreads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
+    if constexpr (N_GEMM == 128) {  // only the folded up-convolution 64 -> 4 x 32
+        modconv3x3_halo_kernel<T, N_GEMM, CIN, STAGES, true, false><<<grid, kHaloThreads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
+    } else if (p.rgb_weight != nullptr) {
+        modconv3x3_halo_kernel<T, N_GEMM, CIN, STAGES, false, true><<<grid, kHaloThreads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
+    } else {
+        modconv3x3_halo_kernel<T, N_GEMM, CIN, STAGES, false, false><<<grid, kHaloThreads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
+    }
     return check_launch("modconv3x3_halo_kernel");
 }
 
@@ -577,12 +780,15 @@ template <int N_GEMM, int CIN, int STAGES>
 static int configure_halo() {
     using L = HaloSmem<N_GEMM, CIN, STAGES>;
     int rc;
-    if ((rc = raise_smem_limit(modconv3x3_halo_kernel<__nv_bfloat16, N_GEMM, CIN, STAGES, false, false>, L::kBytes, "modconv3x3_halo")) != GANCE_OK) return rc;
-    if ((rc = raise_smem_limit(modconv3x3_halo_kernel<__half, N_GEMM, CIN, STAGES, false, false>, L::kBytes, "modconv3x3_halo")) != GANCE_OK) return rc;
-    if ((rc = raise_smem_limit(modconv3x3_halo_kernel<__nv_bfloat16, N_GEMM, CIN, STAGES, true, false>, L::kBytes, "modconv3x3_halo<up>")) != GANCE_OK) return rc;
-    if ((rc = raise_smem_limit(modconv3x3_halo_kernel<__half, N_GEMM, CIN, STAGES, true, false>, L::kBytes, "modconv3x3_halo<up>")) != GANCE_OK) return rc;
-    if ((rc = raise_smem_limit(modconv3x3_halo_kernel<__nv_bfloat16, N_GEMM, CIN, STAGES, false, true>, L::kBytes, "modconv3x3_halo<rgb>")) != GANCE_OK) return rc;
-    return raise_smem_limit(modconv3x3_halo_kernel<__half, N_GEMM, CIN, STAGES, false, true>, L::kBytes, "modconv3x3_halo<rgb>");
+    if constexpr (N_GEMM == 128) {
+        if ((rc = raise_smem_limit(modconv3x3_halo_kernel<__nv_bfloat16, N_GEMM, CIN, STAGES, true, false>, L::kBytes, "modconv3x3_halo<up>")) != GANCE_OK) return rc;
+        return raise_smem_limit(modconv3x3_halo_kernel<__half, N_GEMM, CIN, STAGES, true, false>, L::kBytes, "modconv3x3_halo<up>");
+    } else {
+        if ((rc = raise_smem_limit(modconv3x3_halo_kernel<__nv_bfloat16, N_GEMM, CIN, STAGES, false, false>, L::kBytes, "modconv3x3_halo")) != GANCE_OK) return rc;
+        if ((rc = raise_smem_limit(modconv3x3_halo_kernel<__half, N_GEMM, CIN, STAGES, false, false>, L::kBytes, "modconv3x3_halo")) != GANCE_OK) return rc;
+        if ((rc = raise_smem_limit(modconv3x3_halo_kernel<__nv_bfloat16, N_GEMM, CIN, STAGES, false, true>, L::kBytes, "modconv3x3_halo<rgb>")) != GANCE_OK) return rc;
+        return raise_smem_limit(modconv3x3_halo_kernel<__half, N_GEMM, CIN, STAGES, false, true>, L::kBytes, "modconv3x3_halo<rgb>");
+    }
 }
 
 static bool g_use_halo = true;
@@ -661,6 +867,7 @@ static int launch_tensor_core_conv(const char* who, const void* x, int dtype, in
     GANCE_REQUIRE(is_pow2(p.tile_h), GANCE_E_SHAPE, "%s: H=%d (< %d) must be a power of two", who, h_out, rows);
     GANCE_REQUIRE(is_pow2(c_real) && c_real <= tc::kCacheFloat4PerGroup / (rgb ? 2 : 1), GANCE_E_SHAPE,
                   "%s: Cout=%d must be a power of two <= %d", who, c_real, tc::kCacheFloat4PerGroup / (rgb ? 2 : 1));
+    static_assert(tc::kHaloCacheFloat4 >= 2 * 128, "halo kernels cache up to 128 channels with ToRGB coefficients");
     p.tile_b = 1;
     p.tiles_w = (w_out + p.tile_w - 1) / p.tile_w;
     p.tiles_h = (h_out + p.tile_h - 1) / p.tile_h;
@@ -680,7 +887,7 @@ static int launch_tensor_core_conv(const char* who, const void* x, int dtype, in
 
     // Narrow layers (512^2 / 1024^2): halo kernel, whole weight resident, one activation fetch per tile.
     if (tc::g_use_halo && pad == 1 && w_out % tc::kHaloTileW == 0 && h_out % tc::kHaloTileH == 0 &&
-        ((c_in == 64 && (c_out == 128 || c_out == 64)) || (c_in == 32 && c_out == 32))) {
+        ((c_in == 64 && ((c_out == 128 && up && c_real == 32) || (c_out == 64 && !up))) || (c_in == 32 && c_out == 32 && !up))) {
         p.tile_w = tc::kHaloTileW; p.tile_h = tc::kHaloTileH; p.tile_b = 1;
         p.tile_w_log2 = ilog2(p.tile_w); p.tile_hw_log2 = ilog2(p.tile_w * p.tile_h);
         p.tiles_w = w_out / p.tile_w; p.tiles_h = h_out / p.tile_h; p.tiles_b = batch;
