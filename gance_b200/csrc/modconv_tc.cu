@@ -237,9 +237,69 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
     int cached_b = -1;
     uint32_t full_phase = 0;
 
-    for (int tile = blockIdx.x + group * gridDim.x; tile < total_tiles; tile += GROUPS * gridDim.x) {
-        const TileCoord t = decode_tile(p, tile, N_TILE);
+    // Noise and skip-connection values of a tile do not depend on its accumulator: they are requested one tile AHEAD
+    // (while the current tile is being computed) so their global-memory latency never sits on the tile's critical path.
+    constexpr int NP = UP ? 4 : 1;  // noise values per input pixel
+    struct Ahead {
+        TileCoord t;
+        float nz[4][NP];
+        float4 p00, p01, p10, p11;  // y_prev taps of this lane's own pixel (RGB)
+        float w01, w10, w11;
+        int own_h, own_w;
+    };
+    auto request = [&](int tile) {
+        Ahead n;
+        n.t = decode_tile(p, tile, N_TILE);
+        const float* noise_b = p.noise ? p.noise + (size_t)n.t.b0 * p.noise_batch_stride : nullptr;
+#pragma unroll
+        for (int rr = 0; rr < 4; ++rr) {
+            const int h = n.t.h0 + hl[rr], w = n.t.w0 + wl[rr];
+            if (UP) {
+                float2 top = make_float2(0.f, 0.f), bot = top;
+                if (noise_b != nullptr) {
+                    top = __ldg(reinterpret_cast<const float2*>(noise_b + (size_t)(2 * h) * out_w + 2 * w));
+                    bot = __ldg(reinterpret_cast<const float2*>(noise_b + (size_t)(2 * h + 1) * out_w + 2 * w));
+                }
+                n.nz[rr][0] = top.x; n.nz[rr][1 % NP] = top.y; n.nz[rr][2 % NP] = bot.x; n.nz[rr][3 % NP] = bot.y;
+            } else {
+                n.nz[rr][0] = noise_b ? __ldg(noise_b + (size_t)h * out_w + w) : 0.f;
+            }
+        }
+        n.p00 = n.p01 = n.p10 = n.p11 = make_float4(0.f, 0.f, 0.f, 0.f);
+        n.w01 = n.w10 = n.w11 = 0.f;
+        n.own_h = n.own_w = 0;
+        if (RGB) {  // this lane finishes the pixel of row rr == q4
+            n.own_h = n.t.h0 + (q4 == 0 ? hl[0] : q4 == 1 ? hl[1] : q4 == 2 ? hl[2] : hl[3]);
+            n.own_w = n.t.w0 + (q4 == 0 ? wl[0] : q4 == 1 ? wl[1] : q4 == 2 ? wl[2] : wl[3]);
+            if (p.y_prev != nullptr) {
+                // upsample_2d(k=[1,3,3,1]): y[2a] = .25 p[a-1] + .75 p[a]; y[2a+1] = .75 p[a] + .25 p[a+1]; taps outside
+                // the image contribute zero - fetched anyway (clamped) so the four loads are unconditional
+                const int hp = p.h_out >> 1, wp = p.w_out >> 1;
+                const int a = n.own_h >> 1, c = n.own_w >> 1;
+                const int a2 = (n.own_h & 1) ? a + 1 : a - 1, c2 = (n.own_w & 1) ? c + 1 : c - 1;
+                const bool a_in = a2 >= 0 && a2 < hp, c_in = c2 >= 0 && c2 < wp;
+                const int a2c = a_in ? a2 : a, c2c = c_in ? c2 : c;
+                const float4* base = reinterpret_cast<const float4*>(p.y_prev) + (size_t)n.t.b0 * hp * wp;
+                n.p00 = __ldg(base + (size_t)a * wp + c);
+                n.p01 = __ldg(base + (size_t)a * wp + c2c);
+                n.p10 = __ldg(base + (size_t)a2c * wp + c);
+                n.p11 = __ldg(base + (size_t)a2c * wp + c2c);
+                n.w01 = c_in ? 0.1875f : 0.f;
+                n.w10 = a_in ? 0.1875f : 0.f;
+                n.w11 = (a_in && c_in) ? 0.0625f : 0.f;
+            }
+        }
+        return n;
+    };
+
+    int tile = blockIdx.x + group * gridDim.x;
+    Ahead ahead;
+    if (tile < total_tiles) ahead = request(tile);
+    for (; tile < total_tiles; tile += GROUPS * gridDim.x) {
+        const Ahead cur = ahead;
+        const TileCoord t = cur.t;
         const int b = t.b0;
+        if (tile + GROUPS * (int)gridDim.x < total_tiles) ahead = request(tile + GROUPS * gridDim.x);
         if (b != cached_b) {  // per-sample coefficients of this thread's channels -> registers
 #pragma unroll
             for (int k = 0; k < CPT; ++k) {
@@ -257,32 +317,12 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
             }
             cached_b = b;
         }
-        // everything that does not depend on the accumulator is fetched while the MMAs run
-        const float* noise_b = p.noise ? p.noise + (size_t)b * p.noise_batch_stride : nullptr;
-        constexpr int NP = UP ? 4 : 1;  // noise values per input pixel
         float nz[4][NP];
 #pragma unroll
-        for (int rr = 0; rr < 4; ++rr) {
-            const int h = t.h0 + hl[rr], w = t.w0 + wl[rr];
-            if (UP) {
-                float2 top = make_float2(0.f, 0.f), bot = top;
-                if (noise_b != nullptr) {
-                    top = __ldg(reinterpret_cast<const float2*>(noise_b + (size_t)(2 * h) * out_w + 2 * w));
-                    bot = __ldg(reinterpret_cast<const float2*>(noise_b + (size_t)(2 * h + 1) * out_w + 2 * w));
-                }
-                nz[rr][0] = top.x * p.noise_strength; nz[rr][1 % NP] = top.y * p.noise_strength;
-                nz[rr][2 % NP] = bot.x * p.noise_strength; nz[rr][3 % NP] = bot.y * p.noise_strength;
-            } else {
-                nz[rr][0] = noise_b ? __ldg(noise_b + (size_t)h * out_w + w) * p.noise_strength : 0.f;
-            }
-        }
-        float4 skip = make_float4(0.f, 0.f, 0.f, 0.f);
-        int own_h = 0, own_wp = 0;
-        if (RGB) {  // this lane finishes the pixel of row rr == q4
-            own_h = t.h0 + (q4 == 0 ? hl[0] : q4 == 1 ? hl[1] : q4 == 2 ? hl[2] : hl[3]);
-            own_wp = t.w0 + (q4 == 0 ? wl[0] : q4 == 1 ? wl[1] : q4 == 2 ? wl[2] : wl[3]);
-            if (p.y_prev != nullptr) skip = upsample_tap(p.y_prev, b, p.h_out >> 1, p.w_out >> 1, own_h, own_wp);
-        }
+        for (int rr = 0; rr < 4; ++rr)
+#pragma unroll
+            for (int ph = 0; ph < NP; ++ph) nz[rr][ph] = cur.nz[rr][ph] * p.noise_strength;
+        const int own_h = cur.own_h, own_wp = cur.own_w;
         float rgb[4][3];
 #pragma unroll
         for (int rr = 0; rr < 4; ++rr) rgb[rr][0] = rgb[rr][1] = rgb[rr][2] = 0.f;
@@ -350,8 +390,9 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
                 const float send = h_own ? keep[0][c] : keep[1][c];
                 mine[c] = (h_own ? keep[1][c] : keep[0][c]) + __shfl_xor_sync(0xffffffffu, send, 2);
             }
-            const float red = mine[0] + rgb_bias.x + skip.x, green = mine[1] + rgb_bias.y + skip.y,
-                        blue = mine[2] + rgb_bias.z + skip.z;
+            const float red = mine[0] + rgb_bias.x + 0.5625f * cur.p00.x + cur.w01 * cur.p01.x + cur.w10 * cur.p10.x + cur.w11 * cur.p11.x;
+            const float green = mine[1] + rgb_bias.y + 0.5625f * cur.p00.y + cur.w01 * cur.p01.y + cur.w10 * cur.p10.y + cur.w11 * cur.p11.y;
+            const float blue = mine[2] + rgb_bias.z + 0.5625f * cur.p00.z + cur.w01 * cur.p01.z + cur.w10 * cur.p10.z + cur.w11 * cur.p11.z;
             const size_t pixel = ((size_t)b * p.h_out + own_h) * p.w_out + own_wp;
             if (p.y_out != nullptr) reinterpret_cast<float4*>(p.y_out)[pixel] = make_float4(red, green, blue, 0.f);
             if (p.frames != nullptr) {
@@ -507,9 +548,8 @@ constexpr int kHaloTileW = 8, kHaloTileH = 16;
 constexpr int kHaloW = kHaloTileW + 2, kHaloH = kHaloTileH + 2;
 // A tile of these layers is 18-36 tensor-core instructions: four epilogue groups (= four TMEM accumulator buffers,
 // four tiles in flight) hide the global-memory latency of the noise / skip-connection fetches behind one another.
-constexpr int kHaloGroups = 2;
-constexpr int kHaloThreads = 64 + kHaloGroups * kEpilogueThreads;
-constexpr int kHaloCacheFloat4 = 256;  // per group: up to 128 channels with ToRGB coefficients
+__host__ __device__ constexpr int halo_groups(int n_gemm) { return n_gemm == 32 ? 3 : 2; }  // bounded by registers (65536 / threads)
+__host__ __device__ constexpr int halo_threads(int n_gemm) { return 64 + halo_groups(n_gemm) * kEpilogueThreads; }
 
 template <int N_GEMM, int CIN, int STAGES>
 struct HaloSmem {
@@ -518,8 +558,8 @@ struct HaloSmem {
     static constexpr int kHaloBytes = kHaloH * kHaloW * kRowBytes;
     static constexpr int kHaloStride = (kHaloBytes + 1023) / 1024 * 1024;
     static constexpr int kBarrierOffset = kWeightBytes + STAGES * kHaloStride;
-    static constexpr int kCacheOffset = kBarrierOffset + ((2 * STAGES + 2 * kHaloGroups + 1) * 8 + 16 + 15) / 16 * 16;
-    static constexpr int kBytes = kCacheOffset + kHaloGroups * kHaloCacheFloat4 * 16 + 1024;
+    static constexpr int kCacheOffset = kBarrierOffset + ((2 * STAGES + 2 * halo_groups(N_GEMM) + 1) * 8 + 16 + 15) / 16 * 16;
+    static constexpr int kBytes = kCacheOffset + 1024;
 };
 
 template <int SWIZZLE_BYTES>
@@ -530,12 +570,13 @@ __device__ __forceinline__ uint64_t make_smem_desc_sbo(uint32_t smem_addr, uint3
 }
 
 template <typename T, int N_GEMM, int CIN, int STAGES, bool UP, bool RGB>
-__global__ void __launch_bounds__(kHaloThreads, 1)
+__global__ void __launch_bounds__(halo_threads(N_GEMM), 1)
 modconv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
                        const ConvParams p) {
     using L = HaloSmem<N_GEMM, CIN, STAGES>;
     constexpr int kSwizzle = CIN * 2;  // 128 or 64 bytes per pixel row
-    constexpr uint32_t kTmemCols = kHaloGroups * N_GEMM;
+    constexpr int kHaloGroups = halo_groups(N_GEMM);
+    constexpr uint32_t kTmemCols = kHaloGroups * N_GEMM <= 128 ? 128 : (kHaloGroups * N_GEMM <= 256 ? 256 : 512);
     static_assert((kTmemCols & (kTmemCols - 1)) == 0 && kTmemCols <= 512, "TMEM columns must be a power of two");
     static_assert(CIN == 32 || CIN == 64, "one swizzled row per pixel");
 
@@ -761,11 +802,11 @@ static int launch_halo_typed(const ConvParams& p, const void* x, const void* wei
     const int total_tiles = p.tiles_b * p.tiles_h * p.tiles_w;
     const int grid = total_tiles < g_num_sms ? total_tiles : g_num_sms;
     if constexpr (N_GEMM == 128) {  // only the folded up-convolution 64 -> 4 x 32
-        modconv3x3_halo_kernel<T, N_GEMM, CIN, STAGES, true, false><<<grid, kHaloThreads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
+        modconv3x3_halo_kernel<T, N_GEMM, CIN, STAGES, true, false><<<grid, halo_threads(N_GEMM), L::kBytes, stream>>>(tmap_x, tmap_w, p);
     } else if (p.rgb_weight != nullptr) {
-        modconv3x3_halo_kernel<T, N_GEMM, CIN, STAGES, false, true><<<grid, kHaloThreads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
+        modconv3x3_halo_kernel<T, N_GEMM, CIN, STAGES, false, true><<<grid, halo_threads(N_GEMM), L::kBytes, stream>>>(tmap_x, tmap_w, p);
     } else {
-        modconv3x3_halo_kernel<T, N_GEMM, CIN, STAGES, false, false><<<grid, kHaloThreads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
+        modconv3x3_halo_kernel<T, N_GEMM, CIN, STAGES, false, false><<<grid, halo_threads(N_GEMM), L::kBytes, stream>>>(tmap_x, tmap_w, p);
     }
     return check_launch("modconv3x3_halo_kernel");
 }
@@ -867,7 +908,6 @@ static int launch_tensor_core_conv(const char* who, const void* x, int dtype, in
     GANCE_REQUIRE(is_pow2(p.tile_h), GANCE_E_SHAPE, "%s: H=%d (< %d) must be a power of two", who, h_out, rows);
     GANCE_REQUIRE(is_pow2(c_real) && c_real <= tc::kCacheFloat4PerGroup / (rgb ? 2 : 1), GANCE_E_SHAPE,
                   "%s: Cout=%d must be a power of two <= %d", who, c_real, tc::kCacheFloat4PerGroup / (rgb ? 2 : 1));
-    static_assert(tc::kHaloCacheFloat4 >= 2 * 128, "halo kernels cache up to 128 channels with ToRGB coefficients");
     p.tile_b = 1;
     p.tiles_w = (w_out + p.tile_w - 1) / p.tile_w;
     p.tiles_h = (h_out + p.tile_h - 1) / p.tile_h;
