@@ -302,7 +302,7 @@ def main():
     achieved_tflops = flop_per_step / (conv_step_ms * 1e-3) / 1e12 if conv_step_ms > 0 else 0.0
     tensor_peak = peaks["bf16_tflops_sustained"]
     roofline = {
-        "bound": "tensor", "kernel": "modconv3x3_tc_kernel (all modulated-convolution launches of a step, incl. up-FIR staging)",
+        "bound": "tensor", "kernel": "modconv3x3_tc_kernel + modconv3x3_halo_kernel (every modulated-convolution launch of a step: tcgen05 implicit GEMMs with fused demod/noise/bias/lrelu/ToRGB/skip/uint8 epilogues)",
         "achieved": achieved_tflops, "peak": tensor_peak, "unit": "TFLOP/s", "frac": achieved_tflops / tensor_peak,
         "peak_source": f"bf16_tflops_sustained, {peak_source}", "traffic": None,
         "conv_ms_per_step": conv_step_ms, "other_ms_per_step": float(np.median(other_ms)),

@@ -140,3 +140,40 @@ def test_config1_256_frames_match_oracle():
         print(f"256^2 {mode}: exact {exact:.5f} within1 {within:.5f} worst {worst}")
         assert_16bit_tolerance("fp16" if mode == "fp32" else mode, frames.cpu().numpy(), want)
         gen.release_buffers()
+
+
+def test_config2_1024_frame_matches_oracle():
+    """
+    BASELINE config 2 at its full size: one frame of the 1024^2 config-f generator (perturbed init: noise, bias and
+    truncation paths active) in the fp16 mode against the fp64 oracle, through the same call the bench times.
+    """
+    spec, variables, oracle, z = _case(1024, 4, True, 1)
+    gen = GeneratorOnDevice(spec, variables, _device(), mode="fp16")
+    frames = gen.run_vectors(torch.as_tensor(z), noise_mode="const")
+    assert frames.shape == (1, 1024, 1024, 3) and int(frames.sum()) > 0  # the reference's own check (test_network_functions.py:116-117)
+    want = ref.convert_images_to_uint8(oracle.run_vector(z))
+    within, worst, exact = lsb_stats(frames.cpu().numpy(), want)
+    print(f"1024^2 fp16: exact {exact:.5f} within1 {within:.5f} worst {worst}")
+    assert within >= 0.999, (within, worst)
+
+
+def test_full_size_batch_properties():
+    """
+    Size-independent properties at the bench's size (batch 32, 1024^2), where the oracle is too slow: every frame of a
+    batch equals the same latent rendered in a batch of 1 (bit-exact: no cross-sample leakage through the tiling, the
+    coefficient registers or the accumulator buffers), a permuted batch gives permuted frames, and two runs agree.
+    """
+    spec = GeneratorSpec(1024)
+    gen = GeneratorOnDevice(spec, random_init_variables(spec, seed=5, perturbed=True), _device(), mode="fp16")
+    z = torch.as_tensor(np.random.RandomState(7).randn(32, 512))
+    wplus = gen.mapping(z)
+    together = gen.synthesis(wplus, noise_mode="const").clone()
+    again = gen.synthesis(wplus, noise_mode="const")
+    assert torch.equal(together, again)
+    for i in (0, 13, 31):
+        alone = gen.synthesis(wplus[i: i + 1], noise_mode="const")
+        assert torch.equal(alone[0], together[i]), f"frame {i} differs when rendered alone"
+    perm = torch.randperm(32, generator=torch.Generator().manual_seed(3))
+    permuted = gen.synthesis(wplus[perm.to(wplus.device)], noise_mode="const")
+    assert torch.equal(permuted, together[perm.to(together.device)])
+    gen.release_buffers()
