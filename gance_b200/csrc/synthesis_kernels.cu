@@ -378,6 +378,43 @@ __global__ void to_uint8_kernel(const float4* __restrict__ y, size_t pixels, uin
 }
 
 // ------------------------------------------------------------------------------------------------
+// Fresh N(0,1) noise for every noise input of a batch in ONE launch (the vector path: Gs.run leaves
+// randomize_noise=True, network_functions.py:151-158, so tf.random_normal draws [B,1,H,W] per layer).
+// Counter-based: element group g (4 consecutive floats) = BoxMuller(Philox4x32-10(counter = g + offset,
+// key = seed)), so the stream is reproducible from (seed, offset) and independent of the launch shape.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
+#pragma unroll
+    for (int round = 0; round < 10; ++round) {
+        const uint32_t hi0 = __umulhi(0xD2511F53u, ctr.x), lo0 = 0xD2511F53u * ctr.x;
+        const uint32_t hi1 = __umulhi(0xCD9E8D57u, ctr.z), lo1 = 0xCD9E8D57u * ctr.z;
+        ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
+        key.x += 0x9E3779B9u;
+        key.y += 0xBB67AE85u;
+    }
+    return ctr;
+}
+
+__device__ __forceinline__ float2 box_muller(uint32_t a, uint32_t b) {
+    const float u1 = ((float)a + 1.0f) * 2.3283064365386963e-10f;  // (0, 1]
+    const float u2 = (float)b * 2.3283064365386963e-10f;           // [0, 1)
+    const float radius = sqrtf(-2.0f * __logf(u1));
+    float sn, cs;
+    __sincosf(6.283185307179586f * u2, &sn, &cs);
+    return make_float2(radius * cs, radius * sn);
+}
+
+__global__ void __launch_bounds__(256) normal_noise_kernel(float4* __restrict__ out, size_t groups, uint2 key,
+                                                           unsigned long long offset) {
+    for (size_t g = blockIdx.x * (size_t)blockDim.x + threadIdx.x; g < groups; g += (size_t)gridDim.x * blockDim.x) {
+        const unsigned long long c = g + offset;
+        const uint4 r = philox4x32_10(make_uint4((uint32_t)c, (uint32_t)(c >> 32), 0u, 0u), key);
+        const float2 a = box_muller(r.x, r.y), b = box_muller(r.z, r.w);
+        out[g] = make_float4(a.x, a.y, b.x, b.y);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // fp32 validation-mode 3x3 convolution on CUDA cores (the numerical yard-stick for the tcgen05
 // path). CTA = 8x8 output pixels x 64 output channels; thread = 4 pixels x 4 channels;
 // input channels are staged through shared memory 8 at a time. Weights are HWIO (TF layout).
@@ -672,6 +709,17 @@ int gance_to_uint8_nhwc(const float* y, int batch, int h, int w, uint8_t* frames
     size_t pixels = (size_t)batch * h * w;
     to_uint8_kernel<<<grid_for(pixels, 256), 256, 0, (cudaStream_t)stream>>>((const float4*)y, pixels, frames);
     return check_launch("to_uint8_kernel");
+}
+
+int gance_normal_noise(float* out, long long count, unsigned long long seed, unsigned long long offset, void* stream) {
+    GANCE_REQUIRE(is_initialised(), GANCE_E_NOT_INIT, "gance_init() has not been called");
+    GANCE_REQUIRE(out != nullptr, GANCE_E_NULL, "gance_normal_noise: NULL pointer");
+    GANCE_REQUIRE(count > 0 && count % 4 == 0, GANCE_E_SHAPE, "gance_normal_noise: count %lld must be a positive multiple of 4", count);
+    GANCE_REQUIRE(aligned16(out), GANCE_E_ALIGN, "gance_normal_noise: out must be 16-byte aligned");
+    const size_t groups = (size_t)count / 4;
+    normal_noise_kernel<<<grid_for(groups, 256), 256, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<float4*>(out), groups, make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)), offset);
+    return check_launch("normal_noise_kernel");
 }
 
 }  // extern "C"

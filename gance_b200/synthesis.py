@@ -76,6 +76,8 @@ class GeneratorOnDevice:
         self.convs, self.rgbs = synthesis_layers(spec)
         self._buffers: Dict[tuple, torch.Tensor] = {}
         self.profile_events: Optional[list] = None  # set to [] to collect (name, cuda event) marks
+        self.noise_seed = 0x5EED_0000_0000_0000 | (id(self) & 0xFFFF_FFFF)  # Philox key of the "random" noise mode
+        self.noise_offset = 0  # Philox counter: advances with every batch so no two calls share noise
         self._upload(variables)
 
     # ---- weights ---------------------------------------------------------------------------------
@@ -242,13 +244,28 @@ class GeneratorOnDevice:
                       for i, r in enumerate(self.rgbs)]
         self._mark("styles")
 
+        # fresh noise of every layer in one launch (tf.random_normal per layer in the reference's graph)
+        random_noise: Dict[int, torch.Tensor] = {}
+        if noise_mode == "random":
+            sizes = [(i, c.out_resolution) for i, c in enumerate(self.convs) if self.conv_strength[i] != 0.0]
+            total = sum(batch * side * side for _, side in sizes)
+            if total:
+                flat = self._buffer("noise_random", ((total + 3) // 4 * 4,), torch.float32)
+                _lib.check(lib.gance_normal_noise(flat.data_ptr(), flat.numel(), self.noise_seed, self.noise_offset,
+                                                  stream), "gance_normal_noise")
+                self.noise_offset += flat.numel() // 4
+                start = 0
+                for i, side in sizes:
+                    random_noise[i] = flat[start: start + batch * side * side].view(batch, side, side)
+                    start += batch * side * side
+
         def layer_noise(i: int, side: int):
             if noise_mode == "none" or (noise_mode != "provided" and self.conv_strength[i] == 0.0):
                 return None, 0
             if noise_mode == "const":
                 return self.conv_noise[i], 0
             if noise_mode == "random":
-                return torch.randn((batch, side, side), dtype=torch.float32, device=self.device), side * side
+                return random_noise[i], side * side
             tensor = noise[i].to(self.device, torch.float32).reshape(batch, side, side).contiguous()
             return tensor, side * side
 

@@ -185,6 +185,14 @@ int gance_torgb_skip(const void* x, int dtype, int batch, int h, int w, int chan
 /* Stand-alone convert_images_to_uint8 on a [B,H,W,4] f32 skip tensor -> [B,H,W,3] u8. */
 int gance_to_uint8_nhwc(const float* y, int batch, int h, int w, uint8_t* frames, void* stream);
 
+/* ---- fresh noise inputs ---------------------------------------------------------------------------
+ * Gs.run leaves randomize_noise=True (network_functions.py:151-158), so every call draws
+ * tf.random_normal([B,1,H,W]) per noise input. out[4g..4g+3] = BoxMuller(Philox4x32-10(counter = g + offset,
+ * key = seed)): N(0,1) float32, reproducible from (seed, offset), independent of the launch shape. count % 4 == 0.
+ * One launch fills the noise of every layer of a batch (the layers are slices of one buffer). */
+int gance_normal_noise(float* out, long long count, unsigned long long seed, unsigned long long offset,
+                       void* stream);
+
 /* ---- audio: WAV samples -> float32 -> resampled so that one frame = vector_length samples --------
  * gance_pcm_to_float: music.read_wav_file (gance/vector_sources/music.py:190-205) +
  * remap_values_into_range (vector_sources_common.py:44-61): PCM of `bits` (16, 32, 8) mapped from

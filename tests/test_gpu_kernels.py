@@ -387,3 +387,41 @@ def test_fused_conv_torgb_matches_oracle(lib, mode, cin, cout, side, batch, last
     else:
         ulp = 2.0 ** -8 if mode == "bf16" else 2.0 ** -11
         assert rel_err(out.permute(0, 3, 1, 2), want_x) < 2 * ulp
+
+
+def _philox4x32_10(counter: np.ndarray, key: np.ndarray) -> np.ndarray:
+    """numpy restatement of Philox4x32-10 (Salmon et al. 2011): counter [n,4] uint32, key [2] uint32."""
+    ctr = counter.astype(np.uint64)
+    k0, k1 = np.uint64(key[0]), np.uint64(key[1])
+    mask = np.uint64(0xFFFFFFFF)
+    for _ in range(10):
+        p0 = np.uint64(0xD2511F53) * ctr[:, 0]
+        p1 = np.uint64(0xCD9E8D57) * ctr[:, 2]
+        ctr = np.stack([(p1 >> np.uint64(32)) ^ ctr[:, 1] ^ k0, p1 & mask, (p0 >> np.uint64(32)) ^ ctr[:, 3] ^ k1, p0 & mask], axis=1)
+        k0 = (k0 + np.uint64(0x9E3779B9)) & mask
+        k1 = (k1 + np.uint64(0xBB67AE85)) & mask
+    return ctr.astype(np.uint32)
+
+
+def test_normal_noise_matches_philox_box_muller_restatement(lib):
+    """gance_normal_noise against a numpy Philox4x32-10 + Box-Muller restatement, plus N(0,1) moments."""
+    count, seed, offset = 1 << 20, 0x1234_5678_9ABC_DEF0, 77
+    out = torch.empty(count, device="cuda", dtype=torch.float32)
+    _lib.check(lib.gance_normal_noise(out.data_ptr(), count, seed, offset, stream()), "gance_normal_noise")
+    got = out.cpu().numpy().astype(np.float64)
+    groups = np.arange(count // 4, dtype=np.uint64) + np.uint64(offset)
+    counter = np.stack([groups & np.uint64(0xFFFFFFFF), groups >> np.uint64(32), np.zeros_like(groups), np.zeros_like(groups)], axis=1)
+    bits = _philox4x32_10(counter, np.array([seed & 0xFFFFFFFF, seed >> 32], dtype=np.uint64)).astype(np.float64)
+    u1a, u2a, u1b, u2b = (bits[:, 0] + 1) * 2.0 ** -32, bits[:, 1] * 2.0 ** -32, (bits[:, 2] + 1) * 2.0 ** -32, bits[:, 3] * 2.0 ** -32
+    ra, rb = np.sqrt(-2 * np.log(u1a)), np.sqrt(-2 * np.log(u1b))
+    want = np.stack([ra * np.cos(2 * np.pi * u2a), ra * np.sin(2 * np.pi * u2a), rb * np.cos(2 * np.pi * u2b), rb * np.sin(2 * np.pi * u2b)], axis=1).reshape(-1)
+    # float32 uniforms + fast-math log/sincos on the device: absolute agreement to ~1e-3 of a unit-variance value
+    assert np.abs(got - want).max() < 5e-3 and np.abs(got - want).mean() < 2e-5
+    assert abs(got.mean()) < 4e-3 and abs(got.var() - 1) < 6e-3
+    kurt = ((got - got.mean()) ** 4).mean() / got.var() ** 2
+    assert abs(kurt - 3) < 0.03
+    again = torch.empty(count, device="cuda", dtype=torch.float32)
+    _lib.check(lib.gance_normal_noise(again.data_ptr(), count, seed, offset, stream()), "gance_normal_noise")
+    assert torch.equal(out, again)
+    _lib.check(lib.gance_normal_noise(again.data_ptr(), count, seed, offset + count // 4, stream()), "gance_normal_noise")
+    assert not torch.equal(out, again) and abs(float((out * again).mean())) < 4e-3
