@@ -728,7 +728,8 @@ static int make_tmap(CUtensorMap* map, const void* base, bool half_operands, int
     cuuint32_t elem_strides[5] = {1, 1, 1, 1, 1};
     CUtensorMapSwizzle sw = swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
                                                  : (swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
-                                                                        : CU_TENSOR_MAP_SWIZZLE_32B);
+                                                    : (swizzle_bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B
+                                                                           : CU_TENSOR_MAP_SWIZZLE_NONE));
     CUresult rc = g_encode_tiled(map, half_operands ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16,
                                  (cuuint32_t)rank, const_cast<void*>(base),
                                  dims, strides_bytes, box, elem_strides, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
@@ -834,6 +835,14 @@ static int configure_halo() {
 
 static bool g_use_halo = true;
 
+// used by upconv_phase.cu
+int encode_tensor_map(CUtensorMap* map, const void* base, bool half_operands, int rank, const cuuint64_t* dims,
+                      const cuuint64_t* strides_bytes, const cuuint32_t* box, int swizzle_bytes) {
+    return make_tmap(map, base, half_operands, rank, dims, strides_bytes, box, swizzle_bytes);
+}
+int sm_count() { return g_num_sms; }
+int configure_phase_kernels();
+
 }  // namespace tc
 
 int init_tensor_core_path() {
@@ -856,6 +865,7 @@ int init_tensor_core_path() {
     if ((rc = tc::configure_halo<128, 64, 2>()) != GANCE_OK) return rc;
     if ((rc = tc::configure_halo<64, 64, 3>()) != GANCE_OK) return rc;
     if ((rc = tc::configure_halo<32, 32, 4>()) != GANCE_OK) return rc;
+    if ((rc = tc::configure_phase_kernels()) != GANCE_OK) return rc;
     const char* halo = getenv("GANCE_HALO");  // GANCE_HALO=0 forces the per-tap kernel (A/B measurements)
     tc::g_use_halo = !(halo != nullptr && halo[0] == '0');
     return GANCE_OK;

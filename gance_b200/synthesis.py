@@ -18,6 +18,7 @@ Data flow per batch (NHWC activations, `mode` = "bf16" | "fp16" | "fp32"; DESIGN
       ToRGB + skip (+ uint8)        gance_torgb_skip
 """
 
+import os
 from typing import Dict, Iterable, Iterator, List, Optional, Sequence
 
 import numpy as np
@@ -52,6 +53,29 @@ def fold_up_weight(hwio: torch.Tensor) -> torch.Tensor:
     )
     phases = [torch.einsum("yk,xl,klio->oyxi", taps[py], taps[px], w) for py in range(2) for px in range(2)]
     return torch.cat(phases, dim=0).contiguous().float()
+
+
+PHASE_CHUNK = 64  # output channels per accumulator tile of gance_modconv3x3_up2_phase
+
+
+def phase_up_weight(hwio: torch.Tensor) -> torch.Tensor:
+    """
+    [3,3,Cin,Cout] (runtime-scaled HWIO) -> [9*Cout, Cin]: the B operand of the 4-phase transposed-convolution GEMM
+    (include/gance_b200.h, gance_modconv3x3_up2_phase). The input shifted by (dy,dx) feeds phase (a,b) through tap
+    w[iy(dy,a)][ix(dx,b)], iy(0,0)=2, iy(0,1)=1, iy(1,0)=0; rows are ordered shift -> 64-channel chunk -> phase
+    block (accumulator column blocks are [P01,P00,P10,P11]) -> channel.
+    """
+    tap = {(0, 0): 2, (0, 1): 1, (1, 0): 0}
+    block_phase = [(0, 1), (0, 0), (1, 0), (1, 1)]
+    shifts = [((0, 0), [0, 1, 2, 3]), ((1, 0), [0, 1]), ((0, 1), [1, 2]), ((1, 1), [1])]
+    cout = hwio.shape[3]
+    rows = []
+    for (dy, dx), blocks in shifts:
+        for chunk in range(cout // PHASE_CHUNK):
+            for block in blocks:
+                a, b = block_phase[block]
+                rows.append(hwio[tap[(dy, a)], tap[(dx, b)]][:, chunk * PHASE_CHUNK: (chunk + 1) * PHASE_CHUNK].t())
+    return torch.cat(rows, dim=0).contiguous()
 
 
 def _ptr(tensor: Optional[torch.Tensor]) -> Optional[int]:
@@ -108,6 +132,8 @@ class GeneratorOnDevice:
             self.conv_wsq.append((hwio * hwio).sum(dim=(0, 1)).contiguous())  # [Cin,Cout]
             if self.mode == "fp32":
                 self.conv_w.append(hwio.contiguous())  # [3,3,Cin,Cout]
+            elif conv.up and self._use_phase(conv):
+                self.conv_w.append(phase_up_weight(hwio).to(self.torch_dtype))  # [9*Cout,Cin]
             elif conv.up:
                 self.conv_w.append(fold_up_weight(hwio).to(self.torch_dtype))  # [4*Cout,3,3,Cin]
             else:
@@ -129,6 +155,19 @@ class GeneratorOnDevice:
             self.rgb_bias.append(f32(v[f"{rgb.name}/bias"]))
 
         self._build_style_tables()
+
+    @staticmethod
+    def _use_phase(conv) -> bool:
+        """
+        Up-convolutions that run as the 4-phase GEMM + FIR pass: those with enough input channels that the 4x fewer MACs
+        outweigh the extra HBM round trip of t (measured on B200, profiles/README.md: 64^2..256^2 win, 512^2 with
+        Cin = 128 does not). GANCE_UP=folded / GANCE_UP=phase force one form (A/B measurements).
+        """
+        forced = os.environ.get("GANCE_UP", "")
+        eligible = conv.in_resolution >= 32 and conv.in_channels % 64 == 0 and conv.out_channels % 64 == 0
+        if forced == "folded" or not eligible:
+            return False
+        return forced == "phase" or conv.in_channels >= 256
 
     def _build_style_tables(self) -> None:
         """Concatenated affine weights + chunk descriptors for gance_styles_all (include/gance_b200.h)."""
@@ -322,14 +361,26 @@ class GeneratorOnDevice:
                                                  styles[up_i].data_ptr(), x_scaled.data_ptr(), stream),
                         f"gance_scale_channels({side_in})",
                     )
-                _lib.check(
-                    lib.gance_modconv3x3_up2_folded(x_scaled.data_ptr(), code, batch, side_in, side_in, up.in_channels,
-                                                    up.out_channels, self.conv_w[up_i].data_ptr(),
-                                                    demods[up_i].data_ptr(), _ptr(nz), nz_stride,
-                                                    self.conv_strength[up_i], self.conv_bias[up_i].data_ptr(),
-                                                    styles[conv_i].data_ptr(), x_up.data_ptr(), stream),
-                    f"gance_modconv3x3_up2_folded({side})",
-                )
+                if self._use_phase(up):
+                    scratch = self._buffer("phase_t", (batch * (side + 2) * (side + 2) * up.out_channels,), dt)
+                    _lib.check(
+                        lib.gance_modconv3x3_up2_phase(x_scaled.data_ptr(), code, batch, side_in, side_in, up.in_channels,
+                                                       up.out_channels, self.conv_w[up_i].data_ptr(),
+                                                       demods[up_i].data_ptr(), _ptr(nz), nz_stride,
+                                                       self.conv_strength[up_i], self.conv_bias[up_i].data_ptr(),
+                                                       styles[conv_i].data_ptr(), scratch.data_ptr(), x_up.data_ptr(),
+                                                       stream),
+                        f"gance_modconv3x3_up2_phase({side})",
+                    )
+                else:
+                    _lib.check(
+                        lib.gance_modconv3x3_up2_folded(x_scaled.data_ptr(), code, batch, side_in, side_in,
+                                                        up.in_channels, up.out_channels, self.conv_w[up_i].data_ptr(),
+                                                        demods[up_i].data_ptr(), _ptr(nz), nz_stride,
+                                                        self.conv_strength[up_i], self.conv_bias[up_i].data_ptr(),
+                                                        styles[conv_i].data_ptr(), x_up.data_ptr(), stream),
+                        f"gance_modconv3x3_up2_folded({side})",
+                    )
             self._mark(f"{side}/conv0_up")
             nz, nz_stride = layer_noise(conv_i, side)
             is_last = block == last

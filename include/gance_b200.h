@@ -159,6 +159,22 @@ int gance_modconv3x3_up2_folded(const void* x, int dtype, int batch, int h_in, i
                                 float noise_strength, const float* bias, const float* next_styles,
                                 void* out, void* stream);
 
+/* ---- up-convolution at its algorithmic cost: 4-phase transposed-convolution GEMM + FIR pass -------------------------
+ * The folded form above executes 36 Cin*Cout MACs per input pixel; upsample_conv_2d needs 9. With
+ * t = conv2d_transpose(x, flip(w), stride 2) (upfirdn_2d.py:upsample_conv_2d), phase (a,b) of t at cell (m,n) is
+ *   t[2m+a, 2n+b] = sum_{dy,dx in {0,1}} x[m-dy, n-dx] * w[iy(dy,a)][ix(dx,b)],  iy(0,0)=2, iy(0,1)=1, iy(1,0)=0
+ * so the input shifted by (dy,dx) feeds 4/2/2/1 phases: one tcgen05 GEMM row per cell with columns
+ * [P01|P00|P10|P11] x 64 channels and MMAs of N = 256/128/128/64. Launch 1 writes t*demod as 16-bit NHWC into
+ * scratch [B,2H+2,2W+2,Cout]; launch 2 applies the [1,3,3,1] FIR (pad 1,1) + noise + bias + lrelu*sqrt(2) + next_styles.
+ *   x [B,H,W,Cin] ALREADY multiplied by this layer's styles; H >= 8, W >= 16, Cin % 64 == 0, Cout % 64 == 0
+ *   weight_phase [9*Cout][Cin]: rows ordered shift (0,0),(1,0),(0,1),(1,1) -> 64-channel chunk -> phase block ->
+ *   channel (gance_b200/synthesis.py:phase_up_weight), pre-multiplied by 1/sqrt(9*Cin); GANCE_BF16 / GANCE_F16 only. */
+int gance_modconv3x3_up2_phase(const void* x, int dtype, int batch, int h_in, int w_in, int c_in,
+                               int c_out, const void* weight_phase, const float* demod,
+                               const float* noise, long long noise_batch_stride, float noise_strength,
+                               const float* bias, const float* next_styles, void* scratch, void* out,
+                               void* stream);
+
 /* ---- Conv1 + ToRGB + skip (+ uint8) in one kernel ------------------------------------------------
  * gance_modconv3x3 (SAME) whose epilogue also evaluates torgb() on the fp32 activations it has in
  * registers: rgb = sum_co v[co] * rgb_styles[b,co] * rgb_weight[co,:] + rgb_bias, y = upsample_2d(y_prev)

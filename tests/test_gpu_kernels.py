@@ -425,3 +425,46 @@ def test_normal_noise_matches_philox_box_muller_restatement(lib):
     assert torch.equal(out, again)
     _lib.check(lib.gance_normal_noise(again.data_ptr(), count, seed, offset + count // 4, stream()), "gance_normal_noise")
     assert not torch.equal(out, again) and abs(float((out * again).mean())) < 4e-3
+
+
+@pytest.mark.parametrize("mode", ["bf16", "fp16"])
+@pytest.mark.parametrize("cin,cout,side,batch", [(64, 64, 16, 2), (128, 64, 32, 1), (256, 128, 24, 3), (512, 256, 16, 2)])
+def test_phase_up_convolution_matches_oracle(lib, mode, cin, cout, side, batch):
+    """gance_scale_channels + gance_modconv3x3_up2_phase (4-phase transposed-conv GEMM, then FIR pass) against the
+    transposed-conv + upfirdn oracle; side 24 exercises ragged cell tiles (25 cells = 2 x 4 tiles of 16 x 8)."""
+    from gance_b200.synthesis import phase_up_weight
+
+    code, dt = MODE_CODES[mode]
+    g = torch.Generator().manual_seed(13)
+    x = torch.randn(batch, cin, side, side, dtype=F64, generator=g)
+    wplus, weight, mod_w, mod_b = _style_case(cin, cout, batch, 14)
+    bias = torch.randn(cout, dtype=F64, generator=g) * 0.1
+    noise = torch.randn(batch, 2 * side, 2 * side, dtype=F64, generator=g)
+    nxt = torch.randn(batch, cout, dtype=F64, generator=g)
+    strength = 0.05
+    x_dev = dev(x.permute(0, 2, 3, 1), dt)
+    x_used = x_dev.double().cpu().permute(0, 3, 1, 2)
+    s, d = run_style_demod(lib, wplus, 1, weight, mod_w, mod_b)
+    want = ref.modulated_conv2d_layer(x_used, wplus[:, 1], weight, mod_w, mod_b, up=True)
+    want = want + noise.float().double()[:, None] * np.float32(strength)
+    want = ref.apply_bias_act(want, bias, act="lrelu") * nxt.float().double()[:, :, None, None]
+    w_phase = dev(phase_up_weight(ref.get_weight(weight).float()), dt)
+    assert w_phase.shape == (9 * cout, cin)
+    x_scaled = torch.empty_like(x_dev)
+    _lib.check(lib.gance_scale_channels(x_dev.data_ptr(), code, batch, side, side, cin, s.data_ptr(),
+                                        x_scaled.data_ptr(), stream()), "gance_scale_channels")
+    scratch = torch.full((batch, 2 * side + 2, 2 * side + 2, cout), float("nan"), device="cuda", dtype=dt)
+    out = torch.full((batch, 2 * side, 2 * side, cout), float("nan"), device="cuda", dtype=dt)
+    _lib.check(
+        lib.gance_modconv3x3_up2_phase(x_scaled.data_ptr(), code, batch, side, side, cin, cout, w_phase.data_ptr(),
+                                       d.data_ptr(), dev(noise).data_ptr(), 4 * side * side, strength,
+                                       dev(bias).data_ptr(), dev(nxt).data_ptr(), scratch.data_ptr(), out.data_ptr(),
+                                       stream()),
+        "gance_modconv3x3_up2_phase",
+    )
+    torch.cuda.synchronize()
+    assert not torch.isnan(scratch.float()).any(), "phase GEMM left part of t unwritten"
+    assert float(scratch[:, -1].float().abs().max()) == 0.0 and float(scratch[:, :, -1].float().abs().max()) == 0.0
+    assert not torch.isnan(out.float()).any(), "FIR pass left output unwritten"
+    tol = {"bf16": 2.0 ** -5, "fp16": 2.0 ** -8}[mode]  # weights, scaled activations, t and the output are each rounded once
+    assert rel_err(out.permute(0, 3, 1, 2), want) < tol

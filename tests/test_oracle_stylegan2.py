@@ -157,3 +157,37 @@ def test_uint8_conversion_truncates_and_saturates():
     x = torch.tensor([-2.0, -1.0, -0.999, 0.0, 0.0039, 0.999, 1.0, 3.0], dtype=F64).reshape(1, 1, 1, 8).repeat(1, 3, 1, 1)
     got = ref.convert_images_to_uint8(x)[0, 0, :, 0]
     assert got.tolist() == [0, 0, 0, 128, 128, 255, 255, 255]
+
+
+def test_phase_weight_matrix_reproduces_the_transposed_convolution():
+    """
+    gance_b200.synthesis.phase_up_weight: the [9*Cout, Cin] B operand of the 4-phase GEMM, emulated here in float64
+    (cells x shifts x column blocks exactly as the kernel walks them) + the [1,3,3,1] FIR, equals upsample_conv_2d.
+    """
+    from gance_b200.synthesis import PHASE_CHUNK, phase_up_weight
+
+    g = torch.Generator().manual_seed(5)
+    batch, cin, cout, side = 2, 8, 2 * PHASE_CHUNK, 5
+    x = torch.randn(batch, cin, side, side, dtype=torch.float64, generator=g)
+    w = torch.randn(3, 3, cin, cout, dtype=torch.float64, generator=g)
+    want = torch.stack([ref.upsample_conv_2d(x[i: i + 1], w)[0] for i in range(batch)])
+    wp = phase_up_weight(w)
+    assert wp.shape == (9 * cout, cin)
+    xp = F.pad(x, (1, 1, 1, 1))
+    t = torch.zeros(batch, cout, 2 * side + 2, 2 * side + 2, dtype=torch.float64)
+    block_phase = [(0, 1), (0, 0), (1, 0), (1, 1)]
+    bases, counts, firsts = [0, 4, 6, 8], [4, 2, 2, 1], [0, 0, 1, 1]
+    for sh in range(4):
+        dy, dx = sh & 1, sh >> 1
+        xs = xp[:, :, 1 - dy: 2 - dy + side, 1 - dx: 2 - dx + side]  # x[m-dy, n-dx] for cells m,n in [0, side]
+        for chunk in range(cout // PHASE_CHUNK):
+            row0 = bases[sh] * cout + chunk * counts[sh] * PHASE_CHUNK
+            for j in range(counts[sh]):
+                a, b = block_phase[firsts[sh] + j]
+                rows = wp[row0 + j * PHASE_CHUNK: row0 + (j + 1) * PHASE_CHUNK]  # [64, Cin]
+                t[:, chunk * PHASE_CHUNK: (chunk + 1) * PHASE_CHUNK, a::2, b::2] += torch.einsum("bimn,oi->bomn", xs, rows)
+    assert float(t[:, :, -1].abs().max()) == 0.0 and float(t[:, :, :, -1].abs().max()) == 0.0
+    f = torch.tensor([0.25, 0.75, 0.75, 0.25], dtype=torch.float64)
+    tp = F.pad(t, (1, 0, 1, 0))
+    out = sum(f[a] * f[b] * tp[:, :, a: a + 2 * side, b: b + 2 * side] for a in range(4) for b in range(4))
+    assert float((out - want).abs().max()) < 1e-12
