@@ -67,7 +67,8 @@ unsigned long long gance_launch_count(void);
  * networks_stylegan2.G_mapping + the 'Truncation' block of G_main, as run by Gs.run
  * (network_functions.py:151-158). z [B,512] f32 -> wplus [B,num_ws,512] f32.
  * weights [8][512][512] (in,out) and biases [8][512] are pre-multiplied by their runtime
- * coefficients (lrmul/sqrt(fan_in), lrmul). psi == 1 skips the lerp. */
+ * coefficients (lrmul/sqrt(fan_in), lrmul). psi == 1 skips the lerp. One launch per dense layer (the batch
+ * spreads each layer over every SM); the layers ping-pong between rows 0 and 1 of w+, so num_ws >= 2. */
 int gance_mapping(const float* z, int batch, const float* weights, const float* biases,
                   const float* dlatent_avg, float truncation_psi, int num_ws, float* wplus,
                   void* stream);

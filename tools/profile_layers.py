@@ -19,21 +19,23 @@ def main() -> None:
     ap.add_argument("--batch", type=int, default=32)
     ap.add_argument("--mode", default="bf16")
     ap.add_argument("--iters", type=int, default=5)
+    ap.add_argument("--perturbed", action="store_true", help="non-zero noise strengths / biases (what bench.py runs)")
+    ap.add_argument("--noise", default="const", choices=["const", "random", "none"])
     args = ap.parse_args()
     device = torch.device("cuda", 0)
     torch.cuda.set_device(device)
     spec = GeneratorSpec(args.resolution)
-    gen = GeneratorOnDevice(spec, random_init_variables(spec, 0), device, mode=args.mode)
+    gen = GeneratorOnDevice(spec, random_init_variables(spec, 0, perturbed=args.perturbed), device, mode=args.mode)
     wplus = torch.randn(args.batch, spec.num_ws, 512, device=device)
     for _ in range(2):
-        gen.synthesis(wplus)
+        gen.synthesis(wplus, noise_mode=args.noise)
     torch.cuda.synchronize()
     totals = {}
     for _ in range(args.iters):
         gen.profile_events = []
         start = torch.cuda.Event(enable_timing=True)
         start.record()
-        gen.synthesis(wplus)
+        gen.synthesis(wplus, noise_mode=args.noise)
         torch.cuda.synchronize()
         prev = start
         for name, event in gen.profile_events:
