@@ -49,7 +49,7 @@ FALLBACK_PEAKS = {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustain
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=32)
@@ -140,6 +140,37 @@ def track_latents(seconds: float, device):
         alpha=0.25, fft_roll_enabled=True, fft_amplitude_range=(-5, 5), time_series_audio_vectors=scaled,
         vector_length=512, network_indices=[0])
     return result.latents
+
+
+def audio_half_report(seconds: float, device):
+    """
+    The audio half of the path (WAV -> resample -> STFT -> dB -> resample -> min-max -> smoothing -> roll -> blend ->
+    z latents) timed on our kernels (wall clock incl. the host-side RMS/noise steps, after one warm-up) next to the CPU
+    restatement of the reference's numpy/scipy code (oracle/audio_ref.py, pinned against the reference's own Python) on
+    the same track. Negligible next to synthesis; reported for completeness.
+    """
+    import torch
+
+    from gance_b200 import synthetic
+    from oracle import audio_ref
+
+    wav = synthetic.chirp_wav(seconds)
+    track_latents(seconds, device)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    latents = track_latents(seconds, device)
+    torch.cuda.synchronize()
+    gpu_s = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    audio = audio_ref.scale_wav_for_video(audio_ref.wav_to_float32(wav), 44100, 512, frames_per_second=60.0)
+    want = audio_ref.alpha_blend_vectors_max_rms_power_audio(0.25, True, (-5, 5), audio, 512, [0])
+    cpu_s = time.perf_counter() - t0
+    got = latents.double().cpu().numpy().reshape(-1)
+    ref = np.asarray(want.combined, dtype=np.float64).reshape(-1)
+    frames = int(latents.shape[0])
+    return {"track_seconds": seconds, "frames": frames, "b200_ms": gpu_s * 1e3, "cpu_port_ms": cpu_s * 1e3,
+            "b200_frames_per_s": frames / gpu_s, "cpu_port_frames_per_s": frames / cpu_s,
+            "max_rel_err_vs_cpu_port": float(np.abs(got - ref).max() / np.abs(ref).max()), "cores": 1}
 
 
 def cpu_frames_per_second(resolution: int, frames: int, seed: int = 0):
@@ -346,6 +377,13 @@ def main():
                         "sample": f"{frames} frames of the same {res}^2 generator, batch 1, torch-CPU fp32 restatement "
                                   f"(oracle/stylegan2_ref.py), {seconds:.1f} s"}
 
+    audio = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            audio = audio_half_report(args.track_seconds, device)
+        except Exception as error:  # pylint: disable=broad-except
+            audio = {"error": repr(error)}
+
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -360,6 +398,7 @@ def main():
                 "realtime_multiple_at_60fps": value / 60.0,
             },
             "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu_baseline,
+            "audio_half": audio,
             "clocks": clocks.summary(),
         }
         print(json.dumps(line), flush=True)
