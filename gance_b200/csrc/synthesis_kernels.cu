@@ -423,7 +423,9 @@ __device__ __forceinline__ float2 box_muller(uint32_t a, uint32_t b) {
 }
 
 __global__ void __launch_bounds__(256) normal_noise_kernel(float4* __restrict__ out, size_t groups, uint2 key,
-                                                           unsigned long long offset) {
+                                                           unsigned long long offset,
+                                                           const unsigned long long* __restrict__ counter) {
+    if (counter != nullptr) offset += *counter;  // device-resident stream position (CUDA-graph replays must not repeat noise)
     for (size_t g = blockIdx.x * (size_t)blockDim.x + threadIdx.x; g < groups; g += (size_t)gridDim.x * blockDim.x) {
         const unsigned long long c = g + offset;
         const uint4 r = philox4x32_10(make_uint4((uint32_t)c, (uint32_t)(c >> 32), 0u, 0u), key);
@@ -431,6 +433,8 @@ __global__ void __launch_bounds__(256) normal_noise_kernel(float4* __restrict__ 
         out[g] = make_float4(a.x, a.y, b.x, b.y);
     }
 }
+
+__global__ void advance_counter_kernel(unsigned long long* counter, unsigned long long by) { *counter += by; }
 
 // ------------------------------------------------------------------------------------------------
 // fp32 validation-mode 3x3 convolution on CUDA cores (the numerical yard-stick for the tcgen05
@@ -756,8 +760,22 @@ int gance_normal_noise(float* out, long long count, unsigned long long seed, uns
     GANCE_REQUIRE(aligned16(out), GANCE_E_ALIGN, "gance_normal_noise: out must be 16-byte aligned");
     const size_t groups = (size_t)count / 4;
     normal_noise_kernel<<<grid_for(groups, 256), 256, 0, (cudaStream_t)stream>>>(
-        reinterpret_cast<float4*>(out), groups, make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)), offset);
+        reinterpret_cast<float4*>(out), groups, make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)), offset, nullptr);
     return check_launch("normal_noise_kernel");
+}
+
+int gance_normal_noise_next(float* out, long long count, unsigned long long seed, unsigned long long* counter, void* stream) {
+    GANCE_REQUIRE(is_initialised(), GANCE_E_NOT_INIT, "gance_init() has not been called");
+    GANCE_REQUIRE(out != nullptr && counter != nullptr, GANCE_E_NULL, "gance_normal_noise_next: NULL pointer");
+    GANCE_REQUIRE(count > 0 && count % 4 == 0, GANCE_E_SHAPE, "gance_normal_noise_next: count %lld must be a positive multiple of 4", count);
+    GANCE_REQUIRE(aligned16(out), GANCE_E_ALIGN, "gance_normal_noise_next: out must be 16-byte aligned");
+    const size_t groups = (size_t)count / 4;
+    normal_noise_kernel<<<grid_for(groups, 256), 256, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<float4*>(out), groups, make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)), 0ull, counter);
+    int rc = check_launch("normal_noise_kernel");
+    if (rc != GANCE_OK) return rc;
+    advance_counter_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(counter, (unsigned long long)groups);
+    return check_launch("advance_counter_kernel");
 }
 
 }  // extern "C"

@@ -101,7 +101,10 @@ class GeneratorOnDevice:
         self._buffers: Dict[tuple, torch.Tensor] = {}
         self.profile_events: Optional[list] = None  # set to [] to collect (name, cuda event) marks
         self.noise_seed = 0x5EED_0000_0000_0000 | (id(self) & 0xFFFF_FFFF)  # Philox key of the "random" noise mode
-        self.noise_offset = 0  # Philox counter: advances with every batch so no two calls share noise
+        # Philox stream position, on the device: advances with every batch (also across CUDA-graph replays)
+        self.noise_counter = torch.zeros(1, dtype=torch.int64, device=device)
+        self._graphs: Dict[tuple, tuple] = {}
+        self.launches_per_replay = 0
         self._upload(variables)
 
     # ---- weights ---------------------------------------------------------------------------------
@@ -212,6 +215,7 @@ class GeneratorOnDevice:
         return buf
 
     def release_buffers(self) -> None:
+        self._graphs.clear()  # captured graphs hold the work buffers' addresses
         self._buffers.clear()
 
     def _stream(self) -> int:
@@ -290,9 +294,8 @@ class GeneratorOnDevice:
             total = sum(batch * side * side for _, side in sizes)
             if total:
                 flat = self._buffer("noise_random", ((total + 3) // 4 * 4,), torch.float32)
-                _lib.check(lib.gance_normal_noise(flat.data_ptr(), flat.numel(), self.noise_seed, self.noise_offset,
-                                                  stream), "gance_normal_noise")
-                self.noise_offset += flat.numel() // 4
+                _lib.check(lib.gance_normal_noise_next(flat.data_ptr(), flat.numel(), self.noise_seed,
+                                                       self.noise_counter.data_ptr(), stream), "gance_normal_noise_next")
                 start = 0
                 for i, side in sizes:
                     random_noise[i] = flat[start: start + batch * side * side].view(batch, side, side)
@@ -431,6 +434,32 @@ class GeneratorOnDevice:
         """Batched `Gs.run(z, None, truncation_psi=1.2)` (network_functions.py:151-158)."""
         return self.synthesis(self.mapping(z, truncation_psi), noise_mode=noise_mode, **kwargs)
 
+    def run_vectors_graphed(self, z: torch.Tensor, out: torch.Tensor, truncation_psi: float = 1.2,
+                            noise_mode: str = "random") -> torch.Tensor:
+        """
+        `run_vectors` replayed from a CUDA graph: the ~45 launches of a batch are captured once per (batch size,
+        output buffer, psi, noise mode) and replayed with one driver call - no per-launch CPU cost and back-to-back
+        kernels on the device. `z` is copied into the graph's static input; frames land in `out`.
+        """
+        z = z.to(self.device, torch.float32).reshape(-1, 512)
+        key = (z.shape[0], out.data_ptr(), float(truncation_psi), noise_mode)
+        entry = self._graphs.get(key)
+        if entry is None:
+            static_z = z.clone()
+            self.run_vectors(static_z, truncation_psi=truncation_psi, noise_mode=noise_mode, out=out)  # warm-up: buffers
+            torch.cuda.current_stream(self.device).synchronize()
+            graph = torch.cuda.CUDAGraph()
+            launches_before = _lib.launch_count()
+            with torch.cuda.graph(graph):
+                self.run_vectors(static_z, truncation_psi=truncation_psi, noise_mode=noise_mode, out=out)
+            self.launches_per_replay = _lib.launch_count() - launches_before  # kernels of ours inside one replay
+            entry = (graph, static_z)
+            self._graphs[key] = entry
+        graph, static_z = entry
+        static_z.copy_(z, non_blocking=True)
+        graph.replay()
+        return out
+
     def run_matrices(self, wplus: torch.Tensor, **kwargs):
         """Batched `Gs.components.synthesis.run(w+, randomize_noise=False)` (network_functions.py:167-169)."""
         return self.synthesis(wplus, noise_mode="const", **kwargs)
@@ -489,7 +518,7 @@ class BatchRenderer:
         self.bytes_h2d += array.size * 4
         out = self.frames_dev[slot][:n]
         if is_vectors:
-            gen.run_vectors(on_device, truncation_psi=self.truncation_psi, noise_mode=self.noise_mode or "random", out=out)
+            gen.run_vectors_graphed(on_device, out, truncation_psi=self.truncation_psi, noise_mode=self.noise_mode or "random")
         else:
             gen.synthesis(on_device, noise_mode=self.noise_mode or "const", out=out)
         computed = torch.cuda.Event()

@@ -209,6 +209,10 @@ int gance_to_uint8_nhwc(const float* y, int batch, int h, int w, uint8_t* frames
  * One launch fills the noise of every layer of a batch (the layers are slices of one buffer). */
 int gance_normal_noise(float* out, long long count, unsigned long long seed, unsigned long long offset,
                        void* stream);
+/* The same stream with its position kept in device memory: offset = *counter, then *counter += count/4 (a second,
+ * one-thread launch). Two calls never share noise even when they are replays of one captured CUDA graph. */
+int gance_normal_noise_next(float* out, long long count, unsigned long long seed,
+                            unsigned long long* counter, void* stream);
 
 /* ---- audio: WAV samples -> float32 -> resampled so that one frame = vector_length samples --------
  * gance_pcm_to_float: music.read_wav_file (gance/vector_sources/music.py:190-205) +

@@ -177,3 +177,24 @@ def test_full_size_batch_properties():
     permuted = gen.synthesis(wplus[perm.to(wplus.device)], noise_mode="const")
     assert torch.equal(permuted, together[perm.to(together.device)])
     gen.release_buffers()
+
+
+def test_graph_replay_equals_eager_and_draws_fresh_noise():
+    """run_vectors_graphed (CUDA-graph replay of the same C-ABI calls) against the eager path."""
+    spec, variables, _, z = _case(64, 6, True, 4)
+    gen = GeneratorOnDevice(spec, variables, _device(), mode="fp16")
+    z_dev = torch.as_tensor(z, dtype=torch.float32, device=gen.device)
+    eager = gen.run_vectors(z_dev, noise_mode="const").clone()
+    out = torch.empty_like(eager)
+    for _ in range(3):  # capture, then two replays
+        gen.run_vectors_graphed(z_dev, out, noise_mode="const")
+        assert torch.equal(out, eager)
+    other = torch.as_tensor(z[::-1].copy(), dtype=torch.float32, device=gen.device)
+    gen.run_vectors_graphed(other, out, noise_mode="const")  # new input through the static buffer
+    assert torch.equal(out, torch.flip(eager, [0]))
+    assert gen.launches_per_replay > 10
+    # random noise: the Philox position lives on the device, so replays never repeat it
+    first = gen.run_vectors_graphed(z_dev, out, noise_mode="random").clone()
+    second = gen.run_vectors_graphed(z_dev, out, noise_mode="random").clone()
+    third = gen.run_vectors_graphed(z_dev, out, noise_mode="random").clone()
+    assert not torch.equal(first, second) and not torch.equal(second, third)
