@@ -225,17 +225,41 @@ upconv_phase_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
 }
 
 // ---- pass 2: [1,3,3,1] FIR over t + noise + bias + leaky-ReLU + next-layer style ---------------------------------------
-// HBM-bound by construction: t is read once, out written once. Persistent CTAs; one producer thread streams
-// (8+3) x (32+3)-pixel x 64-channel tiles of t into a 3-stage shared-memory ring with TMA (coordinate -1 = the FIR's zero
-// padding, filled by the TMA unit), 256 consumer threads each filter 2x2 output pixels x 8 channels separably from the
-// tile (25 conflict-free LDS.128, the 6.25x tap re-use hits shared memory, not L1/L2).
-constexpr int kFirTileW = 32, kFirTileH = 8, kFirC = 64, kFirStages = 3, kFirConsumers = 512;
+// HBM-bound by construction: t is read once, out written once. Persistent CTAs (two per SM); one producer thread streams
+// (8+3) x (32+3)-pixel x 64-channel tiles of t into a 2-stage shared-memory ring with TMA (coordinate -1 = the FIR's zero
+// padding, filled by the TMA unit). Each of the 256 consumer threads owns 4 channels x 2 adjacent output columns and
+// walks DOWN the tile: one t row = 5 LDS.64 + one horizontal filter (both x phases), a 4-row sliding window of those
+// gives one output row per step - every t row is converted and filtered horizontally exactly once per thread
+// (16 instructions per output element; the first version recomputed it per 2x2 block: 27).
+constexpr int kFirTileW = 32, kFirTileH = 8, kFirC = 64, kFirStages = 2, kFirConsumers = 256;
 constexpr int kFirTW = kFirTileW + 3, kFirTH = kFirTileH + 3;
 constexpr int kFirStageBytes = ((kFirTW * kFirTH * kFirC * 2) + 1023) / 1024 * 1024;
 constexpr int kFirSmemBytes = kFirStages * kFirStageBytes + 2 * kFirStages * 8 + 1024;
 
 template <typename T>
-__global__ void __launch_bounds__(kFirConsumers + 32, 1)
+__device__ __forceinline__ void unpack4(uint2 raw, float (&v)[4]);
+template <>
+__device__ __forceinline__ void unpack4<__half>(uint2 raw, float (&v)[4]) {
+    const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&raw.x));
+    const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&raw.y));
+    v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+}
+template <>
+__device__ __forceinline__ void unpack4<__nv_bfloat16>(uint2 raw, float (&v)[4]) {
+    v[0] = __uint_as_float(raw.x << 16); v[1] = __uint_as_float(raw.x & 0xffff0000u);
+    v[2] = __uint_as_float(raw.y << 16); v[3] = __uint_as_float(raw.y & 0xffff0000u);
+}
+__device__ __forceinline__ uint2 pack4(const float (&v)[4], __half*) {
+    const __half2 a = __floats2half2_rn(v[0], v[1]), b = __floats2half2_rn(v[2], v[3]);
+    return make_uint2(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b));
+}
+__device__ __forceinline__ uint2 pack4(const float (&v)[4], __nv_bfloat16*) {
+    const __nv_bfloat162 a = __floats2bfloat162_rn(v[0], v[1]), b = __floats2bfloat162_rn(v[2], v[3]);
+    return make_uint2(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b));
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kFirConsumers + 32, 2)
 upfir_act_kernel(const __grid_constant__ CUtensorMap tmap_t, int batch, int h_out, int w_out, int channels,
                  const float* __restrict__ noise, long long noise_batch_stride, float noise_strength,
                  const float* __restrict__ bias, const float* __restrict__ next_styles, T* __restrict__ out) {
@@ -282,76 +306,58 @@ upfir_act_kernel(const __grid_constant__ CUtensorMap tmap_t, int batch, int h_ou
         return;
     }
     const int tid = threadIdx.x, lane = tid & 31;
+    const int quad = tid & 15, bj = tid >> 4;  // 4 channels, output columns 2*bj and 2*bj + 1 of the tile
     int stage = 0;
     uint32_t phase = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         int cc, b, y0, x0;
         decode(tile, cc, b, y0, x0);
+        const int c0 = cc * kFirC + quad * 4;
+        const int x = x0 + 2 * bj;
+        const float4 b4 = __ldg(reinterpret_cast<const float4*>(bias + c0));
+        float4 s4 = make_float4(1.f, 1.f, 1.f, 1.f);
+        if (next_styles) s4 = __ldg(reinterpret_cast<const float4*>(next_styles + (size_t)b * channels + c0));
+        const float bs[4] = {b4.x, b4.y, b4.z, b4.w};
+        const float st[4] = {s4.x * kLreluGain, s4.y * kLreluGain, s4.z * kLreluGain, s4.w * kLreluGain};
         const float* noise_b = noise ? noise + (size_t)b * noise_batch_stride : nullptr;
+        T* out_b = out + ((size_t)b * h_out * w_out) * channels + c0;
         mbar_wait(full_bar + stage, phase);
-        const uint32_t tile_addr = smem_u32(smem + stage * kFirStageBytes);
-#pragma unroll 1
-        for (int item = tid; item < (kFirTileW / 2) * (kFirTileH / 2) * (kFirC / 8); item += kFirConsumers) {
-            const int g = item & 7, bj = (item >> 3) & 15, bi = item >> 7;
-            const int c0 = cc * kFirC + g * 8;
-            // rows stream through: horizontal filter of one t row (both x phases), then its vertical contributions
-            float acc[2][2][8];
+        const uint32_t column_addr = smem_u32(smem + stage * kFirStageBytes) + (uint32_t)((2 * bj * kFirC + quad * 4) * 2);
+        float window[4][2][4];  // horizontally filtered t rows r-3 .. r (slot = r & 3), both x phases, 4 channels
 #pragma unroll
-            for (int q = 0; q < 8; ++q) acc[0][0][q] = acc[0][1][q] = acc[1][0][q] = acc[1][1][q] = 0.f;
+        for (int r = 0; r < kFirTH; ++r) {
+            float v[5][4];
 #pragma unroll
-            for (int r = 0; r < 5; ++r) {
-                float v[5][8];
-#pragma unroll
-                for (int c = 0; c < 5; ++c) {
-                    Vec<T> raw;
-                    const uint32_t addr = tile_addr + (uint32_t)((((2 * bi + r) * kFirTW + 2 * bj + c) * kFirC + g * 8) * 2);
-                    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
-                                 : "=r"(raw.raw.x), "=r"(raw.raw.y), "=r"(raw.raw.z), "=r"(raw.raw.w)
-                                 : "r"(addr));
-                    raw.to_float(v[c]);
-                }
-#pragma unroll
-                for (int q = 0; q < 8; ++q) {
-                    const float h0 = 0.25f * (v[0][q] + v[3][q]) + 0.75f * (v[1][q] + v[2][q]);
-                    const float h1 = 0.25f * (v[1][q] + v[4][q]) + 0.75f * (v[2][q] + v[3][q]);
-                    if (r < 4) {  // output row 2*bi uses t rows r = 0..3 with f[r]
-                        const float f = (r == 0 || r == 3) ? 0.25f : 0.75f;
-                        acc[0][0][q] = fmaf(f, h0, acc[0][0][q]);
-                        acc[0][1][q] = fmaf(f, h1, acc[0][1][q]);
-                    }
-                    if (r > 0) {  // output row 2*bi+1 uses t rows r = 1..4 with f[r-1]
-                        const float f = (r == 1 || r == 4) ? 0.25f : 0.75f;
-                        acc[1][0][q] = fmaf(f, h0, acc[1][0][q]);
-                        acc[1][1][q] = fmaf(f, h1, acc[1][1][q]);
-                    }
-                }
-            }
-            float bs[8], st[8];
-#pragma unroll
-            for (int q = 0; q < 8; q += 4) {
-                const float4 b4 = __ldg(reinterpret_cast<const float4*>(bias + c0 + q));
-                bs[q] = b4.x; bs[q + 1] = b4.y; bs[q + 2] = b4.z; bs[q + 3] = b4.w;
-                float4 s4 = make_float4(1.f, 1.f, 1.f, 1.f);
-                if (next_styles) s4 = __ldg(reinterpret_cast<const float4*>(next_styles + (size_t)b * channels + c0 + q));
-                st[q] = s4.x * kLreluGain; st[q + 1] = s4.y * kLreluGain; st[q + 2] = s4.z * kLreluGain; st[q + 3] = s4.w * kLreluGain;
+            for (int c = 0; c < 5; ++c) {
+                uint2 raw;
+                asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];"
+                             : "=r"(raw.x), "=r"(raw.y)
+                             : "r"(column_addr + (uint32_t)((r * kFirTW + c) * kFirC * 2)));
+                unpack4<T>(raw, v[c]);
             }
 #pragma unroll
-            for (int py = 0; py < 2; ++py) {
+            for (int q = 0; q < 4; ++q) {
+                window[r & 3][0][q] = 0.25f * (v[0][q] + v[3][q]) + 0.75f * (v[1][q] + v[2][q]);
+                window[r & 3][1][q] = 0.25f * (v[1][q] + v[4][q]) + 0.75f * (v[2][q] + v[3][q]);
+            }
+            if (r >= 3) {  // output row y0 + r - 3 = t rows r-3 .. r with [1,3,3,1]/4
+                const int y = y0 + r - 3;
+                if (y < h_out && x < w_out) {
+                    float2 nz = make_float2(0.f, 0.f);
+                    if (noise_b) nz = __ldg(reinterpret_cast<const float2*>(noise_b + (size_t)y * w_out + x));
 #pragma unroll
-                for (int px = 0; px < 2; ++px) {
-                    const int y = y0 + 2 * bi + py, x = x0 + 2 * bj + px;
-                    if (y < h_out && x < w_out) {
-                        const float nz = noise_b ? __ldg(noise_b + (size_t)y * w_out + x) * noise_strength : 0.f;
-                        float o[8];
+                    for (int px = 0; px < 2; ++px) {
+                        const float nzv = (px ? nz.y : nz.x) * noise_strength;
+                        float o[4];
 #pragma unroll
-                        for (int q = 0; q < 8; ++q) {
-                            float value = acc[py][px][q] + (nz + bs[q]);
+                        for (int q = 0; q < 4; ++q) {
+                            float value = 0.25f * (window[(r - 3) & 3][px][q] + window[r & 3][px][q]) +
+                                          0.75f * (window[(r - 2) & 3][px][q] + window[(r - 1) & 3][px][q]);
+                            value += nzv + bs[q];
                             value = fmaxf(value, value * kLreluAlpha);
                             o[q] = value * st[q];
                         }
-                        Vec<T> packed;
-                        packed.from_float(o);
-                        packed.store(out + (((size_t)b * h_out + y) * w_out + x) * channels + c0);
+                        *reinterpret_cast<uint2*>(out_b + ((size_t)y * w_out + x + px) * channels) = pack4(o, (T*)nullptr);
                     }
                 }
             }
@@ -419,7 +425,7 @@ static int launch_phase(const void* x, int batch, int h_in, int w_in, int c_in, 
         if (rc != GANCE_OK) return rc;
     }
     const int fir_tiles = batch * ((h_out + kFirTileH - 1) / kFirTileH) * ((w_out + kFirTileW - 1) / kFirTileW) * (c_out / kFirC);
-    const int fir_grid = fir_tiles < sm_count() ? fir_tiles : sm_count();
+    const int fir_grid = fir_tiles < 2 * sm_count() ? fir_tiles : 2 * sm_count();
     upfir_act_kernel<T><<<fir_grid, kFirConsumers + 32, kFirSmemBytes, stream>>>(tmap_t, batch, h_out, w_out, c_out, noise,
                                                                              noise_batch_stride, noise_strength, bias,
                                                                              next_styles, (T*)out);

@@ -163,14 +163,14 @@ class GeneratorOnDevice:
     def _use_phase(conv) -> bool:
         """
         Up-convolutions that run as the 4-phase GEMM + FIR pass: those with enough input channels that the 4x fewer MACs
-        outweigh the extra HBM round trip of t (measured on B200, profiles/README.md: 64^2..256^2 win, 512^2 with
-        Cin = 128 does not). GANCE_UP=folded / GANCE_UP=phase force one form (A/B measurements).
+        outweigh the extra HBM round trip of t (measured on B200, profiles/README.md: 64^2..256^2 win 1.4-1.9x; at 512^2,
+        Cin = 128, the two forms take the same time and the phase form executes a quarter of the MACs = less power). GANCE_UP=folded / GANCE_UP=phase force one form (A/B measurements).
         """
         forced = os.environ.get("GANCE_UP", "")
         eligible = conv.in_resolution >= 32 and conv.in_channels % 64 == 0 and conv.out_channels % 64 == 0
         if forced == "folded" or not eligible:
             return False
-        return forced == "phase" or conv.in_channels >= 256
+        return forced == "phase" or conv.in_channels >= 128
 
     def _build_style_tables(self) -> None:
         """Concatenated affine weights + chunk descriptors for gance_styles_all (include/gance_b200.h)."""
