@@ -842,6 +842,7 @@ int encode_tensor_map(CUtensorMap* map, const void* base, bool half_operands, in
 }
 int sm_count() { return g_num_sms; }
 int configure_phase_kernels();
+int configure_fused_kernels();
 
 }  // namespace tc
 
@@ -866,6 +867,7 @@ int init_tensor_core_path() {
     if ((rc = tc::configure_halo<64, 64, 3>()) != GANCE_OK) return rc;
     if ((rc = tc::configure_halo<32, 32, 4>()) != GANCE_OK) return rc;
     if ((rc = tc::configure_phase_kernels()) != GANCE_OK) return rc;
+    if ((rc = tc::configure_fused_kernels()) != GANCE_OK) return rc;
     const char* halo = getenv("GANCE_HALO");  // GANCE_HALO=0 forces the per-tap kernel (A/B measurements)
     tc::g_use_halo = !(halo != nullptr && halo[0] == '0');
     return GANCE_OK;

