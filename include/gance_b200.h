@@ -288,6 +288,20 @@ int gance_alpha_blend_wplus(const double* spec, const float* projected, int dupl
                             int vector_length, double* latents_f64, float* latents_f32,
                             void* stream);
 
+/* ---- output-side frame scaling: bicubic resize of uint8 NHWC frames ------------------------------------
+ * Replaces cv2.resize(image, (side, side), interpolation=cv2.INTER_CUBIC) in
+ * gance/image_sources/video_common.py:399-429 (resize_source; used by scale_square_source_duplicate, 432-455, from
+ * gance/projection_file_blend.py:184-199). Bit-exact with OpenCV's own 8-bit code path (resize.cpp: 11-bit fixed-point
+ * coefficients, integer horizontal pass, float vertical pass for the first floor(n/8)*8 elements of a destination row,
+ * integer tail; oracle/resize_ref.py).
+ *   src [B,src_h,src_w,3] u8 -> dst [B,dst_h,dst_w,3] u8 (dst 4-byte aligned)
+ *   xofs [dst_w] i32 / xcoef [dst_w,4] i16, yofs [dst_h] / ycoef [dst_h,4]: per-axis tap-1 source index and
+ *   round(c*2048) coefficients (gance_b200/image_sources/video_common.py:cubic_tables); 8-byte aligned tables.
+ *   win_w / win_h: the largest source extent, taps included, any 128-column / 16-row destination tile needs. */
+int gance_resize_cubic_u8(const uint8_t* src, int batch, int src_h, int src_w, uint8_t* dst, int dst_h,
+                          int dst_w, const int* xofs, const short* xcoef, const int* yofs,
+                          const short* ycoef, int win_w, int win_h, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

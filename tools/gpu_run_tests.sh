@@ -18,3 +18,4 @@ if [ "$1" != "quick" ]; then
 fi
 run conv_tc tests/test_gpu_kernels.py -k "tcgen05 or ((bf16 or fp16) and up_convolution)"
 run synthesis tests/test_gpu_synthesis.py
+run resize tests/test_gpu_resize.py
