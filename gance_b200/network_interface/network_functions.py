@@ -150,13 +150,16 @@ def _wrap_generator(generator: GeneratorOnDevice, alive: Optional[List[bool]] = 
             return to_host(matrices(array[None]))
         return to_host(matrices(array))
 
-    renderers: Dict[int, BatchRenderer] = {}
+    renderers: Dict[tuple, BatchRenderer] = {}
 
-    def render_batches(batches: Iterable[np.ndarray], max_batch: int = 32) -> Iterator[np.ndarray]:
+    def render_batches(batches: Iterable[np.ndarray], max_batch: int = 32,
+                       output_side_length: Optional[int] = None) -> Iterator[np.ndarray]:
         check_alive()
-        renderer = renderers.get(max_batch)
+        key = (max_batch, output_side_length)
+        renderer = renderers.get(key)
         if renderer is None:
-            renderer = renderers[max_batch] = BatchRenderer(generator, max_batch=max_batch, truncation_psi=TRUNCATION_PSI)
+            renderer = renderers[key] = BatchRenderer(generator, max_batch=max_batch, truncation_psi=TRUNCATION_PSI,
+                                                      output_side_length=output_side_length)
         return renderer.render(batches)
 
     return NetworkInterface(
@@ -312,14 +315,23 @@ class MultiNetwork:
         return batch_function(data)
 
     @_raise_exception_if_unloaded
-    def indexed_render_batches(self: "MultiNetwork", index: int, batches: Iterable[np.ndarray], max_batch: int = 32):
-        """Addition: stream batches of host latents of ONE network to host frames, copies overlapped."""
+    def indexed_render_batches(self: "MultiNetwork", index: int, batches: Iterable[np.ndarray], max_batch: int = 32,
+                               output_side_length: Optional[int] = None):
+        """
+        Addition: stream batches of host latents of ONE network to host frames, copies overlapped. With
+        `output_side_length` the frames are scaled on the device (bicubic, the reference's
+        `scale_square_source_duplicate`, gance/projection_file_blend.py:184-199) before they leave for the host.
+        """
         self._load_network_at_index(index)
         render = self._currently_loaded_network.network_interface.render_batches
         if render is None:
+            if output_side_length is not None:
+                raise RuntimeError("output_side_length needs the CUDA renderer (no CPU fallback)")
             generic = self._currently_loaded_network.network_interface.create_image_generic
             return (np.stack([generic(item) for item in batch]) for batch in batches)
-        return render(batches, max_batch)
+        if output_side_length is None:
+            return render(batches, max_batch)
+        return render(batches, max_batch, output_side_length)
 
     def load(self: "MultiNetwork") -> None:
         network_path = self._network_paths[self._currently_loaded_network_index]

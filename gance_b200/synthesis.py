@@ -504,7 +504,13 @@ class BatchRenderer:
     """
 
     def __init__(self, generator: GeneratorOnDevice, max_batch: int = 32, depth: int = 2,
-                 truncation_psi: float = 1.2, noise_mode: Optional[str] = None) -> None:
+                 truncation_psi: float = 1.2, noise_mode: Optional[str] = None,
+                 output_side_length: Optional[int] = None) -> None:
+        """
+        output_side_length: when given and different from the network's resolution, every batch is scaled on the
+        device with the bicubic kernel (what `scale_square_source_duplicate` does per frame with cv2 in the reference,
+        gance/projection_file_blend.py:184-199) before it leaves for the host, and `render` yields [n,S,S,3] arrays.
+        """
         self.generator = generator
         self.max_batch = max_batch
         self.depth = max(2, depth)
@@ -513,7 +519,17 @@ class BatchRenderer:
         dev, res = generator.device, generator.resolution
         self.copy_stream = torch.cuda.Stream(device=dev)
         self.frames_dev = [torch.empty((max_batch, res, res, 3), dtype=torch.uint8, device=dev) for _ in range(self.depth)]
-        self.frames_host = [torch.empty((max_batch, res, res, 3), dtype=torch.uint8).pin_memory() for _ in range(self.depth)]
+        self.output_side = res if output_side_length is None else int(output_side_length)
+        self.resizer = None
+        self.scaled_dev: List[torch.Tensor] = []
+        if self.output_side != res:
+            from gance_b200.image_sources.video_common import FrameResizer
+
+            self.resizer = FrameResizer(dev)
+            self.scaled_dev = [torch.empty((max_batch, self.output_side, self.output_side, 3), dtype=torch.uint8, device=dev)
+                               for _ in range(self.depth)]
+        side = self.output_side
+        self.frames_host = [torch.empty((max_batch, side, side, 3), dtype=torch.uint8).pin_memory() for _ in range(self.depth)]
         self.latents_host = [torch.empty((max_batch * generator.num_ws * 512,), dtype=torch.float32).pin_memory()
                              for _ in range(self.depth)]
         self.done = [torch.cuda.Event() for _ in range(self.depth)]
@@ -546,6 +562,8 @@ class BatchRenderer:
             gen.run_vectors_graphed(on_device, out, truncation_psi=self.truncation_psi, noise_mode=self.noise_mode or "random")
         else:
             gen.synthesis(on_device, noise_mode=self.noise_mode or "const", out=out)
+        if self.resizer is not None:
+            out = self.resizer.resize(out, self.output_side, self.output_side, out=self.scaled_dev[slot][:n])
         computed = torch.cuda.Event()
         computed.record(stream)
         self.copy_stream.wait_event(computed)

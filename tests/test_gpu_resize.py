@@ -80,3 +80,22 @@ def test_argument_validation():
                                      x.data_ptr(), 4, 4, None) == 1
     assert lib.gance_resize_cubic_u8(x.data_ptr(), 1, 4, 4, x.data_ptr(), 0, 4, x.data_ptr(), x.data_ptr(), x.data_ptr(),
                                      x.data_ptr(), 4, 4, None) == 2
+
+
+def test_renderer_scales_on_the_device(tmp_path):
+    """MultiNetwork.indexed_render_batches(output_side_length=S): synthesis -> bicubic resize on the device -> host,
+    identical to resizing the un-scaled frames of the same call with the oracle."""
+    from gance_b200.network_interface import network_functions
+    from gance_b200.networks import container
+
+    path = tmp_path / "net64.pkl"
+    container.write_synthetic_network(path, 64, seed=3, perturbed=True)
+    wplus = np.random.RandomState(4).randn(2, 3, 12, 512).astype(np.float32)  # 2 batches of 3 matrices (const noise)
+    with network_functions.MultiNetwork([path]) as networks:
+        plain = [frames.copy() for frames in networks.indexed_render_batches(0, iter(wplus), max_batch=4)]
+        scaled = [frames.copy() for frames in networks.indexed_render_batches(0, iter(wplus), max_batch=4, output_side_length=135)]
+    assert len(plain) == len(scaled) == 2
+    for small, big in zip(plain, scaled):
+        assert small.shape == (3, 64, 64, 3) and big.shape == (3, 135, 135, 3)
+        for b in range(3):
+            assert np.array_equal(big[b], resize_ref.resize_cubic_u8(small[b], 135, 135))
