@@ -8,7 +8,12 @@ matches the reference's:
   * "gance_b200/synthetic-v1": {resolution, config, seed, perturbed} - a random-init network of a
     named StyleGAN2 config, expanded deterministically at load time (a few hundred bytes on disk);
   * "gance_b200/variables-v1": {variables: {tf_name: ndarray}} - explicit weights keyed by the TF
-    variable names of SURVEY.md Appendix A.2 (what a converted real pickle would contain).
+    variable names of SURVEY.md Appendix A.2 (what a converted real pickle would contain);
+
+and, third, a REAL StyleGAN2 pickle: tuple slot 2 is then a `dnnlib.tflib.network.Network`, whose pickled state
+(static kwargs, components, (name, ndarray) variable list) is captured WITHOUT TensorFlow or dnnlib by the restricted
+unpickler of `tf_pickle.py` and renamed to the same TF variable names. Every file is read through that allow-listed
+unpickler: a network pickle from an untrusted source cannot run code here.
 """
 
 import pickle
@@ -17,6 +22,7 @@ from typing import Dict, NamedTuple
 
 import numpy as np
 
+from gance_b200.networks import tf_pickle
 from gance_b200.networks.generator_spec import (
     GeneratorSpec,
     random_init_variables,
@@ -84,12 +90,17 @@ def _spec_from_variables(variables: Dict[str, np.ndarray], config: str) -> Gener
 def read_network(path: Path) -> LoadedNetwork:
     """`pickle.load(f)[2]` and expansion into TF-named float32 variables."""
     path = Path(path)
-    with open(path, "rb") as handle:
-        payload = pickle.load(handle)
+    try:
+        payload = tf_pickle.restricted_load(path.read_bytes())
+    except pickle.UnpicklingError as error:
+        raise ValueError(f"{path}: refused to unpickle: {error}") from error
     try:
         record = payload[2]
     except (TypeError, IndexError, KeyError) as error:
         raise ValueError(f"{path} is not a (G, D, Gs) network pickle") from error
+    if isinstance(record, tf_pickle.CapturedNetwork):  # a real TF1 StyleGAN2 pickle
+        variables = tf_pickle.variables_from_tf_network(record)
+        return LoadedNetwork(_spec_from_variables(variables, tf_pickle.fmap_config(record)), variables, str(path))
     if not isinstance(record, dict) or "format" not in record:
         raise ValueError(f"{path}: unsupported network payload of type {type(record).__name__}")
     if record["format"] == SYNTHETIC_FORMAT:
