@@ -333,10 +333,20 @@ def main():
     flop_per_step = FLOP_PER_FRAME.get(res, 0.0) * batch
     achieved_tflops = flop_per_step / (conv_step_ms * 1e-3) / 1e12 if conv_step_ms > 0 else 0.0
     tensor_peak = peaks["bf16_tflops_sustained"]
+    traffic, traffic_note = None, None
+    if res == 1024 and batch == 32 and args.mode == "fp16":  # the configuration the committed ncu pass was taken on
+        try:
+            captured = json.loads((ROOT / "profiles" / "r01_conv_traffic.json").read_text())
+            traffic = float(captured["conv_dram_bytes_per_step"])
+            traffic_note = ("dram__bytes_read.sum + dram__bytes_write.sum over the conv launches of one step, "
+                            "profiles/r01_conv_traffic.json (ncu capture, not measured in this run)")
+        except Exception:  # pylint: disable=broad-except
+            traffic = None
     roofline = {
-        "bound": "tensor", "kernel": "modconv3x3_tc_kernel + modconv3x3_halo_kernel (every modulated-convolution launch of a step: tcgen05 implicit GEMMs with fused demod/noise/bias/lrelu/ToRGB/skip/uint8 epilogues)",
+        "bound": "tensor", "kernel": "modconv3x3_tc_kernel + modconv3x3_halo_kernel + upconv_fused_kernel (every modulated-convolution launch of a step: tcgen05 implicit GEMMs with fused demod/noise/bias/lrelu/FIR/ToRGB/skip/uint8 epilogues)",
         "achieved": achieved_tflops, "peak": tensor_peak, "unit": "TFLOP/s", "frac": achieved_tflops / tensor_peak,
-        "peak_source": f"bf16_tflops_sustained, {peak_source}", "traffic": None,
+        "peak_source": f"bf16_tflops_sustained, {peak_source}", "traffic": traffic, "traffic_unit": "bytes per step (same launches as `achieved`)",
+        "traffic_source": traffic_note, "algorithmic_hbm_bytes_per_step": HBM_BYTES_PER_FRAME.get(res, 0.0) * batch,
         "conv_ms_per_step": conv_step_ms, "other_ms_per_step": float(np.median(other_ms)),
         "hbm_algorithmic_gbs_whole_step": HBM_BYTES_PER_FRAME.get(res, 0.0) * batch / (elapsed_ms / args.steps * 1e-3) / 1e9,
         "hbm_peak_gbs": peaks["hbm_gbs"],
