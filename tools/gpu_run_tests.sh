@@ -19,3 +19,4 @@ fi
 run conv_tc tests/test_gpu_kernels.py -k "tcgen05 or ((bf16 or fp16) and up_convolution)"
 run synthesis tests/test_gpu_synthesis.py
 run resize tests/test_gpu_resize.py
+run pipeline tests/test_gpu_pipeline.py
