@@ -28,12 +28,15 @@ def all_frame_ranges(world_size: int, num_frames: int) -> List[Tuple[int, int]]:
 
 
 def gather_frames(
-    local_frames: torch.Tensor, counts: List[int], dst: int = 0, group: Optional[dist.ProcessGroup] = None
+    local_frames: torch.Tensor, counts: List[int], dst: int = 0, group: Optional[dist.ProcessGroup] = None,
+    out: Optional[torch.Tensor] = None,
 ) -> Optional[torch.Tensor]:
     """
     Gather uint8 [n_r,H,W,3] chunks (n_r = counts[r], possibly ragged or zero) to rank `dst`, which
     gets [sum(counts),H,W,3] in global frame order; other ranks get None. One collective:
-    `dist.gather` (grouped ncclSend/ncclRecv under NCCL) over chunks padded to max(counts).
+    `dist.gather` (grouped ncclSend/ncclRecv under NCCL) over chunks padded to max(counts). When every rank sends the
+    same number of frames the chunks are received straight into `out` ([sum(counts),H,W,3], allocated if not given):
+    no staging copies on the encoder rank.
     """
     if not dist.is_initialized() or dist.get_world_size(group) == 1:
         return local_frames
@@ -47,6 +50,14 @@ def gather_frames(
         send = torch.zeros((longest,) + frame_shape, dtype=local_frames.dtype, device=local_frames.device)
         send[: local_frames.shape[0]] = local_frames
     send = send.contiguous()
+    if rank == dst and min(counts) == longest:
+        total = (longest * world_size,) + frame_shape
+        if out is None:
+            out = torch.empty(total, dtype=send.dtype, device=send.device)
+        elif tuple(out.shape) != total or out.dtype != send.dtype or not out.is_contiguous():
+            raise ValueError(f"out must be a contiguous {send.dtype} tensor of shape {total}")
+        dist.gather(send, list(out.split(longest, dim=0)), dst=dst, group=group)
+        return out
     if rank == dst:
         received = [torch.empty_like(send) for _ in range(world_size)]
         dist.gather(send, received, dst=dst, group=group)

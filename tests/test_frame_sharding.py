@@ -53,7 +53,21 @@ def _worker(rank: int, world: int, port: int, total_frames: int, results) -> Non
         start, stop = ranges[rank]
         local = torch.from_numpy(np.stack([_frame(i) for i in range(start, stop)])) if stop > start else \
             torch.zeros((0, 4, 5, 3), dtype=torch.uint8)
-        gathered = gather_frames(local, [b - a for a, b in ranges], dst=0)
+        counts = [b - a for a, b in ranges]
+        gathered = gather_frames(local, counts, dst=0)
+        if len(set(counts)) == 1:  # equal shares: chunks are received straight into a caller-provided buffer
+            out = torch.zeros((total_frames, 4, 5, 3), dtype=torch.uint8) if rank == 0 else None
+            again = gather_frames(local, counts, dst=0, out=out)
+            if rank == 0:
+                results.put(("out", again is out and bool(torch.equal(out, gathered)), ()))
+                try:
+                    gather_frames(local, counts, dst=0, out=torch.zeros((1, 4, 5, 3), dtype=torch.uint8))
+                    results.put(("out-shape", False, ()))
+                except ValueError:
+                    results.put(("out-shape", True, ()))
+            else:
+                results.put(("out", again is None, ()))
+                results.put(("out-shape", True, ()))
         if rank == 0:
             want = np.stack([_frame(i) for i in range(total_frames)])
             results.put(("ok", bool(np.array_equal(gathered.numpy(), want)), tuple(gathered.shape)))
@@ -78,7 +92,8 @@ def test_gather_frames_keeps_global_frame_order_gloo(world, total_frames):
     procs = [ctx.Process(target=_worker, args=(rank, world, port, total_frames, results)) for rank in range(world)]
     for proc in procs:
         proc.start()
-    got = [results.get(timeout=120) for _ in range(2 * world)]
+    per_rank = 4 if total_frames % world == 0 else 2
+    got = [results.get(timeout=120) for _ in range(per_rank * world)]
     for proc in procs:
         proc.join(timeout=60)
         assert proc.exitcode == 0
