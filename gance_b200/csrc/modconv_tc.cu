@@ -292,14 +292,49 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
         return n;
     };
 
+    // With 64 channels and the fused ToRGB (96 coefficient registers per thread) the values fetched one tile ahead do not
+    // fit the register file: ptxas spilled them, and a spill STORE waits for the load it spills - the whole fetch latency
+    // landed back on the critical path (ncu: 14 % of all stall samples on three STL instructions). That flavour therefore
+    // only PREFETCHES the next tile's operands into L2 and loads them at the top of its own iteration, where the L2-hit
+    // latency hides behind the wait for the accumulator.
+    constexpr bool kAheadInRegisters = !(RGB && C == 64);
+    auto prefetch = [&](int next) {
+        const TileCoord n = decode_tile(p, next, N_TILE);
+        if (p.noise != nullptr) {
+            const float* noise_b = p.noise + (size_t)n.b0 * p.noise_batch_stride;
+#pragma unroll
+            for (int rr = 0; rr < 4; ++rr) {
+                const int h = n.h0 + hl[rr], w = n.w0 + wl[rr];
+                const float* address = UP ? noise_b + (size_t)(2 * h) * out_w + 2 * w : noise_b + (size_t)h * out_w + w;
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(address));
+                if (UP) asm volatile("prefetch.global.L2 [%0];" ::"l"(address + out_w));
+            }
+        }
+        if (RGB && p.y_prev != nullptr) {
+            const int own_h = n.h0 + (q4 == 0 ? hl[0] : q4 == 1 ? hl[1] : q4 == 2 ? hl[2] : hl[3]);
+            const int own_w = n.w0 + (q4 == 0 ? wl[0] : q4 == 1 ? wl[1] : q4 == 2 ? wl[2] : wl[3]);
+            const int hp = p.h_out >> 1, wp = p.w_out >> 1;
+            const int a = own_h >> 1, c = own_w >> 1;
+            const int a2 = min(max((own_h & 1) ? a + 1 : a - 1, 0), hp - 1);
+            const float4* base = reinterpret_cast<const float4*>(p.y_prev) + (size_t)n.b0 * hp * wp;
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(base + (size_t)a * wp + c));   // the +-1 column shares the 32-byte sector
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(base + (size_t)a2 * wp + c));  // half of the time, the line always
+        }
+    };
+
     int tile = blockIdx.x + group * gridDim.x;
     Ahead ahead;
-    if (tile < total_tiles) ahead = request(tile);
+    if (kAheadInRegisters && tile < total_tiles) ahead = request(tile);
     for (; tile < total_tiles; tile += GROUPS * gridDim.x) {
+        const bool more = tile + GROUPS * (int)gridDim.x < total_tiles;
+        if (!kAheadInRegisters) {
+            ahead = request(tile);
+            if (more) prefetch(tile + GROUPS * gridDim.x);
+        }
         const Ahead cur = ahead;
         const TileCoord t = cur.t;
         const int b = t.b0;
-        if (tile + GROUPS * (int)gridDim.x < total_tiles) ahead = request(tile + GROUPS * gridDim.x);
+        if (kAheadInRegisters && more) ahead = request(tile + GROUPS * gridDim.x);
         if (b != cached_b) {  // per-sample coefficients of this thread's channels -> registers
 #pragma unroll
             for (int k = 0; k < CPT; ++k) {
