@@ -240,11 +240,13 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
     // Noise and skip-connection values of a tile do not depend on its accumulator: they are requested one tile AHEAD
     // (while the current tile is being computed) so their global-memory latency never sits on the tile's critical path.
     constexpr int NP = UP ? 4 : 1;  // noise values per input pixel
+    constexpr bool kAheadInRegisters = !(RGB && C == 64);  // see the comment above `prefetch` below
     struct Ahead {
         TileCoord t;
         float nz[4][NP];
         float4 p00, p01, p10, p11;  // y_prev taps of this lane's own pixel (RGB)
         float w01, w10, w11;
+        float3 skip;                // prefetch flavour: the four taps already combined (3 registers instead of 19)
         int own_h, own_w;
     };
     auto request = [&](int tile) {
@@ -267,6 +269,7 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
         }
         n.p00 = n.p01 = n.p10 = n.p11 = make_float4(0.f, 0.f, 0.f, 0.f);
         n.w01 = n.w10 = n.w11 = 0.f;
+        n.skip = make_float3(0.f, 0.f, 0.f);
         n.own_h = n.own_w = 0;
         if (RGB) {  // this lane finishes the pixel of row rr == q4
             n.own_h = n.t.h0 + (q4 == 0 ? hl[0] : q4 == 1 ? hl[1] : q4 == 2 ? hl[2] : hl[3]);
@@ -287,6 +290,11 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
                 n.w01 = c_in ? 0.1875f : 0.f;
                 n.w10 = a_in ? 0.1875f : 0.f;
                 n.w11 = (a_in && c_in) ? 0.0625f : 0.f;
+                if (!kAheadInRegisters) {  // same expression, same order as the register flavour evaluates at the end
+                    n.skip.x = 0.5625f * n.p00.x + n.w01 * n.p01.x + n.w10 * n.p10.x + n.w11 * n.p11.x;
+                    n.skip.y = 0.5625f * n.p00.y + n.w01 * n.p01.y + n.w10 * n.p10.y + n.w11 * n.p11.y;
+                    n.skip.z = 0.5625f * n.p00.z + n.w01 * n.p01.z + n.w10 * n.p10.z + n.w11 * n.p11.z;
+                }
             }
         }
         return n;
@@ -297,7 +305,6 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
     // landed back on the critical path (ncu: 14 % of all stall samples on three STL instructions). That flavour therefore
     // only PREFETCHES the next tile's operands into L2 and loads them at the top of its own iteration, where the L2-hit
     // latency hides behind the wait for the accumulator.
-    constexpr bool kAheadInRegisters = !(RGB && C == 64);
     auto prefetch = [&](int next) {
         const TileCoord n = decode_tile(p, next, N_TILE);
         if (p.noise != nullptr) {
@@ -425,9 +432,16 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
                 const float send = h_own ? keep[0][c] : keep[1][c];
                 mine[c] = (h_own ? keep[1][c] : keep[0][c]) + __shfl_xor_sync(0xffffffffu, send, 2);
             }
-            const float red = mine[0] + rgb_bias.x + 0.5625f * cur.p00.x + cur.w01 * cur.p01.x + cur.w10 * cur.p10.x + cur.w11 * cur.p11.x;
-            const float green = mine[1] + rgb_bias.y + 0.5625f * cur.p00.y + cur.w01 * cur.p01.y + cur.w10 * cur.p10.y + cur.w11 * cur.p11.y;
-            const float blue = mine[2] + rgb_bias.z + 0.5625f * cur.p00.z + cur.w01 * cur.p01.z + cur.w10 * cur.p10.z + cur.w11 * cur.p11.z;
+            float red, green, blue;
+            if (kAheadInRegisters) {
+                red = mine[0] + rgb_bias.x + 0.5625f * cur.p00.x + cur.w01 * cur.p01.x + cur.w10 * cur.p10.x + cur.w11 * cur.p11.x;
+                green = mine[1] + rgb_bias.y + 0.5625f * cur.p00.y + cur.w01 * cur.p01.y + cur.w10 * cur.p10.y + cur.w11 * cur.p11.y;
+                blue = mine[2] + rgb_bias.z + 0.5625f * cur.p00.z + cur.w01 * cur.p01.z + cur.w10 * cur.p10.z + cur.w11 * cur.p11.z;
+            } else {
+                red = mine[0] + rgb_bias.x + cur.skip.x;
+                green = mine[1] + rgb_bias.y + cur.skip.y;
+                blue = mine[2] + rgb_bias.z + cur.skip.z;
+            }
             const size_t pixel = ((size_t)b * p.h_out + own_h) * p.w_out + own_wp;
             if (p.y_out != nullptr) reinterpret_cast<float4*>(p.y_out)[pixel] = make_float4(red, green, blue, 0.f);
             if (p.frames != nullptr) {
