@@ -48,12 +48,23 @@ struct TileCoord {
 
 __device__ __forceinline__ TileCoord decode_tile(const ConvParams& p, int tile, int n_tile_size) {
     TileCoord t;
-    int nt = tile % p.n_tiles;
-    int m = tile / p.n_tiles;
-    int tw = m % p.tiles_w;
-    m /= p.tiles_w;
-    int th = m % p.tiles_h;
-    t.b0 = m / p.tiles_h;  // tile_b == 1
+    int nt = 0, m = tile;
+    if (p.n_tiles != 1) {
+        nt = tile % p.n_tiles;
+        m = tile / p.n_tiles;
+    }
+    int tw, th;
+    if (p.tiles_w_log2 >= 0) {  // every 2^k-sized image: three runtime divisions (~60 instructions per warp and tile) become shifts
+        tw = m & (p.tiles_w - 1);
+        m >>= p.tiles_w_log2;
+        th = m & (p.tiles_h - 1);
+        t.b0 = m >> p.tiles_h_log2;
+    } else {
+        tw = m % p.tiles_w;
+        m /= p.tiles_w;
+        th = m % p.tiles_h;
+        t.b0 = m / p.tiles_h;  // tile_b == 1
+    }
     t.n0 = nt * n_tile_size;
     t.w0 = tw << p.tile_w_log2;
     t.h0 = th * p.tile_h;
@@ -985,6 +996,12 @@ static int launch_tensor_core_conv(const char* who, const void* x, int dtype, in
                   "%s: fused ToRGB needs Cout in {32,64,128,256} (got %d)", who, c_out);
     const int h_in = h_out + 2 - 2 * pad, w_in = w_out + 2 - 2 * pad;
     const int m_tiles = p.tiles_w * p.tiles_h * p.tiles_b;
+    auto set_tile_logs = [&]() {
+        const bool pow2 = is_pow2(p.tiles_w) && is_pow2(p.tiles_h);
+        p.tiles_w_log2 = pow2 ? ilog2(p.tiles_w) : -1;
+        p.tiles_h_log2 = pow2 ? ilog2(p.tiles_h) : -1;
+    };
+    set_tile_logs();
 
     // Narrow layers (512^2 / 1024^2): halo kernel, whole weight resident, one activation fetch per tile.
     if (tc::g_use_halo && pad == 1 && w_out % tc::kHaloTileW == 0 && h_out % tc::kHaloTileH == 0 &&
@@ -992,6 +1009,7 @@ static int launch_tensor_core_conv(const char* who, const void* x, int dtype, in
         p.tile_w = tc::kHaloTileW; p.tile_h = tc::kHaloTileH; p.tile_b = 1;
         p.tile_w_log2 = ilog2(p.tile_w); p.tile_hw_log2 = ilog2(p.tile_w * p.tile_h);
         p.tiles_w = w_out / p.tile_w; p.tiles_h = h_out / p.tile_h; p.tiles_b = batch;
+        set_tile_logs();
         p.n_tiles = 1; p.k_chunks = 1;
         if (c_in == 32) return tc::launch_halo<32, 32, 4>(half_operands, p, x, weight, s);
         if (c_out == 128) return tc::launch_halo<128, 64, 2>(half_operands, p, x, weight, s);

@@ -23,6 +23,7 @@ struct ConvParams {
     int c_log2;                      // log2(c_real)
     int a_tx_bytes;                  // bytes one A-tile TMA box delivers (tile_w * tile_h * BLOCK_K * 2)
     int tiles_w, tiles_h, tiles_b;   // m-tiles per dimension
+    int tiles_w_log2, tiles_h_log2;  // log2 of the above when both are powers of two (else -1): tile decode without divisions
     int n_tiles;                     // c_out / N_TILE
     int k_chunks;                    // c_in / BLOCK_K
     const float* demod;
