@@ -221,7 +221,7 @@ __device__ __forceinline__ void store_pair(__nv_bfloat16* dst, float a, float b)
 //   channels 32*chunk + 8*j + 2*(t%4) + e    (j in 0..3, e in {0,1})
 // The ToRGB sum over channels is finished with a two-step reduce-scatter over the four lanes that share a row
 // (9 shuffles), which leaves row rr on lane t%4 == rr: every lane then adds the skip connection for ONE pixel.
-template <typename T, int N_TILE, int C, bool UP, bool RGB, int GROUPS>
+template <typename T, int N_TILE, int C, bool UP, bool RGB, int GROUPS, int TILE_W_LOG2 = -1>
 __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int group, int warp, int lane, int total_tiles,
                                                    uint32_t tmem_base, uint64_t* tmem_full_bar,
                                                    uint64_t* tmem_empty_bar) {
@@ -242,8 +242,13 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
 #pragma unroll
     for (int rr = 0; rr < 4; ++rr) {
         const int row = quarter * 32 + 16 * (rr >> 1) + 8 * (rr & 1) + r8;
-        wl[rr] = row & (p.tile_w - 1);
-        hl[rr] = row >> p.tile_w_log2;
+        if (TILE_W_LOG2 >= 0) {  // compile-time tile width (halo kernels: 8): the four rows of a thread become constant offsets
+            wl[rr] = row & ((1 << TILE_W_LOG2) - 1);
+            hl[rr] = row >> TILE_W_LOG2;
+        } else {
+            wl[rr] = row & (p.tile_w - 1);
+            hl[rr] = row >> p.tile_w_log2;
+        }
     }
     int cached_b = -1;
     uint32_t full_phase = 0;
@@ -743,7 +748,7 @@ modconv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_
             }
         }
     } else {
-        conv_epilogue_frag<T, N_GEMM, (UP ? N_GEMM / 4 : N_GEMM), UP, RGB, kHaloGroups>(
+        conv_epilogue_frag<T, N_GEMM, (UP ? N_GEMM / 4 : N_GEMM), UP, RGB, kHaloGroups, 3>(
             p, (warp - 2) >> 2, warp, lane, total_tiles, tmem_base, tmem_full_bar, tmem_empty_bar);
     }
 
