@@ -333,6 +333,7 @@ def main():
     # ---- roofline of the dominant kernel: CUDA events around every conv launch of a step ---------
     peaks, peak_source = measured_peaks()
     conv_ms, other_ms = [], []
+    per_layer = {}
     for i in range(3):
         generator.profile_events = []
         begin = torch.cuda.Event(enable_timing=True)
@@ -342,6 +343,7 @@ def main():
         prev, conv, other = begin, 0.0, 0.0
         for name, event in generator.profile_events:
             dt = prev.elapsed_time(event)
+            per_layer.setdefault(name, []).append(dt)
             if "conv" in name:
                 conv += dt
             else:
@@ -350,6 +352,24 @@ def main():
         conv_ms.append(conv)
         other_ms.append(other)
     generator.profile_events = None
+    # per-layer view of the same events: each modulated convolution against the roofline that bounds IT (algorithmic
+    # flops = 2 * 9 * Cin * Cout per output pixel (per INPUT pixel for up-convolutions); algorithmic bytes = input +
+    # output activations at 2 B per element), largest first
+    layers = []
+    bytes_per_element = 4 if args.mode == "fp32" else 2
+    for conv in generator.convs:
+        side = conv.out_resolution
+        name = f"{side}/conv0_up" if conv.up else (f"{side}/conv1" if side > 4 else "4/conv")
+        if name not in per_layer:
+            continue
+        ms = float(np.median(per_layer[name]))
+        pixels = conv.in_resolution ** 2 if conv.up else side ** 2
+        flops = 2.0 * 9 * conv.in_channels * conv.out_channels * pixels * batch
+        moved = float(conv.in_resolution ** 2 * conv.in_channels + side ** 2 * conv.out_channels) * bytes_per_element * batch
+        t_tensor, t_hbm = flops / (peaks["bf16_tflops_sustained"] * 1e12), moved / (peaks["hbm_gbs"] * 1e9)
+        layers.append({"layer": name, "ms": ms, "tflops": flops / (ms * 1e-3) / 1e12, "hbm_gbs": moved / (ms * 1e-3) / 1e9,
+                       "bound": "tensor" if t_tensor >= t_hbm else "hbm", "frac_of_bound": max(t_tensor, t_hbm) / (ms * 1e-3)})
+    layers.sort(key=lambda row: -row["ms"])
     conv_step_ms = float(np.median(conv_ms))
     flop_per_step = FLOP_PER_FRAME.get(res, 0.0) * batch
     achieved_tflops = flop_per_step / (conv_step_ms * 1e-3) / 1e12 if conv_step_ms > 0 else 0.0
@@ -367,7 +387,7 @@ def main():
         "bound": "tensor", "kernel": "modconv3x3_tc_kernel + modconv3x3_halo_kernel + upconv_fused_kernel (every modulated-convolution launch of a step: tcgen05 implicit GEMMs with fused demod/noise/bias/lrelu/FIR/ToRGB/skip/uint8 epilogues)",
         "achieved": achieved_tflops, "peak": tensor_peak, "unit": "TFLOP/s", "frac": achieved_tflops / tensor_peak,
         "peak_source": f"bf16_tflops_sustained, {peak_source}", "traffic": traffic, "traffic_unit": "bytes per step (same launches as `achieved`)",
-        "traffic_source": traffic_note, "algorithmic_hbm_bytes_per_step": HBM_BYTES_PER_FRAME.get(res, 0.0) * batch,
+        "traffic_source": traffic_note, "layers": layers[:8], "algorithmic_hbm_bytes_per_step": HBM_BYTES_PER_FRAME.get(res, 0.0) * batch,
         "conv_ms_per_step": conv_step_ms, "other_ms_per_step": float(np.median(other_ms)),
         "hbm_algorithmic_gbs_whole_step": HBM_BYTES_PER_FRAME.get(res, 0.0) * batch / (elapsed_ms / args.steps * 1e-3) / 1e9,
         "hbm_peak_gbs": peaks["hbm_gbs"],
