@@ -71,6 +71,7 @@ _SIGNATURES = {
     "gance_to_uint8_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "gance_normal_noise": (c_int, [c_void_p, c_longlong, c_ulonglong, c_ulonglong, c_void_p]),
     "gance_normal_noise_next": (c_int, [c_void_p, c_longlong, c_ulonglong, c_void_p, c_void_p]),
+    "gance_gaussian_filter_time_wrap": (c_int, [c_void_p, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p]),
     "gance_resize_cubic_u8": (
         c_int,
         [c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,

@@ -206,6 +206,40 @@ def _encode_ordered(values: torch.Tensor) -> torch.Tensor:
     return bits.view(torch.float64)
 
 
+# ---- a9 ------------------------------------------------------------------------------------------
+def gaussian_kernel1d(sigma: float, truncate: float = 4.0):
+    """scipy.ndimage._filters._gaussian_kernel1d(sigma, 0, radius) - (radius, weights from the centre outwards)."""
+    radius = int(truncate * float(sigma) + 0.5)
+    x = np.arange(-radius, radius + 1)
+    phi = np.exp(-0.5 / (float(sigma) * float(sigma)) * x ** 2)
+    phi = phi / phi.sum()
+    return radius, np.ascontiguousarray(phi[radius:][::1], dtype=np.float64)
+
+
+def gaussian_filter_time_wrap(latents: np.ndarray, sigma: float, device: Optional[torch.device] = None) -> np.ndarray:
+    """
+    scipy.ndimage.gaussian_filter(latents, sigma=(sigma, 0, 0), mode="wrap") for a float32 (T, 1, L) / (T, L) array
+    (primatives.py:69), on the device, bit-exact with scipy; returns a host float32 array of the input's shape.
+    """
+    if device is None:
+        if not torch.cuda.is_available():
+            raise RuntimeError("gaussian_filter_time_wrap needs a CUDA device: the hot path has no CPU fallback")
+        device = torch.device("cuda", torch.cuda.current_device())
+    device = _device(device)
+    array = np.ascontiguousarray(latents, dtype=np.float32)
+    num_vectors, length = array.shape[0], int(np.prod(array.shape[1:]))
+    radius, weights = gaussian_kernel1d(sigma)
+    src = torch.as_tensor(array.reshape(num_vectors, length)).to(device)
+    out = torch.empty_like(src)
+    weights_d = torch.as_tensor(weights).to(device)
+    _lib.check(
+        _lib.load_library().gance_gaussian_filter_time_wrap(src.data_ptr(), num_vectors, length, weights_d.data_ptr(), radius,
+                                                            out.data_ptr(), _stream(device)),
+        "gance_gaussian_filter_time_wrap",
+    )
+    return out.cpu().numpy().reshape(array.shape)
+
+
 # ---- a10 / a11 -------------------------------------------------------------------------------
 def alpha_blend_noise(spec: torch.Tensor, noise: np.ndarray, alpha: float, want_f64: bool = True, want_f32: bool = True):
     """combined = noise*(1-alpha) + spectrogram*alpha (visualization_inputs.py:144). Returns (f64 | None, f32 | None)."""

@@ -1,8 +1,10 @@
 """
 The Gaussian noise source of the noise-blend path (mirrors `gaussian_data` of
-/root/reference/gance/vector_sources/primatives.py:49-74). It stays on the host: the values come
-from numpy's legacy MT19937 + polar Box-Muller stream (`RandomState(1234).randn`), which has to be
-reproduced bit for bit, and the filter is a one-off over T x 512 floats.
+/root/reference/gance/vector_sources/primatives.py:49-74). The random values stay on the host - they
+come from numpy's legacy MT19937 + polar Box-Muller stream (`RandomState(1234).randn`), which has to be
+reproduced bit for bit - and so do the two global float32 reductions (RMS here, min-max in the caller).
+The wrap-around Gaussian filter along time, 61 % of the whole audio -> latents time for an album-length
+track when scipy ran it, is `gance_gaussian_filter_time_wrap` (bit-exact with scipy's NI_Correlate1D).
 """
 from typing import NamedTuple, Optional
 
@@ -31,8 +33,11 @@ def gaussian_data(
     if random_state is None:
         random_state = np.random.RandomState(DEFAULT_RANDOM_SEED)  # pylint: disable=no-member
     latents = random_state.randn(num_vectors, 1, vector_length).astype(np.float32)
-    latents = scipy.ndimage.gaussian_filter(
-        input=latents, sigma=(sigmas.across_vectors, 0, sigmas.within_vectors), mode="wrap"
-    )
+    if sigmas.across_vectors > 1e-15:  # scipy skips axes whose sigma is zero
+        from gance_b200 import audio_device  # needs the CUDA library: no CPU fallback on the hot path
+
+        latents = audio_device.gaussian_filter_time_wrap(latents, float(sigmas.across_vectors))
+    if sigmas.within_vectors > 1e-15:  # never set by the hot path (visualization_inputs.py:135-142 passes 0): demo shapes only
+        latents = scipy.ndimage.gaussian_filter(input=latents, sigma=(0, 0, sigmas.within_vectors), mode="wrap")
     latents /= np.sqrt(np.mean(np.square(latents)))
     return ConcatenatedVectors(latents.reshape(vector_length * num_vectors))

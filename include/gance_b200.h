@@ -288,6 +288,15 @@ int gance_alpha_blend_wplus(const double* spec, const float* projected, int dupl
                             int vector_length, double* latents_f64, float* latents_f32,
                             void* stream);
 
+/* ---- a9: Gaussian noise source, wrap-around filter along time ------------------------------------
+ * scipy.ndimage.gaussian_filter(latents, sigma=(sigma,0,0), mode="wrap") of gance/vector_sources/primatives.py:69, as
+ * scipy's NI_Correlate1D evaluates it (double accumulation, symmetric pairs, outermost tap first, no FMA): bit-exact.
+ *   in / out [T, L] f32 (distinct buffers); weights [radius+1] f64 = the normalised kernel from its centre outwards
+ *   (gance_b200/audio_device.py:gaussian_kernel1d builds it the way scipy does). The RNG stays on the host (legacy
+ *   MT19937 stream of RandomState(1234)), as do the two global reductions that follow (RMS, min-max). */
+int gance_gaussian_filter_time_wrap(const float* in, int num_vectors, int vector_length,
+                                    const double* weights, int radius, float* out, void* stream);
+
 /* ---- output-side frame scaling: bicubic resize of uint8 NHWC frames ------------------------------------
  * Replaces cv2.resize(image, (side, side), interpolation=cv2.INTER_CUBIC) in
  * gance/image_sources/video_common.py:399-429 (resize_source; used by scale_square_source_duplicate, 432-455, from

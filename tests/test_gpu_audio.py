@@ -202,3 +202,26 @@ def test_album_length_track_matches_oracle_and_is_frame_sharded_consistently():
     assert dev.latents.shape == (10800, 512)
     assert_latents_close(dev.latents.cpu().numpy().reshape(-1), want.combined, "album noise blend")
     assert np.array_equal(dev.network_indices, want.network_indices)
+
+
+@pytest.mark.parametrize("num_vectors,sigma", [(60, 50), (150, 50), (450, 50), (1000, 20), (7, 3)])
+def test_gaussian_filter_along_time_is_bit_exact_with_scipy(num_vectors, sigma):
+    """gance_gaussian_filter_time_wrap against scipy.ndimage.gaussian_filter(sigma=(s,0,0), mode='wrap') (primatives.py:69),
+    including tracks shorter than the kernel radius (the periodic extension wraps more than once)."""
+    import scipy.ndimage
+
+    latents = np.random.RandomState(num_vectors).randn(num_vectors, 1, 512).astype(np.float32)
+    want = scipy.ndimage.gaussian_filter(input=latents, sigma=(sigma, 0, 0), mode="wrap")
+    got = audio_device.gaussian_filter_time_wrap(latents, float(sigma))
+    assert got.shape == want.shape and got.dtype == np.float32
+    assert np.array_equal(got, want)
+
+
+def test_gaussian_noise_source_equals_the_oracle():
+    """gaussian_data (host MT19937 stream -> device filter -> host RMS) bit for bit against oracle/audio_ref.py."""
+    from gance_b200.vector_sources.primatives import Sigmas, gaussian_data
+
+    for frames in (60, 333):
+        got = gaussian_data(vector_length=512, num_vectors=frames, sigmas=Sigmas(across_vectors=50, within_vectors=0))
+        want = audio_ref.gaussian_data(512, frames, sigma_across=50)
+        assert got.dtype == np.float32 and np.array_equal(np.asarray(got), np.asarray(want))
