@@ -35,7 +35,7 @@ constexpr int kFuEpilogueThreads = 256;
 
 template <int CC>
 struct FusedLayout {
-    static constexpr int kStages = 3;  // measured at batch 32: 2 stages cost +6 % (Cin 128) to +31 % (Cin 512); a 4th does not fit beside the patch
+    static constexpr int kStages = 3;  // measured at batch 32: 2 stages cost +6 % (Cin 128) to +31 % (Cin 512); a 4th (patch halved, two epilogue passes) gained < 4 % - profiles/README.md
     static constexpr int kBBlock = CC * kFuK * 2;              // one phase block of the B operand
     static constexpr int kStageBytes = kFuABytes + 4 * kBBlock;
     static constexpr int kPatchOffset = kStages * kStageBytes;
