@@ -165,7 +165,7 @@ class GeneratorOnDevice:
         """
         Which kernel an up-convolution runs as (include/gance_b200.h):
           "fused"  - 4-phase GEMM with the FIR applied on chip (upconv_fused.cu): one launch, x read once, output written
-                     once, 1.52x the algorithmic MACs. Default for input sides >= 32 with Cout % 64 == 0 (measured on
+                     once, 1.52x the algorithmic MACs. Default for input sides >= 16 with Cout % 64 == 0 (measured on
                      B200, batch 32: 256->512 710 us vs 1280 phase / 1080 folded; 128->256 525 vs 794; 64->128 460 vs
                      595; 32->64 282 vs 282 - profiles/README.md).
           "phase"  - 4-phase GEMM + separate FIR pass through a 16-bit scratch tensor (upconv_phase.cu).
@@ -183,7 +183,7 @@ class GeneratorOnDevice:
             return "phase" if phase_ok else "folded"
         if forced == "fused":
             return "fused" if fused_ok else "folded"
-        if fused_ok and conv.in_resolution >= 32 and conv.out_channels % 64 == 0:
+        if fused_ok and conv.out_channels % 64 == 0:  # in_resolution >= 16 (16->32: 100 us fused vs 132 us folded at batch 32)
             return "fused"
         return "folded"
 
