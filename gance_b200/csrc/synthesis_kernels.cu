@@ -334,15 +334,20 @@ __global__ void __launch_bounds__(256) torgb_skip_kernel(const T* __restrict__ x
                                                          float* __restrict__ y_out,
                                                          uint8_t* __restrict__ frames) {
     constexpr int V = Vec<T>::N;
-    extern __shared__ float wmod[];  // [channels][3]
+    // [3][V][channels / V]: channel c = cv * V + k sits at slot k * (channels / V) + cv, so the lanes of a group
+    // (consecutive cv, same k) read consecutive words - [channels][3] order put them 3 * V words apart, an 8-way
+    // bank conflict on every weight read
+    extern __shared__ float wmod[];
     const int b = blockIdx.y;
-    for (int i = threadIdx.x; i < channels * 3; i += blockDim.x)
-        wmod[i] = styles[(size_t)b * channels + i / 3] * weight[i];
+    const int vec_per_pixel = channels / V;
+    for (int i = threadIdx.x; i < channels * 3; i += blockDim.x) {
+        const int c = i / 3, colour = i - c * 3;
+        wmod[colour * channels + (c % V) * vec_per_pixel + c / V] = styles[(size_t)b * channels + c] * weight[i];
+    }
     __syncthreads();
     const int pixels = h * w;
     const int group = threadIdx.x / LANES, lane = threadIdx.x % LANES;
     const int groups_per_block = blockDim.x / LANES;
-    const int vec_per_pixel = channels / V;
     // the loop bound is CTA-uniform so the group shuffles below always see a full warp
     for (int base = blockIdx.x * groups_per_block; base < pixels; base += gridDim.x * groups_per_block) {
         const int p = base + group;
@@ -356,10 +361,10 @@ __global__ void __launch_bounds__(256) torgb_skip_kernel(const T* __restrict__ x
             v.to_float(f);
 #pragma unroll
             for (int k = 0; k < V; ++k) {
-                const float* wm = wmod + (cv * V + k) * 3;
+                const float* wm = wmod + k * vec_per_pixel + cv;
                 r = fmaf(f[k], wm[0], r);
-                g = fmaf(f[k], wm[1], g);
-                bl = fmaf(f[k], wm[2], bl);
+                g = fmaf(f[k], wm[channels], g);
+                bl = fmaf(f[k], wm[2 * channels], bl);
             }
         }
 #pragma unroll
