@@ -57,6 +57,8 @@ def parse_args():
     ap.add_argument("--mode", default="fp16", choices=["fp16", "bf16", "fp32"])
     ap.add_argument("--track-seconds", type=float, default=24.0, help="length of the synthetic chirp track")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=10.0,
+                    help="CPU work the cpu_baseline leg is bounded to (frames are rendered until this much time has passed)")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
 
@@ -173,8 +175,12 @@ def audio_half_report(seconds: float, device):
             "max_rel_err_vs_cpu_port": float(np.abs(got - ref).max() / np.abs(ref).max()), "cores": 1}
 
 
-def cpu_frames_per_second(resolution: int, frames: int, seed: int = 0):
-    """The CPU restatement (oracle/, torch-CPU fp32, batch 1 per frame like the reference), all host threads."""
+def cpu_frames_per_second(resolution: int, seconds: float = 10.0, min_frames: int = 3, max_frames: int = 512,
+                          seed: int = 0):
+    """
+    The CPU restatement (oracle/, torch-CPU fp32, batch 1 per frame like the reference), all host threads: frames are
+    rendered until `seconds` of CPU work have passed (at least `min_frames`), so the sample is bounded in time.
+    """
     import torch
 
     from gance_b200.networks.generator_spec import GeneratorSpec, random_init_variables
@@ -184,14 +190,16 @@ def cpu_frames_per_second(resolution: int, frames: int, seed: int = 0):
     torch.set_num_threads(cores)
     spec = GeneratorSpec(resolution)
     generator = stylegan2_ref.ReferenceGenerator(random_init_variables(spec, seed, perturbed=True), torch.float32)
-    z = np.random.RandomState(1).randn(frames + 1, 512)
+    z = np.random.RandomState(1).randn(max_frames + 1, 512)
     with torch.no_grad():
         stylegan2_ref.convert_images_to_uint8(generator.run_vector(z[:1]))  # warm-up (thread pool, allocator)
         start = time.perf_counter()
-        for i in range(frames):
-            stylegan2_ref.convert_images_to_uint8(generator.run_vector(z[i + 1: i + 2]))
-        elapsed = time.perf_counter() - start
-    return frames / elapsed, cores, elapsed
+        frames, elapsed = 0, 0.0
+        while frames < max_frames and (frames < min_frames or elapsed < seconds):
+            stylegan2_ref.convert_images_to_uint8(generator.run_vector(z[frames + 1: frames + 2]))
+            frames += 1
+            elapsed = time.perf_counter() - start
+    return frames / elapsed, cores, elapsed, frames
 
 
 def run_reference(args):
@@ -423,8 +431,7 @@ def main():
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        frames = 3 if res >= 1024 else 8
-        fps, cores, seconds = cpu_frames_per_second(res, frames)
+        fps, cores, seconds, frames = cpu_frames_per_second(res, args.cpu_seconds)
         cpu_baseline = {"value": fps, "unit": UNIT, "cores": cores, "kind": "port",
                         "sample": f"{frames} frames of the same {res}^2 generator, batch 1, torch-CPU fp32 restatement "
                                   f"(oracle/stylegan2_ref.py), {seconds:.1f} s"}
