@@ -20,3 +20,4 @@ run conv_tc tests/test_gpu_kernels.py -k "tcgen05 or ((bf16 or fp16) and up_conv
 run synthesis tests/test_gpu_synthesis.py
 run resize tests/test_gpu_resize.py
 run pipeline tests/test_gpu_pipeline.py
+run guards tests/test_gpu_guard_bands.py
