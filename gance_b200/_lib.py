@@ -37,6 +37,11 @@ _SIGNATURES = {
         [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_longlong,
          c_float, c_void_p, c_void_p, c_void_p, c_void_p],
     ),
+    "gance_modconv3x3_dual": (
+        c_int,
+        [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_longlong,
+         c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+    ),
     "gance_upfir2x_pad": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "gance_modconv3x3_up2_fir": (
         c_int,

@@ -161,14 +161,16 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int group, in
             const int oh = UP ? 2 * hv + (phase >> 1) : hv, ow = UP ? 2 * wv + (phase & 1) : wv;
             const float nz = UP ? nz4[phase] : nz4[0];
             T* dst = nullptr;
-            if (p.out != nullptr)
-                dst = reinterpret_cast<T*>(p.out) + (((size_t)b * (UP ? 2 * p.h_out : p.h_out) + oh) * out_w + ow) * C + co0;
+            T* dst_plain = nullptr;
+            const size_t out_offset = (((size_t)b * (UP ? 2 * p.h_out : p.h_out) + oh) * out_w + ow) * C + co0;
+            if (p.out != nullptr) dst = reinterpret_cast<T*>(p.out) + out_offset;
+            if (!UP && !RGB && p.out_plain != nullptr) dst_plain = reinterpret_cast<T*>(p.out_plain) + out_offset;
             const uint32_t ca = coef_a_addr + (uint32_t)co0 * 16u, cb = ca + (uint32_t)C * 16u;
             tmem_ld_wait();
             if (valid) {
 #pragma unroll
                 for (int g = 0; g < 4; ++g) {  // 8 channels -> one 16-byte store
-                    float v[8];
+                    float v[8], plain[8];
 #pragma unroll
                     for (int q = 0; q < 8; ++q) {
                         const float4 a = lds128(ca + (uint32_t)(g * 8 + q) * 16u);
@@ -179,11 +181,17 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int group, in
                             red = fmaf(o, wv4.x, red); green = fmaf(o, wv4.y, green); blue = fmaf(o, wv4.z, blue);
                         }
                         v[q] = o * a.z;
+                        plain[q] = o * kLreluGain;
                     }
                     if (dst != nullptr) {
                         Vec<T> packed;
                         packed.from_float(v);
                         packed.store(dst + g * 8);
+                    }
+                    if (!UP && !RGB && dst_plain != nullptr) {
+                        Vec<T> packed;
+                        packed.from_float(plain);
+                        packed.store(dst_plain + g * 8);
                     }
                 }
             }
@@ -961,7 +969,7 @@ static int launch_tensor_core_conv(const char* who, const void* x, int dtype, in
                                    int c_out, int pad, int up, int c_real, const void* weight, const float* demod,
                                    const float* noise, long long noise_batch_stride, float noise_strength,
                                    const float* bias, const float* next_styles, void* out, cudaStream_t s,
-                                   const RgbFusion* rgb = nullptr) {
+                                   const RgbFusion* rgb = nullptr, void* out_plain = nullptr) {
     GANCE_REQUIRE(dtype == GANCE_BF16 || dtype == GANCE_F16, GANCE_E_DTYPE, "%s: dtype %d", who, dtype);
     const bool half_operands = dtype == GANCE_F16;
     GANCE_REQUIRE(c_in % 32 == 0 && c_real % 32 == 0, GANCE_E_SHAPE,
@@ -992,7 +1000,9 @@ static int launch_tensor_core_conv(const char* who, const void* x, int dtype, in
     p.tile_w_log2 = ilog2(p.tile_w); p.tile_hw_log2 = ilog2(p.tile_w * p.tile_h); p.c_log2 = ilog2(c_real);
     p.a_tx_bytes = 0;  // set per instantiation (depends on BLOCK_K)
     p.demod = demod; p.noise = noise; p.noise_batch_stride = noise_batch_stride; p.noise_strength = noise_strength;
-    p.bias = bias; p.next_styles = next_styles; p.out = out;
+    p.bias = bias; p.next_styles = next_styles; p.out = out; p.out_plain = out_plain;
+    GANCE_REQUIRE(out_plain == nullptr || (!up && rgb == nullptr && c_in % 64 == 0 && c_in >= 128 && aligned16(out_plain)),
+                  GANCE_E_SHAPE, "%s: the unscaled second output needs a plain convolution with Cin %% 64 == 0, Cin >= 128", who);
     p.rgb_styles = rgb ? rgb->styles : nullptr; p.rgb_weight = rgb ? rgb->weight : nullptr;
     p.rgb_bias = rgb ? rgb->bias : nullptr; p.y_prev = rgb ? rgb->y_prev : nullptr;
     p.y_out = rgb ? rgb->y_out : nullptr; p.frames = rgb ? rgb->frames : nullptr;
@@ -1057,6 +1067,22 @@ extern "C" int gance_modconv3x3(const void* x, int dtype, int batch, int h_out, 
                                      (float*)out, s);
     return launch_tensor_core_conv("gance_modconv3x3", x, dtype, batch, h_out, w_out, c_in, c_out, pad, /*up=*/0, c_out,
                                    weight, demod, noise, noise_batch_stride, noise_strength, bias, next_styles, out, s);
+}
+
+extern "C" int gance_modconv3x3_dual(const void* x, int dtype, int batch, int h_out, int w_out, int c_in, int c_out,
+                                     int pad, const void* weight, const float* demod, const float* noise,
+                                     long long noise_batch_stride, float noise_strength, const float* bias,
+                                     const float* next_styles, void* out_scaled, void* out, void* stream) {
+    GANCE_REQUIRE(is_initialised(), GANCE_E_NOT_INIT, "gance_init() has not been called");
+    GANCE_REQUIRE(x && weight && demod && bias && out && out_scaled && next_styles, GANCE_E_NULL,
+                  "gance_modconv3x3_dual: NULL pointer");
+    GANCE_REQUIRE(out != out_scaled, GANCE_E_NULL, "gance_modconv3x3_dual: out and out_scaled must be distinct");
+    GANCE_REQUIRE(batch > 0 && h_out > 0 && w_out > 0 && c_in > 0 && c_out > 0 && (pad == 0 || pad == 1),
+                  GANCE_E_SHAPE, "gance_modconv3x3_dual: shape B=%d H=%d W=%d Cin=%d Cout=%d pad=%d", batch, h_out, w_out,
+                  c_in, c_out, pad);
+    return launch_tensor_core_conv("gance_modconv3x3_dual", x, dtype, batch, h_out, w_out, c_in, c_out, pad, /*up=*/0,
+                                   c_out, weight, demod, noise, noise_batch_stride, noise_strength, bias, next_styles,
+                                   out_scaled, (cudaStream_t)stream, nullptr, out);
 }
 
 extern "C" int gance_modconv3x3_torgb(const void* x, int dtype, int batch, int h, int w, int c_in, int c_out,

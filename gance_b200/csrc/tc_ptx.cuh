@@ -33,6 +33,7 @@ struct ConvParams {
     const float* bias;
     const float* next_styles;
     void* out;  // [B,h_out,w_out,c_out] bf16 or half; up: [B,2*h_out,2*w_out,c_real]
+    void* out_plain;  // optional second copy of `out` WITHOUT next_styles (generic kernel, !up only): what ToRGB reads
     int up;      // 1: folded up-convolution, GEMM column n = phase*c_real + co, phase = py*2+px -> pixel (2h+py, 2w+px)
     // fused ToRGB + skip (+ uint8), conv1 layers whose channels fit one N tile; all NULL otherwise
     const float* rgb_styles;  // [B, c_real]

@@ -333,14 +333,36 @@ class GeneratorOnDevice:
                                          x_in.data_ptr(), stream), "gance_const_input")
         x = self._buffer("act4", (batch, 4, 4, c0.out_channels), dt)
         nz, nz_stride = layer_noise(0, 4)
-        _lib.check(
-            lib.gance_modconv3x3(x_in.data_ptr(), code, batch, 4, 4, c0.in_channels, c0.out_channels, 1,
-                                 self.conv_w[0].data_ptr(), demods[0].data_ptr(), _ptr(nz), nz_stride,
-                                 self.conv_strength[0], self.conv_bias[0].data_ptr(), None, x.data_ptr(), stream),
-            "gance_modconv3x3(4x4)",
-        )
-        self._mark("4/conv")
         last = len(self.rgbs) - 1
+
+        def plain_conv(i: int, conv, side: int, x_src: torch.Tensor, x_dst: torch.Tensor, is_last: bool, nz, nz_stride):
+            """
+            A Conv layer whose ToRGB runs as its own kernel (Cout > 256, and the fp32 mode). In the 16-bit modes the
+            epilogue also writes the next block's modulated input x * styles[i + 1] (returned; None otherwise), which
+            used to be a gance_scale_channels pass over x.
+            """
+            dual = self.mode != "fp32" and not is_last and conv.in_channels % 64 == 0 and conv.in_channels >= 128
+            if not dual:
+                _lib.check(
+                    lib.gance_modconv3x3(x_src.data_ptr(), code, batch, side, side, conv.in_channels, conv.out_channels, 1,
+                                         self.conv_w[i].data_ptr(), demods[i].data_ptr(), _ptr(nz), nz_stride,
+                                         self.conv_strength[i], self.conv_bias[i].data_ptr(), None, x_dst.data_ptr(),
+                                         stream),
+                    f"gance_modconv3x3({side})",
+                )
+                return None
+            scaled = self._buffer(f"scaled{side}", (batch, side, side, conv.out_channels), dt)
+            _lib.check(
+                lib.gance_modconv3x3_dual(x_src.data_ptr(), code, batch, side, side, conv.in_channels, conv.out_channels, 1,
+                                          self.conv_w[i].data_ptr(), demods[i].data_ptr(), _ptr(nz), nz_stride,
+                                          self.conv_strength[i], self.conv_bias[i].data_ptr(), styles[i + 1].data_ptr(),
+                                          scaled.data_ptr(), x_dst.data_ptr(), stream),
+                f"gance_modconv3x3_dual({side})",
+            )
+            return scaled
+
+        x_scaled_next = plain_conv(0, c0, 4, x_in, x, last == 0, nz, nz_stride)
+        self._mark("4/conv")
         want_float = return_float_image or last != 0
         y = self._buffer("skip4", (batch, 4, 4, 4), torch.float32) if want_float else None
         _lib.check(
@@ -352,7 +374,9 @@ class GeneratorOnDevice:
         self._mark("4/torgb")
 
         # -- one block per resolution
-        x_prescaled = False  # True when `x` already carries the next up-convolution's styles
+        x_prescaled = x_scaled_next is not None  # True when `x` already carries the next up-convolution's styles
+        if x_prescaled:
+            x = x_scaled_next
         for block in range(1, len(self.rgbs)):
             up_i, conv_i = 2 * block - 1, 2 * block
             up, conv = self.convs[up_i], self.convs[conv_i]
@@ -433,14 +457,8 @@ class GeneratorOnDevice:
                 self._mark(f"{side}/conv1")
             else:
                 x = self._buffer(f"act{side}", (batch, side, side, conv.out_channels), dt)
-                _lib.check(
-                    lib.gance_modconv3x3(x_up.data_ptr(), code, batch, side, side, conv.in_channels,
-                                         conv.out_channels, 1, self.conv_w[conv_i].data_ptr(),
-                                         demods[conv_i].data_ptr(), _ptr(nz), nz_stride, self.conv_strength[conv_i],
-                                         self.conv_bias[conv_i].data_ptr(), None, x.data_ptr(), stream),
-                    f"gance_modconv3x3({side})",
-                )
-                x_prescaled = False
+                x_scaled_next = plain_conv(conv_i, conv, side, x_up, x, is_last, nz, nz_stride)
+                x_prescaled = x_scaled_next is not None
                 self._mark(f"{side}/conv1")
                 _lib.check(
                     lib.gance_torgb_skip(x.data_ptr(), code, batch, side, side, conv.out_channels,
@@ -450,6 +468,8 @@ class GeneratorOnDevice:
                     f"gance_torgb_skip({side})",
                 )
                 self._mark(f"{side}/torgb")
+                if x_prescaled:
+                    x = x_scaled_next
             y = y_out
         if return_float_image:
             return frames, y

@@ -125,6 +125,17 @@ int gance_modconv3x3(const void* x, int dtype, int batch, int h_out, int w_out, 
                      const float* noise, long long noise_batch_stride, float noise_strength,
                      const float* bias, const float* next_styles, void* out, void* stream);
 
+/* gance_modconv3x3 with TWO outputs from one epilogue: `out` = the activated layer output as G_synthesis_stylegan2's
+ * block() hands it to torgb() (no next_styles), `out_scaled` = the same values * next_styles[b,co], i.e. the
+ * modulated input `x * s` of the next block's Conv0_up (modulated_conv2d_layer's `x *= s`), rounded once from the
+ * fp32 accumulator instead of being re-read and re-rounded by gance_scale_channels. GANCE_BF16 / GANCE_F16,
+ * Cin % 64 == 0 and Cin >= 128 (the 4^2..64^2 Conv layers of config-e/f); arguments otherwise as gance_modconv3x3. */
+int gance_modconv3x3_dual(const void* x, int dtype, int batch, int h_out, int w_out, int c_in,
+                          int c_out, int pad, const void* weight, const float* demod,
+                          const float* noise, long long noise_batch_stride, float noise_strength,
+                          const float* bias, const float* next_styles, void* out_scaled, void* out,
+                          void* stream);
+
 /* ---- 2x FIR upsampling feeding the up-convolution ----------------------------------------------
  * First half of upsample_conv_2d in FIR-first form (tests/test_oracle_stylegan2.py proves
  * conv_transpose(stride 2) -> upfirdn([1,3,3,1]*4, pad 1,1) == VALID 3x3 conv of this tensor):

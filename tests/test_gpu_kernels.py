@@ -270,6 +270,48 @@ def test_modconv3x3_tcgen05_without_next_style_and_noise_per_sample(lib):
     assert rel_err(got, want) < 2.0 ** -7
 
 
+@pytest.mark.parametrize("mode", ["bf16", "fp16"])
+@pytest.mark.parametrize("cin,cout,side,batch", [(512, 512, 4, 3), (512, 512, 16, 2), (256, 512, 8, 1), (128, 128, 24, 2)])
+def test_modconv3x3_dual_writes_the_layer_output_and_the_next_modulated_input(lib, mode, cin, cout, side, batch):
+    """gance_modconv3x3_dual: `out` = the activated layer output (what ToRGB reads), `out_scaled` = out * next styles
+    (what the next block's Conv0_up reads), both from one epilogue; each against the fp64 computation."""
+    code, dt = MODE_CODES[mode]
+    g = torch.Generator().manual_seed(23)
+    x = torch.randn(batch, cin, side, side, dtype=F64, generator=g)
+    weight = torch.randn(3, 3, cin, cout, dtype=F64, generator=g) / np.sqrt(9 * cin)
+    demod = torch.rand(batch, cout, dtype=F64, generator=g) + 0.5
+    noise = torch.randn(batch, side, side, dtype=F64, generator=g)
+    bias = torch.randn(cout, dtype=F64, generator=g) * 0.1
+    nxt = torch.randn(batch, cout, dtype=F64, generator=g)
+    strength = 0.07
+    x_dev = dev(x.permute(0, 2, 3, 1), dt)
+    w_dev = dev(weight.permute(3, 0, 1, 2), dt)
+    acc = F.conv2d(x_dev.double().cpu().permute(0, 3, 1, 2), w_dev.double().cpu().permute(0, 3, 1, 2), padding=1)
+    want = acc * demod.float().double()[:, :, None, None] + noise.float().double()[:, None] * np.float32(strength)
+    want = F.leaky_relu(want + bias.float().double()[None, :, None, None], 0.2) * np.sqrt(2.0)
+    want_scaled = want * nxt.float().double()[:, :, None, None]
+    out = torch.full((batch, side, side, cout), float("nan"), device="cuda", dtype=dt)
+    out_scaled = torch.full_like(out, float("nan"))
+    _lib.check(
+        lib.gance_modconv3x3_dual(x_dev.data_ptr(), code, batch, side, side, cin, cout, 1, w_dev.data_ptr(),
+                                  dev(demod).data_ptr(), dev(noise).data_ptr(), side * side, strength,
+                                  dev(bias).data_ptr(), dev(nxt).data_ptr(), out_scaled.data_ptr(), out.data_ptr(),
+                                  stream()),
+        "gance_modconv3x3_dual",
+    )
+    torch.cuda.synchronize()
+    tol = {"bf16": 2.0 ** -7, "fp16": 2.0 ** -10}[mode]  # one rounding of each output
+    assert rel_err(out.permute(0, 3, 1, 2), want) < tol
+    assert rel_err(out_scaled.permute(0, 3, 1, 2), want_scaled) < tol
+    # arguments the entry refuses: the narrow layers run the halo kernel, which has no second output
+    assert lib.gance_modconv3x3_dual(x_dev.data_ptr(), code, batch, side, side, 64, 64, 1, w_dev.data_ptr(),
+                                     dev(demod).data_ptr(), None, 0, 0.0, dev(bias).data_ptr(), dev(nxt).data_ptr(),
+                                     out_scaled.data_ptr(), out.data_ptr(), stream()) > 0
+    assert lib.gance_modconv3x3_dual(x_dev.data_ptr(), code, batch, side, side, cin, cout, 1, w_dev.data_ptr(),
+                                     dev(demod).data_ptr(), None, 0, 0.0, dev(bias).data_ptr(), dev(nxt).data_ptr(),
+                                     out.data_ptr(), out.data_ptr(), stream()) > 0
+
+
 @pytest.mark.parametrize("mode", ["fp32", "bf16", "fp16"])
 def test_up_convolution_matches_oracle(lib, mode):
     """gance_modconv3x3_up2_fir against the reference's transposed-conv + upfirdn formulation."""
