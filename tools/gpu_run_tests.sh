@@ -13,10 +13,10 @@ run() { # name, pytest args...
 : > gpurun_out/summary.txt
 if [ "$1" != "quick" ]; then
   run audio tests/test_gpu_audio.py
-  run kernels_small tests/test_gpu_kernels.py -k "not modconv3x3 and not up_convolution"
+  run kernels_small tests/test_gpu_kernels.py -k "not modconv3x3 and not up_convolution and not dual"
   run conv_fp32 tests/test_gpu_kernels.py -k "fp32 and (modconv3x3 or up_convolution)"
 fi
-run conv_tc tests/test_gpu_kernels.py -k "tcgen05 or ((bf16 or fp16) and up_convolution)"
+run conv_tc tests/test_gpu_kernels.py -k "tcgen05 or dual or ((bf16 or fp16) and up_convolution)"
 run synthesis tests/test_gpu_synthesis.py
 run resize tests/test_gpu_resize.py
 run pipeline tests/test_gpu_pipeline.py
