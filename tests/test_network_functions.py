@@ -184,3 +184,27 @@ def test_c_abi_library_exports_every_declared_symbol():
     if not torch.cuda.is_available():
         assert lib.gance_init(0) != 0
         assert "no CPU fallback" in _lib.last_error()
+
+
+def test_c_abi_header_is_plain_c_and_matches_the_ctypes_signatures(tmp_path):
+    """include/gance_b200.h compiles as C99 on its own (the boundary is a C ABI, not C++), and every ctypes prototype in
+    gance_b200/_lib.py has as many parameters as the header's declaration."""
+    import re
+    import shutil
+    import subprocess
+
+    header_path = Path(__file__).resolve().parents[1] / "include" / "gance_b200.h"
+    gcc = shutil.which("gcc")
+    if gcc is not None:
+        done = subprocess.run([gcc, "-fsyntax-only", "-x", "c", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror",
+                               str(header_path)], capture_output=True, text=True)
+        assert done.returncode == 0, done.stderr
+    header = re.sub(r"/\*.*?\*/", "", header_path.read_text(), flags=re.S)
+    checked = 0
+    for name, params in re.findall(r"\b(gance_[a-z0-9_]+)\s*\(([^)]*)\)\s*;", header):
+        params = params.strip()
+        count = 0 if params in ("", "void") else len(params.split(","))
+        _, argtypes = _lib._SIGNATURES[name]
+        assert len(argtypes) == count, f"{name}: header declares {count} parameters, ctypes binds {len(argtypes)}"
+        checked += 1
+    assert checked == len(_lib.EXPORTED_SYMBOLS)
