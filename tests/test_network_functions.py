@@ -200,11 +200,25 @@ def test_c_abi_header_is_plain_c_and_matches_the_ctypes_signatures(tmp_path):
                                str(header_path)], capture_output=True, text=True)
         assert done.returncode == 0, done.stderr
     header = re.sub(r"/\*.*?\*/", "", header_path.read_text(), flags=re.S)
+
+    def c_type_of(declaration: str):
+        import ctypes
+
+        text = " ".join(declaration.replace("const", " ").split())
+        if "*" in text:
+            return ctypes.c_void_p
+        base = " ".join(text.split()[:-1])  # drop the parameter name
+        return {"int": ctypes.c_int, "float": ctypes.c_float, "double": ctypes.c_double,
+                "long long": ctypes.c_longlong, "unsigned long long": ctypes.c_ulonglong,
+                "size_t": ctypes.c_size_t}[base]
+
     checked = 0
     for name, params in re.findall(r"\b(gance_[a-z0-9_]+)\s*\(([^)]*)\)\s*;", header):
         params = params.strip()
         count = 0 if params in ("", "void") else len(params.split(","))
         _, argtypes = _lib._SIGNATURES[name]
         assert len(argtypes) == count, f"{name}: header declares {count} parameters, ctypes binds {len(argtypes)}"
+        for position, (declaration, bound) in enumerate(zip(params.split(",") if count else [], argtypes)):
+            assert bound is c_type_of(declaration), f"{name} parameter {position} ('{declaration.strip()}') is bound as {bound.__name__}"
         checked += 1
     assert checked == len(_lib.EXPORTED_SYMBOLS)
