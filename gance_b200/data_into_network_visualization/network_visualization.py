@@ -85,6 +85,8 @@ def create_network_frames(
             network_index, frame_indices = schedule[position]
             LOGGER.debug(f"Rendering frames {frame_indices[0]}..{frame_indices[-1]} on network {network_index}")
             images = networks.indexed_create_images_batch(network_index, latents[frame_indices])
+            if len(images) != len(frame_indices):  # one latent -> one frame, always (frame indexing is bit-exact)
+                raise RuntimeError(f"network {network_index} returned {len(images)} frames for {len(frame_indices)} latents")
             for image, frame_index in zip(images, frame_indices):
                 window_frames[int(frame_index) - window_start] = image
             position += 1

@@ -39,6 +39,9 @@ from gance_b200.vector_sources.vector_types import SingleMatrix, SingleVector, i
 
 TRUNCATION_PSI = 1.2  # hard-wired in the reference (:124, :155)
 DEFAULT_MODE = "fp16"  # operand type of the tcgen05 path; "bf16" and "fp32" (validation) also exist
+# Noise of the VECTOR path. The reference does not override `randomize_noise` in `Gs.run` (:151-158), so every call draws
+# fresh N(0,1) noise: "random". Parity tests set "const" (the network's noise buffers) to compare frames with the oracle.
+VECTOR_NOISE_MODE = "random"
 
 
 def sorted_networks_in_directory(networks_directory: Path) -> List[Path]:
@@ -117,7 +120,7 @@ def _wrap_generator(generator: GeneratorOnDevice, alive: Optional[List[bool]] = 
     def vectors(data: np.ndarray) -> torch.Tensor:
         # Gs.run(z, None, truncation_psi=1.2): randomize_noise is NOT overridden -> fresh noise
         z = torch.as_tensor(np.asarray(data, dtype=np.float32)).reshape(-1, 512)
-        return generator.run_vectors(z, truncation_psi=TRUNCATION_PSI, noise_mode="random")
+        return generator.run_vectors(z, truncation_psi=TRUNCATION_PSI, noise_mode=VECTOR_NOISE_MODE)
 
     def matrices(data: np.ndarray) -> torch.Tensor:
         # Gs.components.synthesis.run(w+, randomize_noise=False); truncation_psi is ignored there
@@ -142,25 +145,28 @@ def _wrap_generator(generator: GeneratorOnDevice, alive: Optional[List[bool]] = 
         return create_image_matrix(data)
 
     def create_images_batch(data: np.ndarray) -> np.ndarray:
+        """
+        The kind of a BATCH is its number of dimensions, never its length: (N,512) is always N vectors and
+        (N,rows,512) always N matrices - so a batch of exactly num_ws vectors stays num_ws frames. (A single
+        (num_ws,512) matrix belongs to `create_image_generic`, where the reference has that dispatch,
+        gance/vector_sources/vector_types.py:58-68.)
+        """
         check_alive()
         array = np.asarray(data)
-        if array.ndim == 2 and array.shape[-1] == 512 and array.shape[0] != num_ws:
+        if array.ndim not in (2, 3) or array.shape[-1] != 512:
+            raise ValueError(f"a batch is (N,512) vectors or (N,rows,512) matrices, got shape {array.shape}")
+        if array.ndim == 2:
             return to_host(vectors(array))
-        if array.ndim == 2:  # ambiguous (num_ws,512): the reference treats 2-D data as ONE matrix
-            return to_host(matrices(array[None]))
         return to_host(matrices(array))
-
-    renderers: Dict[tuple, BatchRenderer] = {}
 
     def render_batches(batches: Iterable[np.ndarray], max_batch: int = 32,
                        output_side_length: Optional[int] = None) -> Iterator[np.ndarray]:
         check_alive()
-        key = (max_batch, output_side_length)
-        renderer = renderers.get(key)
-        if renderer is None:
-            renderer = renderers[key] = BatchRenderer(generator, max_batch=max_batch, truncation_psi=TRUNCATION_PSI,
-                                                      output_side_length=output_side_length)
-        return renderer.render(batches)
+        # renderers (pinned host rings, device rings, captured graphs) live on the GENERATOR: an interface that is
+        # stopped and re-created by a MultiNetwork switch finds them again instead of re-allocating and re-capturing
+        renderer = generator.renderer(max_batch=max_batch, truncation_psi=TRUNCATION_PSI,
+                                      output_side_length=output_side_length)
+        return renderer.render(batches, check_alive=check_alive, vector_noise_mode=VECTOR_NOISE_MODE)
 
     return NetworkInterface(
         expected_vector_length=512,
@@ -184,25 +190,38 @@ class NetworkInterfaceInProcess(NamedTuple):
     stop_function: Callable[[], None]
 
 
-# Weights of every network this process has loaded, keyed by (resolved path, mode).
-_RESIDENT: Dict[Tuple[str, str], GeneratorOnDevice] = {}
+# Weights of every network this process has loaded, keyed by (resolved path, mode, device index).
+_RESIDENT: Dict[Tuple[str, str, int], GeneratorOnDevice] = {}
+# Live (not yet stopped) interfaces per resident generator: work buffers are only dropped when nobody uses them.
+_USERS: Dict[int, int] = {}
 
 
 def resident_generator(network_path: Path, mode: Optional[str] = None) -> GeneratorOnDevice:
-    """The GPU-resident generator for a network file, loading it on first use."""
+    """The GPU-resident generator for a network file on the current device, loading it on first use."""
     mode = mode or DEFAULT_MODE
-    key = (str(Path(network_path).resolve()), mode)
+    device = _device()
+    key = (str(Path(network_path).resolve()), mode, int(device.index))
     generator = _RESIDENT.get(key)
     if generator is None:
         network = load_network_network(Path(network_path), call_init_function=True)
-        generator = GeneratorOnDevice(network.spec, network.variables, _device(), mode=mode)
+        generator = GeneratorOnDevice(network.spec, network.variables, device, mode=mode)
         _RESIDENT[key] = generator
     return generator
 
 
+def release_idle_buffers() -> None:
+    """Drop the work buffers, renderers and captured graphs of every resident generator no live interface uses."""
+    for generator in _RESIDENT.values():
+        if _USERS.get(id(generator), 0) == 0:
+            generator.release_buffers()
+
+
 def evict_resident_networks() -> None:
     """Free every cached generator (the reference frees by killing its TF child, :303-321)."""
+    for generator in _RESIDENT.values():
+        generator.release_buffers()
     _RESIDENT.clear()
+    _USERS.clear()
     if torch.cuda.is_available():
         torch.cuda.empty_cache()
 
@@ -211,16 +230,21 @@ def create_network_interface_process(network_path: Path, mode: Optional[str] = N
     """
     Reference :232-340 spawns a TF worker and re-raises its start-up exception in the parent
     (:270-278). Here loading happens in-process, so a bad path / bad file / missing GPU raises
-    directly; `stop_function()` invalidates the interface (later calls raise RuntimeError) and
-    drops this interface's work buffers. The weights stay resident for fast switching; call
-    `evict_resident_networks()` to free them.
+    directly; `stop_function()` invalidates THIS interface (later calls through it raise RuntimeError) and nothing
+    else: weights, work buffers, renderers and captured CUDA graphs belong to the resident generator and survive, so
+    that a `MultiNetwork` switching back and forth (stop + load per switch, reference :543-563) pays a dictionary
+    lookup, and stopping one interface cannot pull buffers from under another interface of the same file.
+    `MultiNetwork.unload()` / `release_idle_buffers()` drop the work buffers of generators nobody uses;
+    `evict_resident_networks()` frees the weights too.
     """
     generator = resident_generator(network_path, mode or DEFAULT_MODE)
     alive = [True]
+    _USERS[id(generator)] = _USERS.get(id(generator), 0) + 1
 
     def stop_function() -> None:
-        alive[0] = False
-        generator.release_buffers()
+        if alive[0]:
+            alive[0] = False
+            _USERS[id(generator)] = max(0, _USERS.get(id(generator), 1) - 1)
 
     return NetworkInterfaceInProcess(
         network_interface=_wrap_generator(generator, alive), stop_function=stop_function
@@ -248,7 +272,11 @@ def _raise_exception_if_unloaded(function):
 
 
 class MultiNetwork:
-    """Switch between networks during a run (reference :484-640); switching costs a dict lookup."""
+    """
+    Switch between networks during a run (reference :484-640). Control flow is the reference's (stop the current
+    interface, load the next); because every network this process has loaded stays resident with its buffers and
+    graphs, a switch costs a dictionary lookup and a small closure, not a process spawn.
+    """
 
     def __init__(self: "MultiNetwork", network_paths: List[Path], load: bool = False) -> None:
         self._network_paths: List[Path] = network_paths
@@ -341,7 +369,9 @@ class MultiNetwork:
 
     @_raise_exception_if_unloaded
     def unload(self: "MultiNetwork") -> None:
+        """Reference :619-626 kills the TF child; here: stop the interface, then free work buffers nobody uses."""
         self._currently_loaded_network.stop_function()
+        release_idle_buffers()
 
     @property
     def network_indices(self: "MultiNetwork") -> List[int]:

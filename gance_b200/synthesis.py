@@ -85,7 +85,13 @@ def _ptr(tensor: Optional[torch.Tensor]) -> Optional[int]:
 class GeneratorOnDevice:
     """One generator's weights resident in HBM in kernel layout, plus per-batch work buffers."""
 
-    def __init__(self, spec: GeneratorSpec, variables: Dict[str, np.ndarray], device: torch.device, mode: str = "fp16") -> None:
+    def __init__(self, spec: GeneratorSpec, variables: Dict[str, np.ndarray], device: torch.device, mode: str = "fp16",
+                 noise_seed: Optional[int] = None) -> None:
+        """
+        noise_seed: Philox key of the "random" noise mode (the vector path's fresh noise per call). None draws one from
+        os.urandom, so two processes - or two ranks started from the same script - never share a noise stream; pass an
+        integer for a reproducible run (mix the rank in yourself when every rank passes the same number).
+        """
         if mode not in MODES:
             raise ValueError(f"mode must be one of {sorted(MODES)}, got {mode!r}")
         if device.type != "cuda":
@@ -100,11 +106,15 @@ class GeneratorOnDevice:
         self.convs, self.rgbs = synthesis_layers(spec)
         self._buffers: Dict[tuple, torch.Tensor] = {}
         self.profile_events: Optional[list] = None  # set to [] to collect (name, cuda event) marks
-        self.noise_seed = 0x5EED_0000_0000_0000 | (id(self) & 0xFFFF_FFFF)  # Philox key of the "random" noise mode
+        if noise_seed is None:
+            noise_seed = int.from_bytes(os.urandom(8), "little")
+        self.noise_seed = int(noise_seed) & 0x7FFF_FFFF_FFFF_FFFF
         # Philox stream position, on the device: advances with every batch (also across CUDA-graph replays)
         self.noise_counter = torch.zeros(1, dtype=torch.int64, device=device)
         self._graphs: Dict[tuple, tuple] = {}
+        self._renderers: Dict[tuple, "BatchRenderer"] = {}
         self.launches_per_replay = 0
+        self.graph_captures = 0  # how many CUDA graphs this generator has captured (tests: switching must not re-capture)
         self._upload(variables)
 
     # ---- weights ---------------------------------------------------------------------------------
@@ -222,16 +232,40 @@ class GeneratorOnDevice:
 
     # ---- buffers ---------------------------------------------------------------------------------
     def _buffer(self, name: str, shape: Sequence[int], dtype: torch.dtype) -> torch.Tensor:
-        key = (name, tuple(shape), dtype)
-        buf = self._buffers.get(key)
-        if buf is None:
-            buf = torch.empty(tuple(shape), dtype=dtype, device=self.device)
-            self._buffers[key] = buf
-        return buf
+        """
+        Work buffer `name` viewed as `shape`. One flat allocation per (name, dtype) sized for the LARGEST request so
+        far: batches of different sizes (the ragged per-network groups of a model-switching run) share it instead of
+        each batch size owning a full set of activations (10.7 GB per set at 1024^2 x 32). Growing a buffer moves
+        it, so the captured graphs (which hold addresses) are dropped and re-captured on next use; `reserve(batch)`
+        sizes everything up front.
+        """
+        numel = 1
+        for extent in shape:
+            numel *= int(extent)
+        key = (name, dtype)
+        flat = self._buffers.get(key)
+        if flat is None or flat.numel() < numel:
+            if flat is not None:
+                self._graphs.clear()
+            flat = torch.empty((max(numel, 1),), dtype=dtype, device=self.device)
+            self._buffers[key] = flat
+        return flat[:numel].view(tuple(shape))
 
     def release_buffers(self) -> None:
         self._graphs.clear()  # captured graphs hold the work buffers' addresses
+        self._renderers.clear()
         self._buffers.clear()
+
+    def renderer(self, max_batch: int = 32, truncation_psi: float = 1.2, output_side_length: Optional[int] = None,
+                 noise_mode: Optional[str] = None) -> "BatchRenderer":
+        """The BatchRenderer of this generator for a (batch, psi, output side, noise) combination, created once."""
+        side = None if output_side_length in (None, self.resolution) else int(output_side_length)
+        key = (int(max_batch), float(truncation_psi), side, noise_mode)
+        found = self._renderers.get(key)
+        if found is None:
+            found = self._renderers[key] = BatchRenderer(self, max_batch=max_batch, truncation_psi=truncation_psi,
+                                                         noise_mode=noise_mode, output_side_length=side)
+        return found
 
     def _stream(self) -> int:
         return torch.cuda.current_stream(self.device).cuda_stream
@@ -479,31 +513,48 @@ class GeneratorOnDevice:
         """Batched `Gs.run(z, None, truncation_psi=1.2)` (network_functions.py:151-158)."""
         return self.synthesis(self.mapping(z, truncation_psi), noise_mode=noise_mode, **kwargs)
 
-    def run_vectors_graphed(self, z: torch.Tensor, out: torch.Tensor, truncation_psi: float = 1.2,
-                            noise_mode: str = "random") -> torch.Tensor:
+    def _replay(self, kind: str, latents: torch.Tensor, out: torch.Tensor, truncation_psi: float, noise_mode: str) -> torch.Tensor:
         """
-        `run_vectors` replayed from a CUDA graph: the ~45 launches of a batch are captured once per (batch size,
-        output buffer, psi, noise mode) and replayed with one driver call - no per-launch CPU cost and back-to-back
-        kernels on the device. `z` is copied into the graph's static input; frames land in `out`.
+        One batch replayed from a CUDA graph: the ~45 launches are captured once per (kind, batch size, output buffer,
+        psi, noise mode) and replayed with one driver call - no per-launch CPU cost and back-to-back kernels on the
+        device. `latents` is copied into the graph's static input; frames land in `out`.
         """
-        z = z.to(self.device, torch.float32).reshape(-1, 512)
-        key = (z.shape[0], out.data_ptr(), float(truncation_psi), noise_mode)
+        key = (kind, latents.shape[0], out.data_ptr(), float(truncation_psi), noise_mode)
         entry = self._graphs.get(key)
         if entry is None:
-            static_z = z.clone()
-            self.run_vectors(static_z, truncation_psi=truncation_psi, noise_mode=noise_mode, out=out)  # warm-up: buffers
+            static_in = latents.clone()
+
+            def run() -> None:
+                if kind == "vectors":
+                    self.run_vectors(static_in, truncation_psi=truncation_psi, noise_mode=noise_mode, out=out)
+                else:
+                    self.synthesis(static_in, noise_mode=noise_mode, out=out)
+
+            run()  # warm-up: allocates the work buffers
             torch.cuda.current_stream(self.device).synchronize()
             graph = torch.cuda.CUDAGraph()
             launches_before = _lib.launch_count()
             with torch.cuda.graph(graph):
-                self.run_vectors(static_z, truncation_psi=truncation_psi, noise_mode=noise_mode, out=out)
+                run()
             self.launches_per_replay = _lib.launch_count() - launches_before  # kernels of ours inside one replay
-            entry = (graph, static_z)
+            self.graph_captures += 1
+            entry = (graph, static_in, self.launches_per_replay)
             self._graphs[key] = entry
-        graph, static_z = entry
-        static_z.copy_(z, non_blocking=True)
+        graph, static_in, self.launches_per_replay = entry
+        static_in.copy_(latents, non_blocking=True)
         graph.replay()
         return out
+
+    def run_vectors_graphed(self, z: torch.Tensor, out: torch.Tensor, truncation_psi: float = 1.2,
+                            noise_mode: str = "random") -> torch.Tensor:
+        """`run_vectors` as one CUDA-graph replay (see `_replay`)."""
+        z = z.to(self.device, torch.float32).reshape(-1, 512)
+        return self._replay("vectors", z, out, truncation_psi, noise_mode)
+
+    def run_matrices_graphed(self, wplus: torch.Tensor, out: torch.Tensor, noise_mode: str = "const") -> torch.Tensor:
+        """`run_matrices` as one CUDA-graph replay: w+ [B,num_ws,512] -> frames in `out`."""
+        wplus = wplus.to(self.device, torch.float32).reshape(-1, self.num_ws, 512)
+        return self._replay("matrices", wplus, out, 1.0, noise_mode)
 
     def run_matrices(self, wplus: torch.Tensor, **kwargs):
         """Batched `Gs.components.synthesis.run(w+, randomize_noise=False)` (network_functions.py:167-169)."""
@@ -556,14 +607,19 @@ class BatchRenderer:
         self.bytes_h2d = 0
         self.bytes_d2h = 0
 
-    def _submit(self, slot: int, latents: np.ndarray) -> int:
+    def _submit(self, slot: int, latents: np.ndarray, vector_noise_mode: str = "random") -> int:
+        """
+        One batch: (512,) / (N,512) are vectors, (N,rows,512) are matrices - the kind of a batch is its number of
+        dimensions, never its length (a batch of exactly num_ws vectors is num_ws frames). A single (num_ws,512) matrix
+        must arrive as (1,num_ws,512).
+        """
         gen = self.generator
         array = np.asarray(latents, dtype=np.float32)
-        is_vectors = array.ndim == 2 and array.shape[-1] == 512 and array.shape[0] != gen.num_ws or array.ndim == 1
         if array.ndim == 1:
             array = array[None]
-        if not is_vectors and array.ndim == 2:
-            array = array[None]
+        if array.ndim not in (2, 3) or array.shape[-1] != 512:
+            raise ValueError(f"a batch is (N,512) vectors or (N,rows,512) matrices, got shape {array.shape}")
+        is_vectors = array.ndim == 2
         n = array.shape[0]
         if n > self.max_batch:
             raise ValueError(f"batch of {n} exceeds max_batch {self.max_batch}")
@@ -578,8 +634,17 @@ class BatchRenderer:
         on_device = staged.to(gen.device, non_blocking=True)
         self.bytes_h2d += array.size * 4
         out = self.frames_dev[slot][:n]
+        # full batches and multiples of 8 replay a captured graph; the odd-sized groups a model-switching window leaves
+        # over run eagerly (same C-ABI calls), so a run never holds more than a handful of graphs per network
+        graphed = n == self.max_batch or n % 8 == 0
         if is_vectors:
-            gen.run_vectors_graphed(on_device, out, truncation_psi=self.truncation_psi, noise_mode=self.noise_mode or "random")
+            noise_mode = self.noise_mode or vector_noise_mode
+            if graphed:
+                gen.run_vectors_graphed(on_device, out, truncation_psi=self.truncation_psi, noise_mode=noise_mode)
+            else:
+                gen.run_vectors(on_device, truncation_psi=self.truncation_psi, noise_mode=noise_mode, out=out)
+        elif graphed:
+            gen.run_matrices_graphed(on_device, out, noise_mode=self.noise_mode or "const")
         else:
             gen.synthesis(on_device, noise_mode=self.noise_mode or "const", out=out)
         if self.resizer is not None:
@@ -593,12 +658,14 @@ class BatchRenderer:
         self.bytes_d2h += n * out[0].numel()
         return n
 
-    def render(self, batches: Iterable[np.ndarray]) -> Iterator[np.ndarray]:
+    def render(self, batches: Iterable[np.ndarray], check_alive=None, vector_noise_mode: str = "random") -> Iterator[np.ndarray]:
         pending: List[tuple] = []
         index = 0
         for latents in batches:
+            if check_alive is not None:
+                check_alive()  # the interface this iterator was drawn from may have been stopped meanwhile
             slot = index % self.depth
-            n = self._submit(slot, latents)
+            n = self._submit(slot, latents, vector_noise_mode)
             pending.append((slot, n))
             index += 1
             if len(pending) == self.depth:  # keep depth-1 batches in flight

@@ -381,7 +381,8 @@ def test_folded_up_convolution_matches_oracle(lib, mode, cin, cout, side, batch)
 
 @pytest.mark.parametrize("mode", ["bf16", "fp16"])
 @pytest.mark.parametrize("cin,cout,side,batch,last", [(64, 64, 32, 2, False), (32, 32, 32, 3, True), (128, 128, 16, 2, False),
-                                                     (256, 256, 16, 1, False), (64, 32, 16, 2, True)])
+                                                     (256, 256, 16, 1, False), (64, 32, 16, 2, True),
+                                                     (64, 64, 32, 2, True), (64, 64, 16, 3, True)])  # last block of a 512^2 network
 def test_fused_conv_torgb_matches_oracle(lib, mode, cin, cout, side, batch, last):
     """gance_modconv3x3_torgb: Conv1 epilogue + ToRGB + skip upsample (+ uint8) against float64 arithmetic."""
     code, dt = MODE_CODES[mode]

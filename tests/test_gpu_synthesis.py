@@ -198,3 +198,73 @@ def test_graph_replay_equals_eager_and_draws_fresh_noise():
     second = gen.run_vectors_graphed(z_dev, out, noise_mode="random").clone()
     third = gen.run_vectors_graphed(z_dev, out, noise_mode="random").clone()
     assert not torch.equal(first, second) and not torch.equal(second, third)
+
+
+@pytest.mark.parametrize("mode", ["fp16", "fp32"])
+def test_512_generator_matches_oracle(mode):
+    """
+    A 512^2 config-f generator end to end (BASELINE config 5 names 512^2 networks). Its last block runs the 64-channel
+    halo kernel with ToRGB + uint8 fused and NO activation output, a flavour no other size exercises.
+    """
+    spec, variables, oracle, z = _case(512, 7, True, 2)
+    gen = GeneratorOnDevice(spec, variables, _device(), mode=mode)
+    frames, image = gen.run_vectors(torch.as_tensor(z), noise_mode="const", return_float_image=True)
+    assert frames.shape == (2, 512, 512, 3)
+    want = oracle.run_vector(z)
+    got = image[..., :3].permute(0, 3, 1, 2).double().cpu()
+    max_abs = float((got - want).abs().max())
+    within, worst, exact = lsb_stats(frames.cpu().numpy(), ref.convert_images_to_uint8(want))
+    print(f"512^2 {mode}: float max-abs {max_abs:.3e}; uint8 exact {exact:.5f} within1 {within:.5f} worst {worst}")
+    if mode == "fp32":
+        assert max_abs < 1e-3
+    assert within >= 0.999, (within, worst)
+    # the production call (no float image requested: the last block writes uint8 only) gives the same frames
+    assert torch.equal(gen.run_vectors(torch.as_tensor(z), noise_mode="const"), frames)
+    gen.release_buffers()
+
+
+@pytest.mark.parametrize("resolution", [256, 1024])
+def test_fp32_mode_max_abs_at_the_sizes_the_configs_name(resolution):
+    """north_star: fp32-mode images within 1e-3 max-abs in [-1,1] - at 256^2 (config 1) and 1024^2 (config 2), one frame."""
+    spec, variables, oracle, z = _case(resolution, 8, True, 1)
+    gen = GeneratorOnDevice(spec, variables, _device(), mode="fp32")
+    frames, image = gen.run_vectors(torch.as_tensor(z), noise_mode="const", return_float_image=True)
+    want = oracle.run_vector(z)
+    got = image[..., :3].permute(0, 3, 1, 2).double().cpu()
+    max_abs = float((got - want).abs().max())
+    within, worst, exact = lsb_stats(frames.cpu().numpy(), ref.convert_images_to_uint8(want))
+    print(f"fp32 mode {resolution}^2: max-abs {max_abs:.3e} (|image| max {float(want.abs().max()):.2f}); "
+          f"uint8 exact {exact:.5f} within1 {within:.5f} worst {worst}")
+    assert max_abs < 1e-3
+    assert within >= 0.999
+    gen.release_buffers()
+
+
+def test_config2_batch32_provided_noise_frames_match_oracle():
+    """
+    BASELINE config 2 the way the bench runs it - batch 32, 1024^2, per-sample noise on every layer - with the noise
+    handed to both sides (`noise_mode="provided"` = what tf.random_normal would have drawn): frames 0, 13 and 31 of the
+    batch against the fp64 oracle, and the graph-replayed const-noise batch against the eager one.
+    """
+    spec, variables, oracle, z = _case(1024, 9, True, 32)
+    gen = GeneratorOnDevice(spec, variables, _device(), mode="fp16")
+    generator = torch.Generator().manual_seed(17)
+    noise = [torch.randn(32, c.out_resolution, c.out_resolution, generator=generator) for c in gen.convs]
+    frames = gen.run_vectors(torch.as_tensor(z), noise_mode="provided", noise=noise).cpu().numpy()
+    for index in (0, 13, 31):
+        sample_noise = [n[index: index + 1, None].numpy() for n in noise]
+        want = ref.convert_images_to_uint8(oracle.run_vector(z[index: index + 1], noise=sample_noise))
+        within, worst, exact = lsb_stats(frames[index: index + 1], want)
+        print(f"1024^2 fp16 batch-32 frame {index}: exact {exact:.5f} within1 {within:.5f} worst {worst}")
+        assert within >= 0.999, (index, within, worst)
+    z_dev = torch.as_tensor(z, dtype=torch.float32, device=gen.device)
+    eager = gen.run_vectors(z_dev, noise_mode="const").clone()
+    out = torch.empty_like(eager)
+    gen.run_vectors_graphed(z_dev, out, noise_mode="const")
+    gen.run_vectors_graphed(z_dev, out, noise_mode="const")
+    assert torch.equal(out, eager)
+    wplus = gen.mapping(z_dev)
+    gen.run_matrices_graphed(wplus, out)  # the matrix path's replay: synthesis only, constant noise
+    gen.run_matrices_graphed(wplus, out)
+    assert torch.equal(out, eager)
+    gen.release_buffers()

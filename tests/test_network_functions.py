@@ -222,3 +222,96 @@ def test_c_abi_header_is_plain_c_and_matches_the_ctypes_signatures(tmp_path):
             assert bound is c_type_of(declaration), f"{name} parameter {position} ('{declaration.strip()}') is bound as {bound.__name__}"
         checked += 1
     assert checked == len(_lib.EXPORTED_SYMBOLS)
+
+
+class _FakeGenerator:
+    """Duck-typed GeneratorOnDevice for the CPU dispatch tests: frames encode which path rendered them."""
+
+    def __init__(self, num_ws: int) -> None:
+        import torch
+
+        self.num_ws = num_ws
+        self.torch = torch
+        self.calls = []
+
+    def run_vectors(self, z, truncation_psi=1.2, noise_mode="random", **_):
+        self.calls.append(("vectors", tuple(z.shape), noise_mode))
+        return self.torch.full((z.shape[0], 2, 2, 3), 1, dtype=self.torch.uint8)
+
+    def run_matrices(self, wplus, **_):
+        self.calls.append(("matrices", tuple(wplus.shape)))
+        return self.torch.full((wplus.shape[0], 2, 2, 3), 2, dtype=self.torch.uint8)
+
+
+@pytest.mark.parametrize("num_ws", [14, 16, 18])
+def test_a_batch_of_exactly_num_ws_vectors_is_num_ws_frames(num_ws):
+    """
+    The kind of a batch is its number of dimensions, never its length (round-1 bug: an (N,512) batch with N == num_ws was
+    rendered as ONE matrix frame). The single-matrix dispatch stays where the reference has it: `create_image_generic`
+    (gance/vector_sources/vector_types.py:58-68).
+    """
+    generator = _FakeGenerator(num_ws)
+    interface = network_functions._wrap_generator(generator)  # pylint: disable=protected-access
+    for count in (1, num_ws - 1, num_ws, num_ws + 1, 32):
+        frames = interface.create_images_batch(np.zeros((count, 512)))
+        assert frames.shape == (count, 2, 2, 3) and int(frames.max()) == 1, (count, generator.calls[-1])
+        assert generator.calls[-1][:2] == ("vectors", (count, 512))
+    for count in (1, num_ws, 5):
+        frames = interface.create_images_batch(np.zeros((count, 18, 512)))
+        assert frames.shape == (count, 2, 2, 3) and int(frames.min()) == 2
+        assert generator.calls[-1] == ("matrices", (count, num_ws, 512))  # an 18-row projection feeds num_ws rows
+    # one (num_ws,512) matrix / one (512,) vector: the reference's generic dispatch
+    assert int(interface.create_image_generic(np.zeros((num_ws, 512))).max()) == 2
+    assert int(interface.create_image_generic(np.zeros((512,))).max()) == 1
+    for bad in (np.zeros((512,)), np.zeros((3, 100)), np.zeros((2, 3, 18, 512))):
+        with pytest.raises(ValueError):
+            interface.create_images_batch(bad)
+    with pytest.raises(ValueError):
+        interface.create_images_batch(np.zeros((2, num_ws - 1, 512)))  # too few rows for this network
+
+
+def test_create_network_frames_refuses_a_frame_count_mismatch():
+    """One latent -> one frame: a backend that returns fewer images than latents must not be papered over with None."""
+    from gance_b200.data_into_network_visualization import network_visualization
+
+    class Short:
+        network_indices = [0]
+
+        def indexed_create_images_batch(self, index, data):  # pylint: disable=unused-argument
+            return np.zeros((1, 2, 2, 3), np.uint8)
+
+    with pytest.raises(RuntimeError):
+        list(network_visualization.create_network_frames(np.zeros((18, 512)), np.zeros(18, int), Short(), 32, False))
+
+
+def test_stopping_an_interface_keeps_the_generator_buffers_and_unload_releases_idle_ones():
+    """
+    A MultiNetwork switch is stop + load (reference :543-563). Here the stop only invalidates the interface: work buffers,
+    renderers and graphs stay on the resident generator, and are dropped by `unload()` once nobody uses the generator.
+    """
+    released = []
+
+    class Resident(_FakeGenerator):
+        def release_buffers(self):
+            released.append(self)
+
+    a, b = Resident(18), Resident(16)
+    generators = {"a.pkl": a, "b.pkl": b}
+    with mock.patch.object(network_functions, "resident_generator", side_effect=lambda path, mode=None: generators[Path(path).name]), \
+            mock.patch.dict(network_functions._RESIDENT, {("a", "fp16", 0): a, ("b", "fp16", 0): b}, clear=True), \
+            mock.patch.dict(network_functions._USERS, {}, clear=True):
+        net = MultiNetwork([Path("a.pkl"), Path("b.pkl")], load=True)
+        other = network_functions.create_network_interface_process(Path("a.pkl"))  # a second user of the same file
+        first = net._currently_loaded_network  # pylint: disable=protected-access
+        for index in (1, 0, 1, 0):
+            assert net.indexed_create_images_batch(index, np.zeros((3, 512))).shape == (3, 2, 2, 3)
+        assert released == []  # switching never drops buffers
+        with pytest.raises(RuntimeError):
+            first.network_interface.create_image_vector(np.zeros(512))  # a stopped interface is dead
+        assert other.network_interface.create_image_vector(np.zeros(512)).shape == (2, 2, 3)  # ... the other one is not
+        net.unload()
+        assert released == [b]  # `a` still has a live user
+        other.stop_function()
+        other.stop_function()  # idempotent
+        network_functions.release_idle_buffers()
+        assert a in released
