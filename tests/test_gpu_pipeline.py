@@ -46,7 +46,18 @@ def pipeline(tmp_path_factory):
     as_float = audio_ref.wav_to_float32(wav)
     audio = music.read_wavs_scale_for_video([music.WavFileProperties(44100, as_float, "swell")], 512, frames_per_second=FPS)
     num_frames = len(audio.wav_data) // 512
-    projection = MatricesLabel(synthetic.projection_latents(num_frames // 2), 512, "synthetic")  # projection_fps = fps / 2
+    # the projection arrives the way gance/projection_file_blend.py:122-126 gets it: from an HDF5 projection file on disk
+    from gance_b200.projection import projection_file_reader, projector_file_writer
+
+    walk = synthetic.projection_latents(num_frames // 2)  # projection_fps = fps / 2
+    projection_path = projector_file_writer.write_projection_file(
+        directory / "projection.hdf5", projector_file_writer.matrices_to_frames(walk),
+        projector_file_writer.synthetic_attributes(num_frames // 2, projection_fps=FPS / 2))
+    projection_file_reader.verify_projection_file_assumptions(projection_path)
+    with projection_file_reader.load_projection_file(projection_path) as reader:
+        projection = projection_file_reader.final_latents_matrices_label(reader)
+        assert reader.projection_attributes.projection_fps * 2 == FPS
+    assert isinstance(projection, MatricesLabel) and np.array_equal(projection.data, walk)
     data = visualization_inputs.alpha_blend_projection_file(
         final_latents_matrices_label=projection, alpha=0.25, fft_roll_enabled=True, fft_amplitude_range=(-5, 5),
         blend_depth=12, time_series_audio_vectors=audio.wav_data, vector_length=512, network_indices=[0, 1, 2])
