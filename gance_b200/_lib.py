@@ -20,6 +20,7 @@ _SIGNATURES = {
     "gance_init": (c_int, [c_int]),
     "gance_last_error_string": (c_char_p, []),
     "gance_launch_count": (c_ulonglong, []),
+    "gance_set_nonfinite_flag": (c_int, [c_void_p]),
     "gance_mapping": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_float, c_int, c_void_p, c_void_p]),
     "gance_style_demod": (
         c_int,
@@ -107,8 +108,15 @@ _LIB: Optional[ctypes.CDLL] = None
 _INITIALISED_DEVICES = set()
 
 
+GANCE_E_NONFINITE = 7
+
+
 class GanceError(RuntimeError):
     """A libgance_b200 entry returned non-zero."""
+
+
+class NonFiniteFramesError(GanceError):
+    """GANCE_E_NONFINITE: rendered frames held inf/NaN pixels - a 16-bit activation overflowed (include/gance_b200.h)."""
 
 
 def load_library() -> ctypes.CDLL:

@@ -134,9 +134,22 @@ __device__ __forceinline__ float4 upsample_tap(const float* __restrict__ y_prev,
 
 __device__ __forceinline__ uint8_t to_u8(float v) {
     // convert_images_to_uint8: v*127.5 + 128, saturate_cast<uint8> = clamp then truncate
-    float s = fmaf(v, 127.5f, 128.0f);
+    // (a separately rounded fp32 multiply, then add - what TF's graph does and what the oracle states; not an FMA)
+    float s = __fadd_rn(__fmul_rn(v, 127.5f), 128.0f);
     s = fminf(fmaxf(s, 0.0f), 255.0f);
     return (uint8_t)(int)s;
 }
+
+// Range guard of the 16-bit modes. Activations are stored as IEEE half / bfloat16 already multiplied by the next
+// layer's style; a network with a large style overflows half's 65504 to inf, and every later layer carries the inf / NaN
+// into the RGB skip sum - so testing the pixels of the FINAL image (fp32) catches an overflow anywhere upstream, at
+// three instructions per pixel in the one kernel that writes frames. Without it `fmaxf(NaN, 0) = 0` would turn the
+// damage into plausible black pixels.
+__device__ __forceinline__ void flag_nonfinite(int* flag, float red, float green, float blue) {
+    const float sum = red + green + blue;  // non-finite iff any of the three is
+    if (flag != nullptr && !(fabsf(sum) <= 3.0e38f)) atomicOr(flag, 1);
+}
+
+int* nonfinite_flag();  // runtime.cu: the device int registered with gance_set_nonfinite_flag, or nullptr
 
 }  // namespace gance

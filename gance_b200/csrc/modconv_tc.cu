@@ -206,6 +206,7 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int group, in
             if (p.frames != nullptr) {
                 uint8_t* f = p.frames + pixel * 3;
                 f[0] = to_u8(red); f[1] = to_u8(green); f[2] = to_u8(blue);
+                flag_nonfinite(p.nonfinite, red, green, blue);
             }
         }
     }
@@ -471,6 +472,7 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
             if (p.frames != nullptr) {
                 uint8_t* f = p.frames + pixel * 3;
                 f[0] = to_u8(red); f[1] = to_u8(green); f[2] = to_u8(blue);
+                flag_nonfinite(p.nonfinite, red, green, blue);
             }
         }
     }
@@ -1006,6 +1008,7 @@ static int launch_tensor_core_conv(const char* who, const void* x, int dtype, in
     p.rgb_styles = rgb ? rgb->styles : nullptr; p.rgb_weight = rgb ? rgb->weight : nullptr;
     p.rgb_bias = rgb ? rgb->bias : nullptr; p.y_prev = rgb ? rgb->y_prev : nullptr;
     p.y_out = rgb ? rgb->y_out : nullptr; p.frames = rgb ? rgb->frames : nullptr;
+    p.nonfinite = nonfinite_flag();
     const bool one_n_tile = rgb != nullptr;  // the fused ToRGB needs every channel of a pixel in one tile
     GANCE_REQUIRE(!one_n_tile || (up == 0 && (c_out == 256 || c_out == 128 || c_out == 64 || c_out == 32)), GANCE_E_SHAPE,
                   "%s: fused ToRGB needs Cout in {32,64,128,256} (got %d)", who, c_out);

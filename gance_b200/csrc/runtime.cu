@@ -25,6 +25,16 @@ int fail(int code, const char* fmt, ...) {
 
 bool is_initialised() { return g_initialised.load(std::memory_order_acquire) != 0; }
 
+// one registered range-guard flag per device (a flag lives in ONE device's memory; kernels of another device must not
+// be handed it)
+constexpr int kMaxDevices = 64;
+static std::atomic<int*> g_nonfinite_flag[kMaxDevices];
+int* nonfinite_flag() {
+    int device = 0;
+    if (cudaGetDevice(&device) != cudaSuccess || device < 0 || device >= kMaxDevices) return nullptr;
+    return g_nonfinite_flag[device].load(std::memory_order_acquire);
+}
+
 int init_tensor_core_path();  // modconv_tc.cu
 
 }  // namespace gance
@@ -36,6 +46,15 @@ int gance_abi_version(void) { return GANCE_ABI_VERSION; }
 const char* gance_last_error_string(void) { return gance::error_buffer(); }
 
 unsigned long long gance_launch_count(void) { return gance::g_launches.load(); }
+
+int gance_set_nonfinite_flag(int* device_flag) {
+    int device = 0;
+    cudaError_t err = cudaGetDevice(&device);
+    if (err != cudaSuccess) return gance::fail(-(int)err, "gance_set_nonfinite_flag: %s", cudaGetErrorString(err));
+    GANCE_REQUIRE(device >= 0 && device < gance::kMaxDevices, GANCE_E_SHAPE, "gance_set_nonfinite_flag: device %d", device);
+    gance::g_nonfinite_flag[device].store(device_flag, std::memory_order_release);
+    return GANCE_OK;
+}
 
 int gance_init(int device) {
     int count = 0;

@@ -332,7 +332,7 @@ __global__ void __launch_bounds__(256) torgb_skip_kernel(const T* __restrict__ x
                                                          const float* __restrict__ bias,
                                                          const float* __restrict__ y_prev,
                                                          float* __restrict__ y_out,
-                                                         uint8_t* __restrict__ frames) {
+                                                         uint8_t* __restrict__ frames, int* nonfinite) {
     constexpr int V = Vec<T>::N;
     // [3][V][channels / V]: channel c = cv * V + k sits at slot k * (channels / V) + cv, so the lanes of a group
     // (consecutive cv, same k) read consecutive words - [channels][3] order put them 3 * V words apart, an 8-way
@@ -385,18 +385,20 @@ __global__ void __launch_bounds__(256) torgb_skip_kernel(const T* __restrict__ x
             if (frames != nullptr) {
                 uint8_t* f = frames + ((size_t)b * pixels + p) * 3;
                 f[0] = to_u8(r); f[1] = to_u8(g); f[2] = to_u8(bl);
+                flag_nonfinite(nonfinite, r, g, bl);
             }
         }
     }
 }
 
-__global__ void to_uint8_kernel(const float4* __restrict__ y, size_t pixels, uint8_t* __restrict__ frames) {
+__global__ void to_uint8_kernel(const float4* __restrict__ y, size_t pixels, uint8_t* __restrict__ frames, int* nonfinite) {
     for (size_t p = blockIdx.x * (size_t)blockDim.x + threadIdx.x; p < pixels;
          p += (size_t)gridDim.x * blockDim.x) {
         float4 v = y[p];
         frames[p * 3 + 0] = to_u8(v.x);
         frames[p * 3 + 1] = to_u8(v.y);
         frames[p * 3 + 2] = to_u8(v.z);
+        flag_nonfinite(nonfinite, v.x, v.y, v.z);
     }
 }
 
@@ -569,7 +571,7 @@ static int launch_torgb(const void* x, int batch, int h, int w, int channels, co
     dim3 grid(gx, batch);
 #define GANCE_TORGB(L)                                                                                   \
     torgb_skip_kernel<T, L><<<grid, 256, smem, s>>>((const T*)x, h, w, channels, styles, weight, bias, \
-                                                    y_prev, y_out, frames)
+                                                    y_prev, y_out, frames, nonfinite_flag())
     switch (lanes) {
         case 1: GANCE_TORGB(1); break;
         case 2: GANCE_TORGB(2); break;
@@ -754,7 +756,7 @@ int gance_to_uint8_nhwc(const float* y, int batch, int h, int w, uint8_t* frames
     GANCE_REQUIRE(y && frames, GANCE_E_NULL, "gance_to_uint8_nhwc: NULL pointer");
     GANCE_REQUIRE(batch > 0 && h > 0 && w > 0, GANCE_E_SHAPE, "gance_to_uint8_nhwc: shape");
     size_t pixels = (size_t)batch * h * w;
-    to_uint8_kernel<<<grid_for(pixels, 256), 256, 0, (cudaStream_t)stream>>>((const float4*)y, pixels, frames);
+    to_uint8_kernel<<<grid_for(pixels, 256), 256, 0, (cudaStream_t)stream>>>((const float4*)y, pixels, frames, nonfinite_flag());
     return check_launch("to_uint8_kernel");
 }
 

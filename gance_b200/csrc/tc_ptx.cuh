@@ -42,6 +42,7 @@ struct ConvParams {
     const float* y_prev;      // [B, H/2, W/2, 4] f32 or NULL
     float* y_out;             // [B, H, W, 4] f32 or NULL
     uint8_t* frames;          // [B, H, W, 3] u8 or NULL
+    int* nonfinite;           // registered range-guard flag (gance_set_nonfinite_flag) or NULL
     int c_real;  // channels of `out` (= c_out when !up, c_out/4 when up); demod/bias/next_styles are indexed by co
 };
 

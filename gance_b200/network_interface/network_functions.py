@@ -115,7 +115,11 @@ def _wrap_generator(generator: GeneratorOnDevice, alive: Optional[List[bool]] = 
             raise RuntimeError("This network interface has been stopped")
 
     def to_host(frames: torch.Tensor) -> np.ndarray:
-        return frames.cpu().numpy()
+        on_host = frames.cpu().numpy()
+        check_finite = getattr(generator, "check_finite", None)
+        if check_finite is not None:
+            check_finite()  # GANCE_E_NONFINITE instead of silently black pixels when a 16-bit activation overflowed
+        return on_host
 
     def vectors(data: np.ndarray) -> torch.Tensor:
         # Gs.run(z, None, truncation_psi=1.2): randomize_noise is NOT overridden -> fresh noise

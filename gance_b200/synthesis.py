@@ -78,6 +78,32 @@ def phase_up_weight(hwio: torch.Tensor, chunk: int = PHASE_CHUNK) -> torch.Tenso
     return torch.cat(rows, dim=0).contiguous()
 
 
+_NONFINITE_FLAGS: Dict[int, torch.Tensor] = {}
+
+
+def nonfinite_flag(device: torch.device) -> torch.Tensor:
+    """
+    The device's range-guard flag (include/gance_b200.h, gance_set_nonfinite_flag): an int32 the frame-writing kernels
+    set when a pixel of the final fp32 image is inf/NaN, i.e. when an activation overflowed the 16-bit storage type
+    anywhere upstream. One per device, registered with the library on first use.
+    """
+    index = device.index if device.index is not None else torch.cuda.current_device()
+    flag = _NONFINITE_FLAGS.get(index)
+    if flag is None:
+        flag = torch.zeros(1, dtype=torch.int32, device=torch.device("cuda", index))
+        with torch.cuda.device(index):
+            _lib.check(_lib.init(index).gance_set_nonfinite_flag(flag.data_ptr()), "gance_set_nonfinite_flag")
+        _NONFINITE_FLAGS[index] = flag
+    return flag
+
+
+def nonfinite_error(mode: str) -> _lib.NonFiniteFramesError:
+    return _lib.NonFiniteFramesError(
+        f"GANCE_E_NONFINITE (code {_lib.GANCE_E_NONFINITE}): rendered frames hold inf/NaN pixels - an activation left the "
+        f"range of the {mode!r} storage type (IEEE half tops out at 65504; a style or weight of this network is too "
+        "large for it). Load the network with mode='bf16' (fp32 range, 8-bit significand) or mode='fp32'.")
+
+
 def _ptr(tensor: Optional[torch.Tensor]) -> Optional[int]:
     return None if tensor is None else tensor.data_ptr()
 
@@ -101,6 +127,7 @@ class GeneratorOnDevice:
         self.mode = mode
         self.dtype_code, self.torch_dtype = MODES[mode]
         self.lib = _lib.init(device.index if device.index is not None else torch.cuda.current_device())
+        self.nonfinite = nonfinite_flag(device)
         self.num_ws = spec.num_ws
         self.resolution = spec.resolution
         self.convs, self.rgbs = synthesis_layers(spec)
@@ -269,6 +296,16 @@ class GeneratorOnDevice:
 
     def _stream(self) -> int:
         return torch.cuda.current_stream(self.device).cuda_stream
+
+    def check_finite(self) -> None:
+        """
+        Synchronising read of the device's range-guard flag: raises NonFiniteFramesError (GANCE_E_NONFINITE) when any
+        frame rendered on this device since the last check held inf/NaN pixels, and clears the flag. `BatchRenderer`
+        reads the flag back with each batch's frames instead, without an extra synchronisation.
+        """
+        if int(self.nonfinite.item()) != 0:
+            self.nonfinite.zero_()
+            raise nonfinite_error(self.mode)
 
     def _mark(self, name: str) -> None:
         """Per-layer timing for tools/profile_layers.py: an event after the step called `name`."""
@@ -604,6 +641,7 @@ class BatchRenderer:
         self.latents_host = [torch.empty((max_batch * generator.num_ws * 512,), dtype=torch.float32).pin_memory()
                              for _ in range(self.depth)]
         self.done = [torch.cuda.Event() for _ in range(self.depth)]
+        self.flags_host = [torch.zeros(1, dtype=torch.int32).pin_memory() for _ in range(self.depth)]
         self.bytes_h2d = 0
         self.bytes_d2h = 0
 
@@ -654,6 +692,7 @@ class BatchRenderer:
         self.copy_stream.wait_event(computed)
         with torch.cuda.stream(self.copy_stream):
             self.frames_host[slot][:n].copy_(out, non_blocking=True)
+            self.flags_host[slot].copy_(gen.nonfinite, non_blocking=True)  # the range-guard flag travels with the frames
             self.done[slot].record(self.copy_stream)
         self.bytes_d2h += n * out[0].numel()
         return n
@@ -669,9 +708,13 @@ class BatchRenderer:
             pending.append((slot, n))
             index += 1
             if len(pending) == self.depth:  # keep depth-1 batches in flight
-                ready_slot, ready_n = pending.pop(0)
-                self.done[ready_slot].synchronize()
-                yield self.frames_host[ready_slot][:ready_n].numpy()
-        for ready_slot, ready_n in pending:
-            self.done[ready_slot].synchronize()
-            yield self.frames_host[ready_slot][:ready_n].numpy()
+                yield self._collect(*pending.pop(0))
+        for ready in pending:
+            yield self._collect(*ready)
+
+    def _collect(self, slot: int, n: int) -> np.ndarray:
+        self.done[slot].synchronize()
+        if int(self.flags_host[slot][0]) != 0:
+            self.generator.nonfinite.zero_()
+            raise nonfinite_error(self.generator.mode)
+        return self.frames_host[slot][:n].numpy()

@@ -52,6 +52,8 @@ extern "C" {
 #define GANCE_E_ALIGN 4       /* a pointer is not aligned as the kernel requires (16 B) */
 #define GANCE_E_NOT_INIT 5    /* gance_init() has not succeeded on this device */
 #define GANCE_E_DRIVER 6      /* CUDA driver entry point (TMA descriptor encode) unavailable */
+#define GANCE_E_NONFINITE 7   /* a rendered frame held inf/NaN pixels: a 16-bit activation overflowed (see
+                                 gance_set_nonfinite_flag); raised by the host binding after a batch, never by a launch */
 
 /* ---- lifecycle ------------------------------------------------------------------------------
  * Replaces dnnlib.tflib.init_tf() + custom_ops.get_plugin() (nvcc build of the TF plugin) called
@@ -62,6 +64,15 @@ int gance_init(int device);
 const char* gance_last_error_string(void);
 /* Number of kernel launches issued through this library since load (bench.py's gpu_launches). */
 unsigned long long gance_launch_count(void);
+/* Range guard of the 16-bit modes (no counterpart in the reference, whose arithmetic is fp32 throughout). Activations
+ * are stored as half / bfloat16 pre-multiplied by the next layer's style; a network with a large style overflows half's
+ * 65504 to inf, which every later layer carries into the RGB sum. Registers a device int (zeroed by the caller) into
+ * which every entry that writes uint8 frames (gance_modconv3x3_torgb, gance_torgb_skip, gance_to_uint8_nhwc) ORs 1 when
+ * a pixel of the fp32 image it converts is inf or NaN - the flag is sticky until the caller clears it. NULL unregisters.
+ * The registration is per device (the calling thread's current device), process-wide, and is read at launch time (a
+ * CUDA graph keeps the pointer it was captured with).
+ * The host reads the flag back with the frames and reports GANCE_E_NONFINITE. */
+int gance_set_nonfinite_flag(int* device_flag);
 
 /* ---- G_mapping + truncation ------------------------------------------------------------------
  * networks_stylegan2.G_mapping + the 'Truncation' block of G_main, as run by Gs.run

@@ -268,3 +268,39 @@ def test_config2_batch32_provided_noise_frames_match_oracle():
     gen.run_matrices_graphed(wplus, out)
     assert torch.equal(out, eager)
     gen.release_buffers()
+
+
+def test_fp16_range_guard_reports_overflow_instead_of_black_pixels():
+    """
+    Activations are stored in IEEE half already multiplied by the next layer's style. A network whose style is large
+    (here: one mod_bias of 3e5 - harmless in exact arithmetic, the demodulation divides it out again) overflows 65504:
+    the frames would come out as plausible black pixels (`fmaxf(NaN, 0) = 0`). The sticky device flag set by the
+    frame-writing epilogues surfaces it as GANCE_E_NONFINITE; bf16 (fp32 range) and fp32 render the same network fine.
+    """
+    from gance_b200 import _lib
+    from gance_b200.synthesis import BatchRenderer
+
+    spec, variables, oracle, z = _case(64, 10, True, 2)
+    large = dict(variables)
+    large["G_synthesis/64x64/Conv0_up/mod_bias"] = variables["G_synthesis/64x64/Conv0_up/mod_bias"] + np.float32(3e5)
+    want = ref.convert_images_to_uint8(ref.ReferenceGenerator(large, torch.float64).run_vector(z))
+    gen = GeneratorOnDevice(spec, large, _device(), mode="fp16")
+    frames = gen.run_vectors(torch.as_tensor(z), noise_mode="const")
+    with pytest.raises(_lib.NonFiniteFramesError, match="GANCE_E_NONFINITE"):
+        gen.check_finite()
+    gen.check_finite()  # the flag was cleared by the report
+    assert lsb_stats(frames.cpu().numpy(), want)[0] < 0.9  # what the caller would otherwise have been handed
+    renderer = BatchRenderer(gen, max_batch=2, noise_mode="const")
+    with pytest.raises(_lib.NonFiniteFramesError):
+        list(renderer.render(iter([z, z])))
+    gen.check_finite()
+    # the same network in the wide-range modes
+    for mode in ("bf16", "fp32"):
+        wide = GeneratorOnDevice(spec, large, _device(), mode=mode)
+        got = wide.run_vectors(torch.as_tensor(z), noise_mode="const").cpu().numpy()
+        wide.check_finite()
+        assert_16bit_tolerance("bf16" if mode == "bf16" else "fp16", got, want)
+    # an ordinary network never trips the guard, through the per-frame boundary call either
+    normal = GeneratorOnDevice(spec, variables, _device(), mode="fp16")
+    normal.run_vectors(torch.as_tensor(z), noise_mode="random")
+    normal.check_finite()
