@@ -66,14 +66,44 @@ def frame_schedule(
     return schedule
 
 
+def _uniform_output_side(networks: MultiNetwork, network_indices: np.ndarray, output_side_length: Optional[int]) -> Optional[int]:
+    """The one side length every frame of the run will have, or None when it cannot be known / is not uniform."""
+    if getattr(networks, "indexed_render_into", None) is None or getattr(networks, "indexed_output_resolution", None) is None:
+        return None
+    sides = {networks.indexed_output_resolution(int(index)) for index in np.unique(network_indices)}
+    if None in sides:
+        return None  # an interface built from the reference's four fields only (no CUDA renderer behind it)
+    if output_side_length is not None:
+        return int(output_side_length)
+    return sides.pop() if len(sides) == 1 else None
+
+
 def create_network_frames(
-    latents: np.ndarray, network_indices: np.ndarray, networks: MultiNetwork, batch_size: int, group_by_network: bool
+    latents: np.ndarray, network_indices: np.ndarray, networks: MultiNetwork, batch_size: int, group_by_network: bool,
+    output_side_length: Optional[int] = None, reuse_frame_buffers: bool = False,
 ) -> Iterator[RGBInt8ImageType]:
     """
     Batched `create_network_frames` (network_visualization.py:598-681): `latents` is (T,512) or
     (T,num_ws,512); yields T frames in frame-index order.
+
+    When every frame of the run has the same size - one network, networks of one resolution, or `output_side_length`
+    given (then frames are scaled on the device, the reference's `scale_square_source_duplicate` step,
+    gance/projection_file_blend.py:184-199) - the run is pipelined through pinned window buffers
+    (gance_b200/track_renderer.py): rendering, device -> host copies and the consumer overlap. Networks of different
+    resolutions without a common output size are rendered batch by batch, synchronously.
     """
     num_frames = len(latents)
+    if num_frames == 0:
+        return
+    side = _uniform_output_side(networks, np.asarray(network_indices[:num_frames]), output_side_length)
+    if side is not None:
+        from gance_b200 import track_renderer
+
+        for image in track_renderer.windowed_frames(networks, latents, np.asarray(network_indices), side, batch_size,
+                                                    output_side_length, group_by_network,
+                                                    reuse_frame_buffers=reuse_frame_buffers):
+            yield RGBInt8ImageType(image)
+        return
     schedule = frame_schedule(network_indices, num_frames, batch_size, group_by_network)
     position = 0
     while position < len(schedule):
@@ -106,12 +136,20 @@ def vector_synthesis(  # pylint: disable=too-many-arguments,unused-argument
     force_optimize_synthesis_order: bool = True,
     unload_networks_when_complete: bool = False,
     batch_size: int = DEFAULT_BATCH_SIZE,
+    output_side_length: Optional[int] = None,
+    reuse_frame_buffers: bool = False,
 ) -> SynthesisOutput:
     """
     network_visualization.py:462-690 without the plots: every latent in `data.combined` goes through
     the network its `network_indices` entry names; `synthesized_images` is a lazy iterator of frames in
     frame-index order at the network's native resolution. The frame count is the number of latents
     (or network indices, whichever is fewer - `zip`, 245-249), truncated to `frames_to_visualize`.
+
+    Additions (keyword-only in spirit, defaults keep the reference's behaviour): `batch_size` frames are rendered per
+    launch sequence; `output_side_length` scales every frame on the device before it leaves for the host (the
+    `scale_square_source_duplicate` step of gance/projection_file_blend.py:184-199, which then passes the frames through
+    untouched); `reuse_frame_buffers` yields views of pinned window buffers instead of copies (valid until two windows
+    later).
     """
     if networks is None:
         if not enable_3d and not enable_2d:
@@ -127,7 +165,8 @@ def vector_synthesis(  # pylint: disable=too-many-arguments,unused-argument
     group = compute_force_synthesis_order(force_optimize_synthesis_order, len(networks.network_indices))
 
     def frames() -> Iterator[RGBInt8ImageType]:
-        yield from create_network_frames(latents[:total], indices[:total], networks, batch_size, group)
+        yield from create_network_frames(latents[:total], indices[:total], networks, batch_size, group,
+                                         output_side_length=output_side_length, reuse_frame_buffers=reuse_frame_buffers)
         if unload_networks_when_complete:
             networks.unload()
 

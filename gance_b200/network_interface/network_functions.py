@@ -66,10 +66,13 @@ class BatchImageFunction(Protocol):  # pylint: disable=too-few-public-methods
 class NetworkInterface(NamedTuple):
     """
     The only view of a network the rest of GANce uses. The first four fields are the reference's,
-    in the reference's order (:66-78). Two additions, with defaults so that code constructing the
+    in the reference's order (:66-78). Additions, with defaults so that code constructing the
     tuple from the four original fields keeps working: `create_images_batch` renders many frames per
-    call, `render_batches` streams batches of host latents to host frames with the copies overlapped
-    (gance_b200.synthesis.BatchRenderer; each yielded array is valid until the next one is drawn).
+    call; `render_batches` streams batches of host latents to host frames with the copies overlapped
+    (gance_b200.synthesis.BatchRenderer; each yielded array is valid until the next one is drawn);
+    `render_into(latents, dest, dest_indices, max_batch, output_side_length)` renders one batch and
+    delivers frame i to `dest[dest_indices[i]]` asynchronously (BatchRenderer.submit_into), returning
+    an arrival handle (`synchronize()`); `output_resolution` is the side of the frames the network produces.
     """
 
     expected_vector_length: int
@@ -78,6 +81,8 @@ class NetworkInterface(NamedTuple):
     create_image_generic: ImageFunction
     create_images_batch: Optional[BatchImageFunction] = None
     render_batches: Optional[Callable[[Iterable[np.ndarray]], Iterator[np.ndarray]]] = None
+    render_into: Optional[Callable[..., object]] = None
+    output_resolution: Optional[int] = None
 
 
 def fix_cuda_path() -> None:
@@ -172,6 +177,13 @@ def _wrap_generator(generator: GeneratorOnDevice, alive: Optional[List[bool]] = 
                                       output_side_length=output_side_length)
         return renderer.render(batches, check_alive=check_alive, vector_noise_mode=VECTOR_NOISE_MODE)
 
+    def render_into(latents, dest: torch.Tensor, dest_indices, max_batch: int = 32,
+                    output_side_length: Optional[int] = None):
+        check_alive()
+        renderer = generator.renderer(max_batch=max_batch, truncation_psi=TRUNCATION_PSI,
+                                      output_side_length=output_side_length)
+        return renderer.submit_into(latents, dest, dest_indices, vector_noise_mode=VECTOR_NOISE_MODE)
+
     return NetworkInterface(
         expected_vector_length=512,
         create_image_vector=create_image_vector,
@@ -179,6 +191,8 @@ def _wrap_generator(generator: GeneratorOnDevice, alive: Optional[List[bool]] = 
         create_image_generic=create_image_generic,
         create_images_batch=create_images_batch,
         render_batches=render_batches,
+        render_into=render_into,
+        output_resolution=getattr(generator, "resolution", None),
     )
 
 
@@ -364,6 +378,31 @@ class MultiNetwork:
         if output_side_length is None:
             return render(batches, max_batch)
         return render(batches, max_batch, output_side_length)
+
+    @_raise_exception_if_unloaded
+    def indexed_render_into(self: "MultiNetwork", index: int, latents, dest: torch.Tensor, dest_indices,
+                            max_batch: int = 32, output_side_length: Optional[int] = None):
+        """
+        Addition: render one batch on network `index` and deliver frame i to `dest[dest_indices[i]]` (pinned host or
+        device memory) asynchronously; returns an arrival handle (`synchronize()` = frames are there and finite), or None when the interface has no
+        CUDA renderer (then the frames were written synchronously through `create_image_generic`). This is what lets frames
+        rendered grouped by network land at their frame index without the reference's per-frame HDF5 spill files
+        (gance/data_into_network_visualization/network_visualization.py:631-674).
+        """
+        self._load_network_at_index(index)
+        interface = self._currently_loaded_network.network_interface
+        if interface.render_into is None:
+            generic = interface.create_image_generic
+            for item, position in zip(latents, dest_indices):
+                dest[int(position)] = torch.as_tensor(generic(np.asarray(item)))
+            return None
+        return interface.render_into(latents, dest, dest_indices, max_batch, output_side_length)
+
+    @_raise_exception_if_unloaded
+    def indexed_output_resolution(self: "MultiNetwork", index: int) -> Optional[int]:
+        """Addition: side length of the frames network `index` produces (None for an interface that does not say)."""
+        self._load_network_at_index(index)
+        return self._currently_loaded_network.network_interface.output_resolution
 
     def load(self: "MultiNetwork") -> None:
         network_path = self._network_paths[self._currently_loaded_network_index]

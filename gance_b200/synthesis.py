@@ -598,6 +598,28 @@ class GeneratorOnDevice:
         return self.synthesis(wplus, noise_mode="const", **kwargs)
 
 
+class Arrival:
+    """
+    What `BatchRenderer.submit_into` returns: `synchronize()` blocks until the batch's frames are in the destination and
+    raises NonFiniteFramesError (GANCE_E_NONFINITE) if the range-guard flag that travelled with them is set.
+    """
+
+    __slots__ = ("event", "flag", "generator")
+
+    def __init__(self, event: torch.cuda.Event, flag: torch.Tensor, generator: "GeneratorOnDevice") -> None:
+        self.event, self.flag, self.generator = event, flag, generator
+
+    def synchronize(self) -> None:
+        self.event.synchronize()
+        if int(self.flag[0]) != 0:
+            self.flag.zero_()
+            self.generator.nonfinite.zero_()
+            raise nonfinite_error(self.generator.mode)
+
+    def query(self) -> bool:
+        return self.event.query()
+
+
 class BatchRenderer:
     """
     Host latents in, host frames out, with the three legs overlapped: while batch i is computed,
@@ -636,27 +658,32 @@ class BatchRenderer:
             self.resizer = FrameResizer(dev)
             self.scaled_dev = [torch.empty((max_batch, self.output_side, self.output_side, 3), dtype=torch.uint8, device=dev)
                                for _ in range(self.depth)]
-        side = self.output_side
-        self.frames_host = [torch.empty((max_batch, side, side, 3), dtype=torch.uint8).pin_memory() for _ in range(self.depth)]
+        self.frames_host: List[torch.Tensor] = []  # pinned result ring of `render`, allocated on first use
         self.latents_host = [torch.empty((max_batch * generator.num_ws * 512,), dtype=torch.float32).pin_memory()
                              for _ in range(self.depth)]
         self.done = [torch.cuda.Event() for _ in range(self.depth)]
+        self.staged = [torch.cuda.Event() for _ in range(self.depth)]  # H2D of the slot's staged latents has run
+        self._next_slot = 0
         self.flags_host = [torch.zeros(1, dtype=torch.int32).pin_memory() for _ in range(self.depth)]
         self.bytes_h2d = 0
         self.bytes_d2h = 0
 
-    def _submit(self, slot: int, latents: np.ndarray, vector_noise_mode: str = "random") -> int:
+    def _compute(self, slot: int, latents, vector_noise_mode: str = "random"):
         """
-        One batch: (512,) / (N,512) are vectors, (N,rows,512) are matrices - the kind of a batch is its number of
-        dimensions, never its length (a batch of exactly num_ws vectors is num_ws frames). A single (num_ws,512) matrix
-        must arrive as (1,num_ws,512).
+        H2D of one batch's latents, the generator pass and the optional resize, all on the current stream, into this
+        slot's device buffers. Returns (n, device frames [n,S,S,3]).
+
+        (512,) / (N,512) are vectors, (N,rows,512) are matrices - the kind of a batch is its number of dimensions, never
+        its length (a batch of exactly num_ws vectors is num_ws frames). A single (num_ws,512) matrix must arrive as
+        (1,num_ws,512). `latents` may be a numpy array (staged through this slot's pinned buffer) or a CUDA tensor.
         """
         gen = self.generator
-        array = np.asarray(latents, dtype=np.float32)
+        on_gpu = isinstance(latents, torch.Tensor) and latents.is_cuda
+        array = latents.to(torch.float32) if on_gpu else np.asarray(latents, dtype=np.float32)
         if array.ndim == 1:
             array = array[None]
         if array.ndim not in (2, 3) or array.shape[-1] != 512:
-            raise ValueError(f"a batch is (N,512) vectors or (N,rows,512) matrices, got shape {array.shape}")
+            raise ValueError(f"a batch is (N,512) vectors or (N,rows,512) matrices, got shape {tuple(array.shape)}")
         is_vectors = array.ndim == 2
         n = array.shape[0]
         if n > self.max_batch:
@@ -667,10 +694,15 @@ class BatchRenderer:
             array = array[:, : gen.num_ws]
         stream = torch.cuda.current_stream(gen.device)
         stream.wait_event(self.done[slot])  # the frames of the batch that last used this slot have left the device
-        staged = self.latents_host[slot][: array.size].view(array.shape)
-        staged.copy_(torch.from_numpy(np.ascontiguousarray(array)))
-        on_device = staged.to(gen.device, non_blocking=True)
-        self.bytes_h2d += array.size * 4
+        if on_gpu:
+            on_device = array.contiguous()
+        else:
+            self.staged[slot].synchronize()  # host side: the H2D that last read this slot's staging buffer has run
+            staged = self.latents_host[slot][: array.size].view(array.shape)
+            staged.copy_(torch.from_numpy(np.ascontiguousarray(array)))
+            on_device = staged.to(gen.device, non_blocking=True)
+            self.staged[slot].record(stream)
+            self.bytes_h2d += array.size * 4
         out = self.frames_dev[slot][:n]
         # full batches and multiples of 8 replay a captured graph; the odd-sized groups a model-switching window leaves
         # over run eagerly (same C-ABI calls), so a run never holds more than a handful of graphs per network
@@ -687,8 +719,18 @@ class BatchRenderer:
             gen.synthesis(on_device, noise_mode=self.noise_mode or "const", out=out)
         if self.resizer is not None:
             out = self.resizer.resize(out, self.output_side, self.output_side, out=self.scaled_dev[slot][:n])
+        return n, out
+
+    def _submit(self, slot: int, latents, vector_noise_mode: str = "random") -> int:
+        """One batch through `_compute`, then its frames to this slot's pinned host buffer on the copy stream."""
+        gen = self.generator
+        if not self.frames_host:
+            side = self.output_side
+            self.frames_host = [torch.empty((self.max_batch, side, side, 3), dtype=torch.uint8).pin_memory()
+                                for _ in range(self.depth)]
+        n, out = self._compute(slot, latents, vector_noise_mode)
         computed = torch.cuda.Event()
-        computed.record(stream)
+        computed.record(torch.cuda.current_stream(gen.device))
         self.copy_stream.wait_event(computed)
         with torch.cuda.stream(self.copy_stream):
             self.frames_host[slot][:n].copy_(out, non_blocking=True)
@@ -696,6 +738,45 @@ class BatchRenderer:
             self.done[slot].record(self.copy_stream)
         self.bytes_d2h += n * out[0].numel()
         return n
+
+    def submit_into(self, latents, dest: torch.Tensor, dest_indices, vector_noise_mode: str = "random") -> Arrival:
+        """
+        Render one batch and deliver frame i of it to `dest[dest_indices[i]]`, without an intermediate host buffer: `dest`
+        is a uint8 [T,S,S,3] tensor - pinned / CUDA-registered host memory (a window buffer, the encoder rank's shared
+        frame sink) or device memory (the send buffer of a gather) - and every run of consecutive indices becomes one
+        asynchronous copy on the copy stream. This is how frames rendered out of frame order (grouped by network, as the
+        reference sorts them, network_visualization.py:659-674) land at their frame index: an indexed buffer instead of
+        gzip-HDF5 spill files. Returns an `Arrival` (synchronize() = the frames have arrived and are finite); slots are
+        used round-robin, so at most `depth` batches of this renderer are in flight.
+        """
+        gen = self.generator
+        indices = np.asarray(dest_indices, dtype=np.int64).reshape(-1)
+        slot = self._next_slot
+        self._next_slot = (slot + 1) % self.depth
+        n, out = self._compute(slot, latents, vector_noise_mode)
+        if len(indices) != n:
+            raise ValueError(f"{n} latents but {len(indices)} destination indices")
+        if tuple(dest.shape[1:]) != tuple(out.shape[1:]) or dest.dtype != torch.uint8:
+            raise ValueError(f"dest must be uint8 [T,{out.shape[1]},{out.shape[2]},3], got {tuple(dest.shape)} {dest.dtype}")
+        if n and (int(indices.min()) < 0 or int(indices.max()) >= dest.shape[0]):
+            raise IndexError("destination index outside dest")
+        computed = torch.cuda.Event()
+        computed.record(torch.cuda.current_stream(gen.device))
+        self.copy_stream.wait_event(computed)
+        arrived = torch.cuda.Event()
+        with torch.cuda.stream(self.copy_stream):
+            begin = 0
+            for position in range(1, n + 1):  # one copy per run of consecutive destination indices
+                if position == n or indices[position] != indices[position - 1] + 1:
+                    first = int(indices[begin])
+                    dest[first: first + position - begin].copy_(out[begin:position], non_blocking=True)
+                    begin = position
+            self.flags_host[slot].copy_(gen.nonfinite, non_blocking=True)
+            self.done[slot].record(self.copy_stream)
+            arrived.record(self.copy_stream)
+        if not dest.is_cuda:
+            self.bytes_d2h += n * out[0].numel()
+        return Arrival(arrived, self.flags_host[slot], gen)
 
     def render(self, batches: Iterable[np.ndarray], check_alive=None, vector_noise_mode: str = "random") -> Iterator[np.ndarray]:
         pending: List[tuple] = []

@@ -117,3 +117,113 @@ def test_sharded_schedule_equals_the_unsharded_one():
             assert np.all(indices[start:stop][frames] == network_index) and len(frames) <= 32
             seen.extend((frames + start).tolist())
     assert sorted(seen) == list(range(len(indices)))
+
+
+# ---- the indexed frame buffer: batches grouped by network land at their frame index ----------------------------------
+from gance_b200 import track_renderer  # noqa: E402
+from gance_b200.frame_sharding import SharedFrameSink, open_shared_frame_sink  # noqa: E402
+
+
+class _FakeNetworks:
+    """Duck-typed MultiNetwork without a GPU: frame = (network index, first latent element) in every pixel."""
+
+    def __init__(self, side: int = 2) -> None:
+        self.side = side
+        self.calls = []
+
+    def indexed_render_into(self, index, latents, dest, dest_indices, max_batch=32, output_side_length=None):
+        latents = np.asarray(latents)
+        assert len(latents) == len(dest_indices) <= max_batch
+        self.calls.append((int(index), len(latents)))
+        for item, position in zip(latents, dest_indices):
+            dest[int(position)] = torch.tensor([index, int(item.reshape(-1)[0]) % 251, 7], dtype=torch.uint8)
+        return None
+
+
+@pytest.mark.parametrize("group", [True, False])
+def test_network_batches_cover_every_frame_once(group):
+    rng = np.random.RandomState(1)
+    indices = rng.randint(0, 3, size=200)
+    frames = np.arange(37, 170)
+    batches = track_renderer.network_batches(indices, frames, 32, group)
+    seen = np.concatenate([members for _, members in batches])
+    assert sorted(seen.tolist()) == frames.tolist()
+    for network, members in batches:
+        assert 1 <= len(members) <= 32 and np.all(indices[members] == network) and np.all(np.diff(members) > 0)
+    if group:  # a network's frames fill whole batches: at most one ragged batch per network
+        assert sum(1 for _, members in batches if len(members) < 32) <= 3
+        assert [network for network, _ in batches] == sorted(network for network, _ in batches)
+    assert track_renderer.network_batches(indices, np.arange(0), 32, group) == []
+    with pytest.raises(ValueError):
+        track_renderer.network_batches(indices, frames, 0, group)
+
+
+def test_render_frames_into_puts_each_frame_at_its_index():
+    rng = np.random.RandomState(2)
+    total = 150
+    indices = rng.randint(0, 3, size=total)
+    latents = np.arange(total, dtype=np.float64)[:, None] * np.ones((1, 512))
+    networks = _FakeNetworks()
+    dest = torch.zeros((total, 2, 2, 3), dtype=torch.uint8)
+    batches = track_renderer.render_frames_into(networks, latents, indices, dest, batch_size=32)
+    assert batches == len(networks.calls) and sum(count for _, count in networks.calls) == total
+    for frame in range(total):
+        assert dest[frame, 0, 0].tolist() == [indices[frame], frame % 251, 7]
+    # a rank's contiguous share, written at an offset (the rank's slice of the shared sink)
+    start, stop = frame_range(1, 4, total)
+    share = torch.zeros((stop - start, 2, 2, 3), dtype=torch.uint8)
+    track_renderer.render_frames_into(networks, latents, indices, share, frames=np.arange(start, stop), dest_offset=-start)
+    assert torch.equal(share, dest[start:stop])
+
+
+def _sink_worker(rank: int, world: int, port: int, total_frames: int, name: str, directory: str, results) -> None:
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        sink = open_shared_frame_sink(name, total_frames, 2, register=False, directory=directory)
+        start, stop = sink.frame_range
+        indices = np.arange(total_frames) % 2
+        latents = np.arange(total_frames, dtype=np.float64)[:, None] * np.ones((1, 512))
+        # every rank renders ITS frames, grouped by network, straight to their global positions
+        track_renderer.render_frames_into(_FakeNetworks(), latents, indices, sink.frames, frames=np.arange(start, stop), batch_size=3)
+        dist.barrier()
+        if rank == 0:  # the encoder rank sees every frame, in order, in its own mapping
+            ok = all(sink.frames[f, 1, 1].tolist() == [f % 2, f % 251, 7] for f in range(total_frames))
+            results.put(("sink", ok, tuple(sink.frames.shape)))
+        dist.barrier()
+        path = sink.path
+        sink.close()
+        dist.barrier()
+        results.put(("closed", not os.path.exists(path), ()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,total_frames", [(2, 11), (3, 4)])
+def test_shared_frame_sink_collects_every_ranks_frames_in_order_gloo(tmp_path, world, total_frames):
+    ctx = mp.get_context("spawn")
+    results = ctx.Queue()
+    port = _free_port()
+    name = f"gance_b200_test_sink_{os.getpid()}_{world}"
+    procs = [ctx.Process(target=_sink_worker, args=(rank, world, port, total_frames, name, str(tmp_path), results))
+             for rank in range(world)]
+    for proc in procs:
+        proc.start()
+    got = [results.get(timeout=120) for _ in range(world + 1)]
+    for proc in procs:
+        proc.join(timeout=60)
+        assert proc.exitcode == 0
+    assert all(flag for _, flag, _ in got), got
+    assert [shape for kind, _, shape in got if kind == "sink"] == [(total_frames, 2, 2, 3)]
+
+
+def test_shared_frame_sink_single_process(tmp_path):
+    with open_shared_frame_sink("solo", 5, 3, register=False, directory=str(tmp_path)) as sink:
+        assert sink.frame_range == (0, 5) and tuple(sink.frames.shape) == (5, 3, 3, 3)
+        sink.local_frames()[2] = 9
+        other = SharedFrameSink("solo", 5, 3, (0, 0), create=False, register=False, directory=str(tmp_path))
+        assert int(other.frames[2].sum()) == 9 * 27  # a second mapping of the same file sees the write
+        other.close()
+        with pytest.raises(ValueError):
+            SharedFrameSink("solo", 6, 3, (0, 0), create=False, register=False, directory=str(tmp_path))
+    assert not (tmp_path / "solo").exists()
