@@ -12,9 +12,18 @@ ranks' uint8 frames to rank 0 (the encoder rank). Weak scaling: every rank rende
 contiguous frame range of the track, weights replicated.
 
 Prints ONE JSON line (rank 0): value = frames/s over all ranks with inputs resident in HBM; e2e =
-the same through the NetworkInterface boundary with host latents in / host frames out; roofline =
-the modulated-convolution kernel's achieved TFLOP/s (CUDA events around its launches) against the
-measured bf16 peak; cpu_baseline = the CPU restatement timed on this box's cores.
+the same through the MultiNetwork boundary with HOST latents in and the frames of every rank arriving, in global frame
+order, in ONE host buffer the encoder rank reads (frame_sharding.SharedFrameSink: each rank DMA-writes its own range
+over its own PCIe link); roofline = the modulated-convolution kernels' achieved TFLOP/s (CUDA events around their
+launches) against the measured bf16 peak; cpu_baseline = the CPU restatement timed on this box's cores.
+
+Extra keys of the default line (the other BASELINE configs, each measured by the same process):
+  matrix_path  config 3's device path: CUDA-graphed `run_matrices` at batch 32 from projection-blend w+ latents
+  album        config 4: the whole 180 s / 10 800-frame job - WAV file -> latents -> frames in the encoder's host buffer
+  projection   config 3 as a job: HDF5 projection file + WAV -> w+ blend -> matrix path -> encoder's host buffer
+  switching    config 5: three resident networks (512^2, 1024^2, 1024^2) switched per frame by the RMS index, frames
+               resized to 2160^2 on the device before the hand-over
+`--config album|projection|switching|matrices` makes that measurement the headline `value` instead.
 """
 
 import argparse
@@ -60,6 +69,13 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=10.0,
                     help="CPU work the cpu_baseline leg is bounded to (frames are rendered until this much time has passed)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--config", default="vectors", choices=["vectors", "matrices", "album", "projection", "switching"],
+                    help="which BASELINE config provides the headline value (default: configs[1], the vector path)")
+    ap.add_argument("--no-extras", action="store_true", help="skip the matrix_path / album / projection / switching legs")
+    ap.add_argument("--album-seconds", type=float, default=180.0)
+    ap.add_argument("--projection-seconds", type=float, default=60.0)
+    ap.add_argument("--switching-seconds", type=float, default=20.0)
+    ap.add_argument("--output-side", type=int, default=2160, help="output side length of the switching job")
     return ap.parse_args()
 
 
@@ -142,6 +158,16 @@ def track_latents(seconds: float, device):
         alpha=0.25, fft_roll_enabled=True, fft_amplitude_range=(-5, 5), time_series_audio_vectors=scaled,
         vector_length=512, network_indices=[0])
     return result.latents
+
+
+def synthetic_track_audio(seconds: float, device):
+    """The synthetic chirp scaled for 60 fps video: float32 (T*512,) on the host (the input of the blend functions)."""
+    from gance_b200 import audio_device, synthetic
+    from gance_b200.vector_sources import music
+
+    as_float = audio_device.pcm_to_float(synthetic.chirp_wav(seconds), device).cpu().numpy()
+    return music.read_wavs_scale_for_video([music.WavFileProperties(44100, as_float, "chirp")], 512,
+                                           frames_per_second=60.0).wav_data
 
 
 def audio_half_report(seconds: float, device):
@@ -242,6 +268,31 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def layer_bytes(generator, index: int, batch: int, random_noise: bool) -> float:
+    """
+    Bytes the launch of conv layer `index` really reads and writes in the 16-bit modes (weights and per-sample
+    coefficients are negligible): its input and output activations (2 B/element; the last Conv1 writes NO activation,
+    layers with Cout > 256 write it twice - plain for their separate ToRGB kernel and pre-scaled for the next layer),
+    the per-sample noise plane (4 B/pixel), and for the layers with a fused ToRGB the fp32 skip image read at the
+    previous resolution and written at this one (16 B/pixel), or the uint8 frame on the last layer.
+    """
+    conv = generator.convs[index]
+    element = 4 if generator.mode == "fp32" else 2
+    side_in, side = conv.in_resolution, conv.out_resolution
+    last = index == len(generator.convs) - 1
+    moved = float(side_in * side_in * conv.in_channels * element)
+    fused_rgb = (not conv.up) and generator.mode != "fp32" and conv.out_channels <= 256 and side > 4
+    writes = 0 if (last and fused_rgb) else (2 if (not conv.up and not fused_rgb and generator.mode != "fp32" and not last
+                                                      and conv.in_channels % 64 == 0 and conv.in_channels >= 128) else 1)
+    moved += float(side * side * conv.out_channels * element) * writes
+    if generator.conv_strength[index] != 0.0:
+        moved += float(side * side * 4) * (1.0 if random_noise else 1.0 / batch)
+    if fused_rgb:
+        moved += float((side // 2) ** 2 * 16)  # skip image of the previous resolution (fp32 x 4)
+        moved += float(side * side * 3) if last else float(side * side * 16)
+    return moved * batch
+
+
 def main():
     args = parse_args()
     if args.impl == "reference":
@@ -251,11 +302,16 @@ def main():
     import torch
     import torch.distributed as dist
 
-    from gance_b200 import _lib
-    from gance_b200.frame_sharding import frame_range, gather_frames
+    from gance_b200 import _lib, synthetic
+    from gance_b200.data_into_network_visualization import visualization_inputs
+    from gance_b200.frame_sharding import frame_range, gather_frames, open_shared_frame_sink
     from gance_b200.network_interface import network_functions
     from gance_b200.networks import container
     from gance_b200.synthesis import GeneratorOnDevice  # noqa: F401  (fails loudly without the CUDA library)
+    from gance_b200.vector_sources.vector_types import MatricesLabel
+
+    sys.path.insert(0, str(ROOT / "tools"))
+    import track_jobs
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -268,6 +324,44 @@ def main():
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # NCCL's version banner / warnings go to stderr: stdout is ONE JSON line
         dist.init_process_group("nccl", device_id=device)
     batch, res = args.batch, args.resolution
+    peaks, peak_source = measured_peaks()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(value: float) -> float:
+        if world == 1:
+            return value
+        t = torch.tensor([value], dtype=torch.float64, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- whole-track jobs as the headline (configs 3, 4, 5) ----------------------------------------------------------
+    if args.config in ("album", "projection", "switching"):
+        seconds = {"album": args.album_seconds, "projection": args.projection_seconds, "switching": args.switching_seconds}[args.config]
+        with ClockSampler(local_rank) as clocks:
+            report = track_jobs.run_track_job(args.config, seconds, device, mode=args.mode, batch=batch,
+                                              output_side=args.output_side if args.config == "switching" else None)
+        if rank == 0:
+            steps = -(-report["frames"] // (batch * world))
+            line = {
+                "metric": METRIC, "value": report["frames_per_s"], "unit": UNIT, "n_gpus": world, "steps": steps,
+                "warmup": 1, "ms_per_step": report["wall_s"] / steps * 1e3, "higher_is_better": True, "scaling": "strong",
+                "vs_baseline": None, "dtype": args.mode, "data": "synthetic",
+                "config": {"workload": report["workload"], "global_batch": batch * world,
+                           "l2": "per-batch working set (> 10 GB of activations) far exceeds the 126 MB L2; no flush needed",
+                           "timing": "wall clock from the input files on disk to every frame in the encoder rank's host buffer, max over ranks"},
+                "e2e": {"value": report["frames_per_s"], "unit": UNIT, "h2d_bytes_per_step": 0,
+                        "d2h_bytes_per_step": batch * report["frame_bytes"],
+                        "api": "noise_blend / projection_file_blend render-into-sink jobs (latents computed on the device from the WAV file)"},
+                "gpu_launches": int(_lib.launch_count()), "job": report, "clocks": clocks.summary(),
+            }
+            print(json.dumps(line), flush=True)
+        if world > 1:
+            dist.destroy_process_group()
+        return
 
     # ---- set-up (untimed): network file -> resident weights; WAV -> latents on the device ----------
     network_path = Path(f"/tmp/gance_b200_bench_{res}_{rank}.pkl")
@@ -283,6 +377,15 @@ def main():
     local_frames = latents.shape[0]
     if local_frames < batch:
         raise RuntimeError(f"track too short: rank {rank} has {local_frames} frames, needs {batch}")
+    # the matrix path's input: projection-blend w+ [T,18,512] from a synthetic projection (alpha .25, depth 12, roll)
+    wav_float = synthetic_track_audio(args.track_seconds, device)
+    projection = MatricesLabel(synthetic.projection_latents(total_frames // 2), 512, "synthetic")
+    wplus_all = visualization_inputs.alpha_blend_projection_file_device(
+        final_latents_matrices_label=projection, alpha=0.25, fft_roll_enabled=True, fft_amplitude_range=(-5, 5),
+        blend_depth=12, time_series_audio_vectors=wav_float[: (total_frames // 2) * 2 * 512], vector_length=512,
+        network_indices=[0]).latents
+    wplus = wplus_all[start_frame: start_frame + local_frames, : generator.num_ws].contiguous()
+    matrices = args.config == "matrices"
     # two output slots: with N > 1 the gather of step i runs on a communication stream while step i+1 is computed
     slots = 2 if world > 1 else 1
     frames_slots = [torch.empty((batch, res, res, 3), dtype=torch.uint8, device=device) for _ in range(slots)]
@@ -292,13 +395,19 @@ def main():
     comm_stream = torch.cuda.Stream(device=device) if world > 1 else None
     slot_free = [None] * slots
 
-    def step(i: int):
-        offset = (i * batch) % (local_frames - batch + 1)
+    def render(i: int, out, use_matrices: bool):
+        offset = (i * batch) % (min(local_frames, wplus.shape[0]) - batch + 1)
+        if use_matrices:
+            generator.run_matrices_graphed(wplus[offset: offset + batch], out)
+        else:
+            generator.run_vectors_graphed(latents[offset: offset + batch], out, truncation_psi=1.2, noise_mode="random")
+
+    def step(i: int, use_matrices: bool = matrices):
         slot = i % slots
         main = torch.cuda.current_stream(device)
         if slot_free[slot] is not None:
             main.wait_event(slot_free[slot])  # the gather that last read this slot has finished
-        generator.run_vectors_graphed(latents[offset: offset + batch], frames_slots[slot], truncation_psi=1.2, noise_mode="random")
+        render(i, frames_slots[slot], use_matrices)
         if world > 1:
             computed = torch.cuda.Event()
             computed.record(main)
@@ -310,43 +419,48 @@ def main():
             return result
         return frames_slots[slot]
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    for i in range(args.warmup):
-        step(i)
-    barrier()
-    launches_before = _lib.launch_count()
-    start_event, stop_event = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local_rank) as clocks:
+    def timed_steps(use_matrices: bool, sampler=None):
+        for i in range(args.warmup):
+            step(i, use_matrices)
+        barrier()
+        before = _lib.launch_count()
+        start_event, stop_event = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
         start_event.record()
         for i in range(args.steps):
-            step(args.warmup + i)
+            step(args.warmup + i, use_matrices)
         if comm_stream is not None:
             torch.cuda.current_stream(device).wait_stream(comm_stream)  # the last gathers are inside the timed region
         stop_event.record()
         barrier()
-    elapsed_ms = start_event.elapsed_time(stop_event)
-    # a step is one CUDA-graph replay: our kernels inside it were counted when the graph was captured
-    launches = (_lib.launch_count() - launches_before) + generator.launches_per_replay * args.steps
-    if world > 1:
-        t = torch.tensor([elapsed_ms], device=device)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        elapsed_ms = float(t.item())
-    value = world * batch * args.steps / (elapsed_ms * 1e-3)
+        elapsed = max_over_ranks(start_event.elapsed_time(stop_event))
+        # a step is one CUDA-graph replay: our kernels inside it were counted when the graph was captured
+        launched = (_lib.launch_count() - before) + generator.launches_per_replay * args.steps
+        return elapsed, launched
 
-    # ---- roofline of the dominant kernel: CUDA events around every conv launch of a step ---------
-    peaks, peak_source = measured_peaks()
+    with ClockSampler(local_rank) as clocks:
+        elapsed_ms, launches = timed_steps(matrices)
+    value = world * batch * args.steps / (elapsed_ms * 1e-3)
+    matrix_path = None
+    if not matrices and not args.no_extras:
+        matrix_ms, _ = timed_steps(True)
+        matrix_path = {"value": world * batch * args.steps / (matrix_ms * 1e-3), "unit": UNIT, "ms_per_step": matrix_ms / args.steps,
+                       "what": "BASELINE configs[2] on the device: CUDA-graphed run_matrices (G_synthesis only, constant noise "
+                               f"buffers) at {res}^2 batch {batch} from projection-blend w+ latents [T,18,512] resident in HBM"
+                               + (", NCCL gather to rank 0 each step" if world > 1 else "")}
+
+    # ---- roofline of the dominant kernels: CUDA events around every conv launch of a step ---------
+    random_noise = not matrices
     conv_ms, other_ms = [], []
     per_layer = {}
     for i in range(3):
         generator.profile_events = []
         begin = torch.cuda.Event(enable_timing=True)
         begin.record()
-        generator.run_vectors(latents[:batch], truncation_psi=1.2, noise_mode="random", out=frames_out)
+        if matrices:
+            generator.synthesis(wplus[:batch], noise_mode="const", out=frames_out)
+        else:
+            generator.run_vectors(latents[:batch], truncation_psi=1.2, noise_mode="random", out=frames_out)
         torch.cuda.synchronize()
         prev, conv, other = begin, 0.0, 0.0
         for name, event in generator.profile_events:
@@ -360,12 +474,13 @@ def main():
         conv_ms.append(conv)
         other_ms.append(other)
     generator.profile_events = None
-    # per-layer view of the same events: each modulated convolution against the roofline that bounds IT (algorithmic
-    # flops = 2 * 9 * Cin * Cout per output pixel (per INPUT pixel for up-convolutions); algorithmic bytes = input +
-    # output activations at 2 B per element), largest first
+    # per-layer view of the same events: each modulated convolution against the roofline that bounds IT. Algorithmic
+    # flops = 2 * 9 * Cin * Cout per output pixel (per INPUT pixel for up-convolutions) + the fused ToRGB's 2 * 3 * Cout;
+    # bytes = what the launch really reads and writes (layer_bytes). Peaks: burst figures - each launch is timed alone
+    # inside three eager 8 ms passes, not inside a seconds-long step.
+    burst_tflops, sustained_tflops = peaks["bf16_tflops"], peaks["bf16_tflops_sustained"]
     layers = []
-    bytes_per_element = 4 if args.mode == "fp32" else 2
-    for conv in generator.convs:
+    for index, conv in enumerate(generator.convs):
         side = conv.out_resolution
         name = f"{side}/conv0_up" if conv.up else (f"{side}/conv1" if side > 4 else "4/conv")
         if name not in per_layer:
@@ -373,61 +488,87 @@ def main():
         ms = float(np.median(per_layer[name]))
         pixels = conv.in_resolution ** 2 if conv.up else side ** 2
         flops = 2.0 * 9 * conv.in_channels * conv.out_channels * pixels * batch
-        moved = float(conv.in_resolution ** 2 * conv.in_channels + side ** 2 * conv.out_channels) * bytes_per_element * batch
-        t_tensor, t_hbm = flops / (peaks["bf16_tflops_sustained"] * 1e12), moved / (peaks["hbm_gbs"] * 1e9)
+        moved = layer_bytes(generator, index, batch, random_noise)
+        t_tensor, t_hbm = flops / (burst_tflops * 1e12), moved / (peaks["hbm_gbs"] * 1e9)
         layers.append({"layer": name, "ms": ms, "tflops": flops / (ms * 1e-3) / 1e12, "hbm_gbs": moved / (ms * 1e-3) / 1e9,
-                       "bound": "tensor" if t_tensor >= t_hbm else "hbm", "frac_of_bound": max(t_tensor, t_hbm) / (ms * 1e-3)})
+                       "bound": "tensor" if t_tensor >= t_hbm else "hbm", "frac": max(t_tensor, t_hbm) / (ms * 1e-3)})
     layers.sort(key=lambda row: -row["ms"])
     conv_step_ms = float(np.median(conv_ms))
     flop_per_step = FLOP_PER_FRAME.get(res, 0.0) * batch
     achieved_tflops = flop_per_step / (conv_step_ms * 1e-3) / 1e12 if conv_step_ms > 0 else 0.0
-    tensor_peak = peaks["bf16_tflops_sustained"]
     traffic, traffic_note = None, None
-    if res == 1024 and batch == 32 and args.mode == "fp16":  # the configuration the committed ncu pass was taken on
-        try:
-            captured = json.loads((ROOT / "profiles" / "r01_conv_traffic.json").read_text())
-            traffic = float(captured["conv_dram_bytes_per_step"])
-            traffic_note = ("dram__bytes_read.sum + dram__bytes_write.sum over the conv launches of one step, "
-                            "profiles/r01_conv_traffic.json (ncu capture, not measured in this run)")
-        except Exception:  # pylint: disable=broad-except
-            traffic = None
+    if res == 1024 and batch == 32 and args.mode == "fp16" and not matrices:  # the configuration the committed ncu pass was taken on
+        for name in ("r02_conv_traffic.json", "r01_conv_traffic.json"):
+            try:
+                captured = json.loads((ROOT / "profiles" / name).read_text())
+                traffic = float(captured["conv_dram_bytes_per_step"])
+                traffic_note = ("dram__bytes_read.sum + dram__bytes_write.sum over the conv launches of one step, "
+                                f"profiles/{name} (ncu capture, not measured in this run)")
+                break
+            except Exception:  # pylint: disable=broad-except
+                traffic = None
     roofline = {
         "bound": "tensor", "kernel": "modconv3x3_tc_kernel + modconv3x3_halo_kernel + upconv_fused_kernel (every modulated-convolution launch of a step: tcgen05 implicit GEMMs with fused demod/noise/bias/lrelu/FIR/ToRGB/skip/uint8 epilogues)",
-        "achieved": achieved_tflops, "peak": tensor_peak, "unit": "TFLOP/s", "frac": achieved_tflops / tensor_peak,
-        "peak_source": f"bf16_tflops_sustained, {peak_source}", "traffic": traffic, "traffic_unit": "bytes per step (same launches as `achieved`)",
-        "traffic_source": traffic_note, "layers": layers[:8], "algorithmic_hbm_bytes_per_step": HBM_BYTES_PER_FRAME.get(res, 0.0) * batch,
+        "achieved": achieved_tflops, "peak": burst_tflops, "unit": "TFLOP/s", "frac": achieved_tflops / burst_tflops,
+        "peak_source": f"bf16_tflops (burst: the conv launches are timed with CUDA events inside three eager 8 ms passes), {peak_source}",
+        "frac_of_sustained_peak": achieved_tflops / sustained_tflops, "sustained_peak": sustained_tflops,
+        "traffic": traffic, "traffic_unit": "bytes per step (same launches as `achieved`)",
+        "traffic_source": traffic_note, "layers": layers[:10], "algorithmic_hbm_bytes_per_step": HBM_BYTES_PER_FRAME.get(res, 0.0) * batch,
         "conv_ms_per_step": conv_step_ms, "other_ms_per_step": float(np.median(other_ms)),
+        "whole_step_tflops": flop_per_step / (elapsed_ms / args.steps * 1e-3) / 1e12,
+        "whole_step_frac_of_burst": flop_per_step / (elapsed_ms / args.steps * 1e-3) / 1e12 / burst_tflops,
         "hbm_algorithmic_gbs_whole_step": HBM_BYTES_PER_FRAME.get(res, 0.0) * batch / (elapsed_ms / args.steps * 1e-3) / 1e9,
         "hbm_peak_gbs": peaks["hbm_gbs"],
     }
 
-    # ---- e2e through the boundary: host latents -> MultiNetwork.indexed_render_batches -> host frames
+    # ---- e2e through the boundary: host latents -> MultiNetwork.indexed_render_into -> ONE host frame buffer ---------
+    # Every rank renders its own contiguous frame range; the frames of all ranks arrive, in global frame order, in a
+    # single host buffer that the encoder rank (rank 0) reads: a /dev/shm mapping each rank has CUDA-registered its own
+    # slice of, so the device -> host copies are DMA over that rank's own PCIe link.
     e2e = None
     if not args.no_e2e:
-        host_latents = latents.cpu().numpy()
-        renderer_steps = args.steps
+        host_source = (wplus if matrices else latents).cpu().numpy()
+        e2e_steps = args.steps
+        sink = open_shared_frame_sink(f"gance_b200_bench_{os.getppid()}_{world}", world * e2e_steps * batch, res)
+        try:
+            first = rank * e2e_steps * batch  # this rank's contiguous range of the buffer
 
-        def host_batches(count, first):
-            for i in range(count):
-                offset = ((first + i) * batch) % (local_frames - batch + 1)
-                yield host_latents[offset: offset + batch]
+            def run_e2e(count: int):
+                arrivals = []
+                for i in range(count):
+                    offset = (i * batch) % (host_source.shape[0] - batch + 1)
+                    arrivals.append(networks.indexed_render_into(0, host_source[offset: offset + batch], sink.frames,
+                                                                 np.arange(first + i * batch, first + (i + 1) * batch),
+                                                                 max_batch=batch))
+                    if len(arrivals) > 4:
+                        arrivals.pop(0).synchronize()
+                for arrival in arrivals:
+                    arrival.synchronize()
 
-        checksum = 0
-        for frames in networks.indexed_render_batches(0, host_batches(args.warmup, 0), max_batch=batch):
-            checksum += int(frames[0, 0, 0, 0])
-        barrier()
-        t0 = time.perf_counter()
-        for frames in networks.indexed_render_batches(0, host_batches(renderer_steps, args.warmup), max_batch=batch):
-            checksum += int(frames[0, 0, 0, 0])  # touch the host result of every step
-        torch.cuda.synchronize()
-        e2e_s = time.perf_counter() - t0
-        if world > 1:
-            t = torch.tensor([e2e_s], device=device)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            e2e_s = float(t.item())
-        e2e = {"value": world * batch * renderer_steps / e2e_s, "unit": UNIT,
-               "h2d_bytes_per_step": batch * 512 * 4, "d2h_bytes_per_step": batch * res * res * 3,
-               "api": "MultiNetwork.indexed_render_batches (pinned host latents in, pinned host uint8 frames out)"}
+            run_e2e(min(args.warmup, e2e_steps))
+            barrier()
+            t0 = time.perf_counter()
+            run_e2e(e2e_steps)
+            torch.cuda.synchronize()
+            local_s = time.perf_counter() - t0
+            if world > 1:
+                dist.barrier()  # every rank's frames are in the buffer
+            e2e_s = max_over_ranks(time.perf_counter() - t0)
+            checksum = 0
+            if rank == 0:  # the encoder rank touches the first and last frame of every rank's range
+                for r in range(world):
+                    block = sink.frames[r * e2e_steps * batch: (r + 1) * e2e_steps * batch]
+                    checksum += int(block[0].sum()) + int(block[-1].sum())
+                    if int(block[-1].max()) == 0:
+                        raise RuntimeError(f"rank {r}'s frames did not arrive in the encoder's buffer")
+            e2e = {"value": world * batch * e2e_steps / e2e_s, "unit": UNIT,
+                   "h2d_bytes_per_step": int(host_source[:batch].nbytes), "d2h_bytes_per_step": batch * res * res * 3,
+                   "d2h_gbs_per_rank": batch * e2e_steps * res * res * 3 / local_s / 1e9,
+                   "api": "MultiNetwork.indexed_render_into (host latents in; every rank's frames DMA-written to their global "
+                          "frame index in ONE /dev/shm host buffer the encoder rank reads - frame_sharding.SharedFrameSink)"}
+        finally:
+            sink.close()
+    barrier()
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -443,21 +584,42 @@ def main():
         except Exception as error:  # pylint: disable=broad-except
             audio = {"error": repr(error)}
 
+    # ---- the other BASELINE configs as whole-track jobs (every rank takes part) ---------------------------------------
+    jobs = {}
+    if not args.no_extras and not matrices:
+        generator.release_buffers()
+        torch.cuda.empty_cache()
+        for kind, seconds in (("album", args.album_seconds), ("projection", args.projection_seconds), ("switching", args.switching_seconds)):
+            try:
+                report = track_jobs.run_track_job(kind, seconds, device, mode=args.mode, batch=batch,
+                                                  output_side=args.output_side if kind == "switching" else None)
+            except Exception as error:  # pylint: disable=broad-except
+                report = {"error": repr(error)}
+                if world > 1:
+                    raise
+            if rank == 0:
+                jobs[kind] = report
+            network_functions.release_idle_buffers()
+            torch.cuda.empty_cache()
+
     if rank == 0:
+        workload = (f"StyleGAN2 config-f {res}x{res} random-init (perturbed), batch-{batch} frame synthesis from "
+                    + ("projection-blend w+ latents (BASELINE configs[2]): w+ -> G_synthesis (constant noise) -> uint8" if matrices else
+                       "music latents (BASELINE configs[1]): z -> G_mapping -> psi 1.2 -> G_synthesis (fresh noise) -> uint8"))
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": args.mode, "data": "synthetic",
             "config": {
-                "workload": f"StyleGAN2 config-f {res}x{res} random-init (perturbed), batch-{batch} frame synthesis from "
-                            "music latents (BASELINE configs[1]): z -> G_mapping -> psi 1.2 -> G_synthesis (fresh noise) -> uint8",
+                "workload": workload,
                 "global_batch": batch * world, "frames_per_rank_per_step": batch, "track_frames": int(total_frames),
                 "parallelism": f"frame-range x{world}, weights replicated" + (", NCCL gather of uint8 frames to rank 0 each step (on a communication stream, overlapped with the next step; all gathers complete inside the timed region)" if world > 1 else ""),
                 "launch": "one CUDA-graph replay per step (captured once from the same C-ABI calls)",
                 "l2": "per-step working set (activations of 32 frames, > 10 GB) far exceeds the 126 MB L2; no flush needed",
                 "realtime_multiple_at_60fps": value / 60.0,
             },
-            "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu_baseline,
+            "e2e": e2e, "encoder_e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu_baseline,
+            "matrix_path": matrix_path, **jobs,
             "audio_half": audio,
             "clocks": clocks.summary(),
         }

@@ -565,8 +565,16 @@ class Dataset(_Object):
                 chunk = zlib.decompress(chunk)
             elif filter_id == FILTER_SHUFFLE:
                 count = len(chunk) // element
-                body = np.frombuffer(chunk, np.uint8, count * element).reshape(element, count).T
-                chunk = body.tobytes() + chunk[count * element:]
+                planes = np.frombuffer(chunk, np.uint8, count * element).reshape(element, count)
+                if element in (2, 4, 8):  # byte plane j is byte j of every element: rebuild the words with shifts
+                    word = np.dtype(f"<u{element}")
+                    merged = planes[0].astype(word)
+                    for j in range(1, element):
+                        merged |= planes[j].astype(word) << word.type(8 * j)
+                    body = merged.tobytes()
+                else:
+                    body = planes.T.tobytes()
+                chunk = body + chunk[count * element:]
             elif filter_id == FILTER_FLETCHER32:
                 chunk = chunk[:-4]
             else:
