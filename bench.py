@@ -441,19 +441,11 @@ def main():
     with ClockSampler(local_rank) as clocks:
         elapsed_ms, launches = timed_steps(matrices)
     value = world * batch * args.steps / (elapsed_ms * 1e-3)
-    matrix_path = None
-    if not matrices and not args.no_extras:
-        matrix_ms, _ = timed_steps(True)
-        matrix_path = {"value": world * batch * args.steps / (matrix_ms * 1e-3), "unit": UNIT, "ms_per_step": matrix_ms / args.steps,
-                       "what": "BASELINE configs[2] on the device: CUDA-graphed run_matrices (G_synthesis only, constant noise "
-                               f"buffers) at {res}^2 batch {batch} from projection-blend w+ latents [T,18,512] resident in HBM"
-                               + (", NCCL gather to rank 0 each step" if world > 1 else "")}
-
     # ---- roofline of the dominant kernels: CUDA events around every conv launch of a step ---------
     random_noise = not matrices
     conv_ms, other_ms = [], []
     per_layer = {}
-    for i in range(3):
+    for i in range(5):  # straight after the timed steps, so the clocks are the timed region's
         generator.profile_events = []
         begin = torch.cuda.Event(enable_timing=True)
         begin.record()
@@ -474,10 +466,18 @@ def main():
         conv_ms.append(conv)
         other_ms.append(other)
     generator.profile_events = None
+    matrix_path = None
+    if not matrices and not args.no_extras:
+        matrix_ms, _ = timed_steps(True)
+        matrix_path = {"value": world * batch * args.steps / (matrix_ms * 1e-3), "unit": UNIT, "ms_per_step": matrix_ms / args.steps,
+                       "what": "BASELINE configs[2] on the device: CUDA-graphed run_matrices (G_synthesis only, constant noise "
+                               f"buffers) at {res}^2 batch {batch} from projection-blend w+ latents [T,18,512] resident in HBM"
+                               + (", NCCL gather to rank 0 each step" if world > 1 else "")}
+
     # per-layer view of the same events: each modulated convolution against the roofline that bounds IT. Algorithmic
     # flops = 2 * 9 * Cin * Cout per output pixel (per INPUT pixel for up-convolutions) + the fused ToRGB's 2 * 3 * Cout;
     # bytes = what the launch really reads and writes (layer_bytes). Peaks: burst figures - each launch is timed alone
-    # inside three eager 8 ms passes, not inside a seconds-long step.
+    # inside five eager 8 ms passes, not inside a seconds-long step.
     burst_tflops, sustained_tflops = peaks["bf16_tflops"], peaks["bf16_tflops_sustained"]
     layers = []
     for index, conv in enumerate(generator.convs):
@@ -510,7 +510,7 @@ def main():
     roofline = {
         "bound": "tensor", "kernel": "modconv3x3_tc_kernel + modconv3x3_halo_kernel + upconv_fused_kernel (every modulated-convolution launch of a step: tcgen05 implicit GEMMs with fused demod/noise/bias/lrelu/FIR/ToRGB/skip/uint8 epilogues)",
         "achieved": achieved_tflops, "peak": burst_tflops, "unit": "TFLOP/s", "frac": achieved_tflops / burst_tflops,
-        "peak_source": f"bf16_tflops (burst: the conv launches are timed with CUDA events inside three eager 8 ms passes), {peak_source}",
+        "peak_source": f"bf16_tflops (burst: the conv launches are timed with CUDA events inside five eager 8 ms passes right after the timed steps), {peak_source}",
         "frac_of_sustained_peak": achieved_tflops / sustained_tflops, "sustained_peak": sustained_tflops,
         "traffic": traffic, "traffic_unit": "bytes per step (same launches as `achieved`)",
         "traffic_source": traffic_note, "layers": layers[:10], "algorithmic_hbm_bytes_per_step": HBM_BYTES_PER_FRAME.get(res, 0.0) * batch,

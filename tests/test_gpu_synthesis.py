@@ -5,9 +5,11 @@ against oracle/stylegan2_ref.py (float64 CPU) on the same random-init / perturbe
 Tolerances are BASELINE.json's: fp32 mode images within 1e-3 max-abs in [-1,1]; 16-bit mode uint8
 frames within +-1 LSB on >= 99.9 % of pixels. The 16-bit mode that meets that bar is "fp16"
 (11 significand bits, same tcgen05 kind::f16 rate as bf16) and it is the default everywhere.
-"bf16" stays selectable for networks whose activations overflow half precision, but 8 significand
-bits per stored activation over 2*log2(R)-2 layers put it at 3-7 LSB worst case, so it is held to
-the looser, measured bound written in BF16_MAX_ABS / BF16_WORST_LSB below ("Precision").
+"bf16" is a NON-CONFORMING fallback for networks whose activations overflow half precision (the range
+guard, GANCE_E_NONFINITE, says when): 8 significand bits per stored activation over 2*log2(R)-2
+layers put it at 3-7 LSB worst case and 83-97 % of pixels within 1 LSB. Its conformance test is an
+`xfail(strict=True)` that states the gap; `test_bf16_fallback_error_does_not_grow` holds it to the
+error it was measured at (BF16_* below) - a regression guard, not a parity claim ("Precision").
 (Pixel parity is "unpinned": the oracle is a restatement, the reference's StyleGAN2 code is absent
 - see oracle/stylegan2_ref.py.)
 """
@@ -76,9 +78,12 @@ def test_fp32_mode_matches_oracle(resolution, perturbed):
     assert within >= 0.999
 
 
-@pytest.mark.parametrize("mode", ["bf16", "fp16"])
-@pytest.mark.parametrize("resolution,perturbed", [(32, False), (64, True), (128, True)])
-def test_16bit_modes_match_oracle(mode, resolution, perturbed):
+BF16_GAP = ("bf16 operands (8-bit significand) do not reach the north_star tolerance of +-1 LSB on >= 99.9 % of pixels: "
+            "measured 83-97 % (3-7 LSB worst case). fp16 - same tcgen05 kind::f16 instruction, same rate - is the conforming "
+            "16-bit mode and the default; bf16 is the fallback for networks that overflow half's range.")
+
+
+def _sixteen_bit_case(mode, resolution, perturbed):
     spec, variables, oracle, z = _case(resolution, 1, perturbed, 2)
     gen = GeneratorOnDevice(spec, variables, _device(), mode=mode)
     want_w = oracle.truncate(oracle.mapping(z), 1.2)
@@ -89,7 +94,23 @@ def test_16bit_modes_match_oracle(mode, resolution, perturbed):
     max_abs = float((got - want).abs().max())
     print(f"{mode} mode {resolution}^2 perturbed={perturbed}: float max-abs {max_abs:.3e}; "
           f"uint8 exact {exact:.5f}, within 1 LSB {within:.5f}, worst {worst}")
-    assert_16bit_tolerance(mode, frames.cpu().numpy(), ref.convert_images_to_uint8(want), max_abs)
+    return frames.cpu().numpy(), ref.convert_images_to_uint8(want), max_abs
+
+
+@pytest.mark.parametrize("mode", ["fp16", pytest.param("bf16", marks=pytest.mark.xfail(strict=True, reason=BF16_GAP))])
+@pytest.mark.parametrize("resolution,perturbed", [(32, False), (64, True), (128, True)])
+def test_16bit_modes_match_oracle(mode, resolution, perturbed):
+    """The north_star bar for the 16-bit mode: uint8 frames within +-1 LSB on >= 99.9 % of pixels. fp16 meets it."""
+    got, want, _ = _sixteen_bit_case(mode, resolution, perturbed)
+    within, worst, _ = lsb_stats(got, want)
+    assert within >= 0.999, (within, worst)
+
+
+@pytest.mark.parametrize("resolution,perturbed", [(32, False), (64, True), (128, True)])
+def test_bf16_fallback_error_does_not_grow(resolution, perturbed):
+    """Regression guard of the non-conforming bf16 fallback: it stays within the error it was measured at."""
+    got, want, max_abs = _sixteen_bit_case("bf16", resolution, perturbed)
+    assert_16bit_tolerance("bf16", got, want, max_abs)
 
 
 def test_vector_and_matrix_paths_agree_with_oracle_semantics():
