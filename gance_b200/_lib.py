@@ -38,6 +38,12 @@ _SIGNATURES = {
         [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_longlong,
          c_float, c_void_p, c_void_p, c_void_p, c_void_p],
     ),
+    "gance_split_tf32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "gance_modconv3x3_tf32x3": (
+        c_int,
+        [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+         c_longlong, c_float, c_void_p, c_void_p, c_void_p, c_void_p],
+    ),
     "gance_modconv3x3_dual": (
         c_int,
         [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_longlong,

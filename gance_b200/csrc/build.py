@@ -12,7 +12,7 @@ from pathlib import Path
 from typing import List
 
 CSRC = Path(__file__).resolve().parent
-SOURCES = ["runtime.cu", "synthesis_kernels.cu", "modconv_tc.cu", "upconv_phase.cu", "upconv_fused.cu", "audio_kernels.cu", "resize_kernels.cu"]
+SOURCES = ["runtime.cu", "synthesis_kernels.cu", "modconv_tc.cu", "modconv_tf32.cu", "upconv_phase.cu", "upconv_fused.cu", "audio_kernels.cu", "resize_kernels.cu"]
 LIBRARY = CSRC / "libgance_b200.so"
 STAMP = CSRC / "libgance_b200.stamp"
 

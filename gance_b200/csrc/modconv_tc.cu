@@ -915,6 +915,16 @@ int encode_tensor_map(CUtensorMap* map, const void* base, bool half_operands, in
                       const cuuint64_t* strides_bytes, const cuuint32_t* box, int swizzle_bytes) {
     return make_tmap(map, base, half_operands, rank, dims, strides_bytes, box, swizzle_bytes);
 }
+// used by modconv_tf32.cu: fp32 elements, 128-byte swizzled rows
+int encode_tensor_map_f32(CUtensorMap* map, const void* base, int rank, const cuuint64_t* dims,
+                          const cuuint64_t* strides_bytes, const cuuint32_t* box) {
+    cuuint32_t elem_strides[5] = {1, 1, 1, 1, 1};
+    CUresult rc = g_encode_tiled(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<void*>(base), dims,
+                                 strides_bytes, box, elem_strides, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (rc != CUDA_SUCCESS) return fail(GANCE_E_DRIVER, "cuTensorMapEncodeTiled (fp32) failed with CUresult %d", (int)rc);
+    return GANCE_OK;
+}
 int sm_count() { return g_num_sms; }
 int configure_phase_kernels();
 int configure_fused_kernels();

@@ -34,6 +34,9 @@ from gance_b200.networks.generator_spec import (
 
 MODES = {
     "fp32": (_lib.GANCE_F32, torch.float32),
+    # fp32-grade validation mode on the tensor core: tcgen05 kind::tf32 with hi/lo operand splitting ("3xTF32"); fp32
+    # activations and fp32 bandwidth kernels exactly as "fp32", only the convolutions change (csrc/modconv_tf32.cu)
+    "tf32": (_lib.GANCE_F32, torch.float32),
     "bf16": (_lib.GANCE_BF16, torch.bfloat16),
     "fp16": (_lib.GANCE_F16, torch.float16),
 }
@@ -172,6 +175,11 @@ class GeneratorOnDevice:
             self.conv_wsq.append((hwio * hwio).sum(dim=(0, 1)).contiguous())  # [Cin,Cout]
             if self.mode == "fp32":
                 self.conv_w.append(hwio.contiguous())  # [3,3,Cin,Cout]
+            elif self.mode == "tf32":
+                # K-major [Cout,3,3,Cin], split like the activations: hi = low 13 significand bits cleared, lo = w - hi
+                kmajor = hwio.permute(3, 0, 1, 2).contiguous()
+                hi = (kmajor.view(torch.int32) & -8192).view(torch.float32)
+                self.conv_w.append(torch.stack([hi, kmajor - hi]).contiguous())  # [2,Cout,3,3,Cin]
             elif conv.up and self._up_form(conv) != "folded":
                 chunk = PHASE_CHUNK if self._up_form(conv) == "phase" else min(PHASE_CHUNK, conv.out_channels)
                 self.conv_w.append(phase_up_weight(hwio, chunk).to(self.torch_dtype))  # [9*Cout,Cin]
@@ -412,6 +420,9 @@ class GeneratorOnDevice:
             epilogue also writes the next block's modulated input x * styles[i + 1] (returned; None otherwise), which
             used to be a gance_scale_channels pass over x.
             """
+            if self.mode == "tf32":
+                self._tf32_conv(i, conv, batch, side, side, 1, x_src, demods[i], nz, nz_stride, None, x_dst, stream)
+                return None
             dual = self.mode != "fp32" and not is_last and conv.in_channels % 64 == 0 and conv.in_channels >= 128
             if not dual:
                 _lib.check(
@@ -454,7 +465,13 @@ class GeneratorOnDevice:
             side_in, side = up.in_resolution, up.out_resolution
             x_up = self._buffer(f"up{side}", (batch, side, side, up.out_channels), dt)
             nz, nz_stride = layer_noise(up_i, side)
-            if self.mode == "fp32":  # validation mode: FIR-first form on CUDA cores
+            if self.mode == "tf32":  # FIR-first: upsampled + style-modulated input, then a VALID 3xTF32 convolution
+                scratch = self._buffer("upfir", (batch, 2 * side_in + 2, 2 * side_in + 2, up.in_channels), dt)
+                _lib.check(lib.gance_upfir2x_pad(x.data_ptr(), code, batch, side_in, side_in, up.in_channels,
+                                                 styles[up_i].data_ptr(), scratch.data_ptr(), stream), "gance_upfir2x_pad")
+                self._tf32_conv(up_i, up, batch, side, side, 0, scratch, demods[up_i], nz, nz_stride, styles[conv_i], x_up,
+                                stream)
+            elif self.mode == "fp32":  # validation mode: FIR-first form on CUDA cores
                 scratch = self._buffer("upfir", (batch, 2 * side_in + 2, 2 * side_in + 2, up.in_channels), dt)
                 _lib.check(
                     lib.gance_modconv3x3_up2_fir(x.data_ptr(), code, batch, side_in, side_in, up.in_channels,
@@ -509,7 +526,7 @@ class GeneratorOnDevice:
             is_last = block == last
             want_float = return_float_image or not is_last
             y_out = self._buffer(f"skip{side}", (batch, side, side, 4), torch.float32) if want_float else None
-            if self.mode != "fp32" and conv.out_channels <= 256:
+            if self.mode not in ("fp32", "tf32") and conv.out_channels <= 256:
                 # Conv1 + ToRGB + skip (+ uint8) in one kernel; its activation output is pre-multiplied by the
                 # NEXT up-convolution's styles, and not written at all on the last block (nothing reads it).
                 x = None if is_last else self._buffer(f"act{side}", (batch, side, side, conv.out_channels), dt)
@@ -545,6 +562,22 @@ class GeneratorOnDevice:
         if return_float_image:
             return frames, y
         return frames
+
+    def _tf32_conv(self, i: int, conv, batch: int, h_out: int, w_out: int, pad: int, x_src: torch.Tensor, demod, nz,
+                   nz_stride: int, next_styles, x_dst: torch.Tensor, stream: int) -> None:
+        """One convolution of the "tf32" mode: split the (already modulated) fp32 input into hi + lo, then 3xTF32."""
+        h_in, w_in = h_out + 2 - 2 * pad, w_out + 2 - 2 * pad
+        split = self._buffer("tf32_split", (2, batch, h_in, w_in, conv.in_channels), torch.float32)
+        _lib.check(self.lib.gance_split_tf32(x_src.data_ptr(), None, batch, h_in, w_in, conv.in_channels,
+                                             split[0].data_ptr(), split[1].data_ptr(), stream), "gance_split_tf32")
+        weights = self.conv_w[i]
+        _lib.check(
+            self.lib.gance_modconv3x3_tf32x3(split[0].data_ptr(), split[1].data_ptr(), batch, h_out, w_out, conv.in_channels,
+                                             conv.out_channels, pad, weights[0].data_ptr(), weights[1].data_ptr(),
+                                             demod.data_ptr(), _ptr(nz), nz_stride, self.conv_strength[i],
+                                             self.conv_bias[i].data_ptr(), _ptr(next_styles), x_dst.data_ptr(), stream),
+            f"gance_modconv3x3_tf32x3({h_out})",
+        )
 
     def run_vectors(self, z: torch.Tensor, truncation_psi: float = 1.2, noise_mode: str = "random", **kwargs):
         """Batched `Gs.run(z, None, truncation_psi=1.2)` (network_functions.py:151-158)."""

@@ -147,6 +147,23 @@ int gance_modconv3x3_dual(const void* x, int dtype, int batch, int h_out, int w_
                           const float* bias, const float* next_styles, void* out_scaled, void* out,
                           void* stream);
 
+/* ---- fp32-grade validation mode on the tensor core ("3xTF32") -----------------------------------
+ * north_star: "tcgen05/TMEM implicit-GEMM ... bf16 with fp32 accumulate, plus an fp32/TF32 validation mode". The same
+ * modulated 3x3 convolution + noise + fused_bias_act as gance_modconv3x3(GANCE_F32) - the reference's fp32 arithmetic in
+ * networks_stylegan2.modulated_conv2d_layer - computed by tcgen05.mma.kind::tf32 with error compensation: every operand
+ * is split x = hi + lo (hi = x with its low 13 significand bits cleared, exactly a tf32 value; lo = x - hi, exact) and
+ * D += lo*hi + hi*lo + hi*hi with fp32 accumulation in TMEM (the dropped lo*lo term is ~2^-22 relative).
+ * gance_split_tf32: x [B,H,W,C] f32 (times styles [B,C] when styles != NULL) -> hi, lo [B,H,W,C] f32. C % 4 == 0.
+ * gance_modconv3x3_tf32x3: x_hi/x_lo [B,H+2-2pad,W+2-2pad,Cin] f32 (already modulated), w_hi/w_lo [Cout][3][3][Cin] f32
+ * (runtime-scaled, split the same way), epilogue and remaining arguments as gance_modconv3x3; out [B,H,W,Cout] f32.
+ * Cin % 32 == 0, Cout % 32 == 0. The up-convolutions of this mode run FIR-first: gance_upfir2x_pad, split, pad = 0. */
+int gance_split_tf32(const float* x, const float* styles, int batch, int h, int w, int channels, float* hi,
+                     float* lo, void* stream);
+int gance_modconv3x3_tf32x3(const float* x_hi, const float* x_lo, int batch, int h_out, int w_out, int c_in,
+                            int c_out, int pad, const float* w_hi, const float* w_lo, const float* demod,
+                            const float* noise, long long noise_batch_stride, float noise_strength,
+                            const float* bias, const float* next_styles, float* out, void* stream);
+
 /* ---- 2x FIR upsampling feeding the up-convolution ----------------------------------------------
  * First half of upsample_conv_2d in FIR-first form (tests/test_oracle_stylegan2.py proves
  * conv_transpose(stride 2) -> upfirdn([1,3,3,1]*4, pad 1,1) == VALID 3x3 conv of this tensor):

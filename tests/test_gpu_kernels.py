@@ -265,6 +265,75 @@ def test_modconv3x3_tcgen05_matches_oracle(lib, mode, cin, cout, side, batch, pa
     assert bool((diff <= bound).all()), f"{name}: {int((diff > bound).sum())} elements out of bound"
 
 
+def _split_tf32(lib, tensor, styles=None):
+    """gance_split_tf32 on an NHWC fp32 device tensor -> (hi, lo)."""
+    batch, h, w, c = tensor.shape
+    hi, lo = torch.empty_like(tensor), torch.empty_like(tensor)
+    _lib.check(lib.gance_split_tf32(tensor.data_ptr(), None if styles is None else styles.data_ptr(), batch, h, w, c,
+                                    hi.data_ptr(), lo.data_ptr(), stream()), "gance_split_tf32")
+    return hi, lo
+
+
+def test_split_tf32_is_exact_and_hi_is_a_tf32_value(lib):
+    g = torch.Generator().manual_seed(3)
+    x = (torch.randn(2, 5, 7, 64, generator=g) * torch.logspace(-6, 6, 64)).cuda()
+    styles = torch.randn(2, 64, generator=g).cuda()
+    hi, lo = _split_tf32(lib, x)
+    assert torch.equal(hi + lo, x)  # the split loses nothing
+    assert int((hi.view(torch.int32) & 0x1FFF).abs().max()) == 0  # low 13 significand bits of hi are clear
+    assert float((lo.abs() / x.abs().clamp_min(1e-30)).max()) < 2.0 ** -10
+    hi_s, lo_s = _split_tf32(lib, x, styles)
+    assert torch.equal(hi_s + lo_s, x * styles[:, None, None, :])
+
+
+@pytest.mark.parametrize("cin,cout,side,batch,pad,name", CONV_CASES)
+def test_modconv3x3_tf32x3_matches_oracle_at_fp32_grade(lib, cin, cout, side, batch, pad, name):
+    """
+    The tensor-core validation mode (tcgen05 kind::tf32, hi/lo split, 3 MMAs per K step) against float64 arithmetic, at
+    the tolerance the CUDA-core fp32 kernel is held to - and against that kernel itself.
+    """
+    g = torch.Generator().manual_seed(0)
+    side_in = side + 2 - 2 * pad
+    x = torch.randn(batch, cin, side_in, side_in, dtype=F64, generator=g)
+    weight = torch.randn(3, 3, cin, cout, dtype=F64, generator=g) / np.sqrt(9 * cin)
+    demod = torch.rand(batch, cout, dtype=F64, generator=g) + 0.5
+    noise = torch.randn(batch, side, side, dtype=F64, generator=g)
+    bias = torch.randn(cout, dtype=F64, generator=g) * 0.1
+    nxt = torch.randn(batch, cout, dtype=F64, generator=g)
+    strength = 0.07
+    x_dev = dev(x.permute(0, 2, 3, 1))
+    w_kmajor = dev(weight.permute(3, 0, 1, 2))  # [Cout,3,3,Cin]
+    w_hi = (w_kmajor.view(torch.int32) & -8192).view(torch.float32)
+    w_lo = w_kmajor - w_hi
+    x_hi, x_lo = _split_tf32(lib, x_dev)
+    out = torch.full((batch, side, side, cout), float("nan"), device="cuda")
+    _lib.check(
+        lib.gance_modconv3x3_tf32x3(x_hi.data_ptr(), x_lo.data_ptr(), batch, side, side, cin, cout, pad, w_hi.data_ptr(),
+                                    w_lo.data_ptr(), dev(demod).data_ptr(), dev(noise).data_ptr(), side * side, strength,
+                                    dev(bias).data_ptr(), dev(nxt).data_ptr(), out.data_ptr(), stream()),
+        "gance_modconv3x3_tf32x3",
+    )
+    torch.cuda.synchronize()
+    assert not torch.isnan(out).any(), "kernel left output unwritten"
+    x_used, w_used = x_dev.double().cpu().permute(0, 3, 1, 2), w_kmajor.double().cpu().permute(1, 2, 3, 0)
+    f32 = lambda t: t.float().double()  # noqa: E731
+    want = F.conv2d(x_used, w_used.permute(3, 2, 0, 1), padding=pad) * f32(demod)[:, :, None, None]
+    want = want + f32(noise)[:, None] * np.float32(strength) + f32(bias)[None, :, None, None]
+    want = F.leaky_relu(want, 0.2) * np.sqrt(2.0) * f32(nxt)[:, :, None, None]
+    err = rel_err(out.permute(0, 3, 1, 2), want)
+    print(f"tf32x3 {name}: rel err {err:.3e}")
+    assert err < 2e-5, name
+    # the same layer on the CUDA-core fp32 kernel: the two validation modes agree far inside the parity tolerance
+    plain = torch.empty_like(out)
+    _lib.check(
+        lib.gance_modconv3x3(x_dev.data_ptr(), 0, batch, side, side, cin, cout, pad, dev(weight).data_ptr(),
+                             dev(demod).data_ptr(), dev(noise).data_ptr(), side * side, strength, dev(bias).data_ptr(),
+                             dev(nxt).data_ptr(), plain.data_ptr(), stream()),
+        "gance_modconv3x3",
+    )
+    assert rel_err(out.permute(0, 3, 1, 2), plain.permute(0, 3, 1, 2).double().cpu()) < 1e-5
+
+
 def test_modconv3x3_tcgen05_without_next_style_and_noise_per_sample(lib):
     got, want = _run_modconv(lib, "bf16", 64, 64, 16, 3, 1, seed=4, with_next=False)
     assert rel_err(got, want) < 2.0 ** -7

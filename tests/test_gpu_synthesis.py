@@ -60,10 +60,12 @@ def lsb_stats(got_u8: np.ndarray, want_u8: np.ndarray):
     return float((diff <= 1).mean()), int(diff.max()), float((diff == 0).mean())
 
 
+@pytest.mark.parametrize("mode", ["fp32", "tf32"])
 @pytest.mark.parametrize("resolution,perturbed", [(32, False), (64, True)])
-def test_fp32_mode_matches_oracle(resolution, perturbed):
+def test_fp32_mode_matches_oracle(resolution, perturbed, mode):
+    """Both validation modes: CUDA-core fp32 FMA ("fp32") and 3xTF32 on the tensor core ("tf32")."""
     spec, variables, oracle, z = _case(resolution, 0, perturbed, 3)
-    gen = GeneratorOnDevice(spec, variables, _device(), mode="fp32")
+    gen = GeneratorOnDevice(spec, variables, _device(), mode=mode)
     wplus = gen.mapping(torch.as_tensor(z), truncation_psi=1.2)
     want_w = oracle.truncate(oracle.mapping(z), 1.2)
     assert float((wplus.double().cpu() - want_w).abs().max() / want_w.abs().max()) < 2e-5
@@ -71,7 +73,7 @@ def test_fp32_mode_matches_oracle(resolution, perturbed):
     want = oracle.synthesis(want_w.numpy())  # [B,3,R,R] float64
     got = image[..., :3].permute(0, 3, 1, 2).double().cpu()
     max_abs = float((got - want).abs().max())
-    print(f"fp32 mode {resolution}^2 perturbed={perturbed}: max-abs {max_abs:.3e} (|image| max {float(want.abs().max()):.2f})")
+    print(f"{mode} mode {resolution}^2 perturbed={perturbed}: max-abs {max_abs:.3e} (|image| max {float(want.abs().max()):.2f})")
     assert max_abs < 1e-3
     within, worst, exact = lsb_stats(frames.cpu().numpy(), ref.convert_images_to_uint8(want))
     print(f"   uint8: exact {exact:.5f}, within 1 LSB {within:.5f}, worst {worst}")
@@ -221,7 +223,7 @@ def test_graph_replay_equals_eager_and_draws_fresh_noise():
     assert not torch.equal(first, second) and not torch.equal(second, third)
 
 
-@pytest.mark.parametrize("mode", ["fp16", "fp32"])
+@pytest.mark.parametrize("mode", ["fp16", "fp32", "tf32"])
 def test_512_generator_matches_oracle(mode):
     """
     A 512^2 config-f generator end to end (BASELINE config 5 names 512^2 networks). Its last block runs the 64-channel
@@ -236,7 +238,7 @@ def test_512_generator_matches_oracle(mode):
     max_abs = float((got - want).abs().max())
     within, worst, exact = lsb_stats(frames.cpu().numpy(), ref.convert_images_to_uint8(want))
     print(f"512^2 {mode}: float max-abs {max_abs:.3e}; uint8 exact {exact:.5f} within1 {within:.5f} worst {worst}")
-    if mode == "fp32":
+    if mode in ("fp32", "tf32"):
         assert max_abs < 1e-3
     assert within >= 0.999, (within, worst)
     # the production call (no float image requested: the last block writes uint8 only) gives the same frames
@@ -244,17 +246,18 @@ def test_512_generator_matches_oracle(mode):
     gen.release_buffers()
 
 
+@pytest.mark.parametrize("mode", ["fp32", "tf32"])
 @pytest.mark.parametrize("resolution", [256, 1024])
-def test_fp32_mode_max_abs_at_the_sizes_the_configs_name(resolution):
+def test_fp32_mode_max_abs_at_the_sizes_the_configs_name(resolution, mode):
     """north_star: fp32-mode images within 1e-3 max-abs in [-1,1] - at 256^2 (config 1) and 1024^2 (config 2), one frame."""
     spec, variables, oracle, z = _case(resolution, 8, True, 1)
-    gen = GeneratorOnDevice(spec, variables, _device(), mode="fp32")
+    gen = GeneratorOnDevice(spec, variables, _device(), mode=mode)
     frames, image = gen.run_vectors(torch.as_tensor(z), noise_mode="const", return_float_image=True)
     want = oracle.run_vector(z)
     got = image[..., :3].permute(0, 3, 1, 2).double().cpu()
     max_abs = float((got - want).abs().max())
     within, worst, exact = lsb_stats(frames.cpu().numpy(), ref.convert_images_to_uint8(want))
-    print(f"fp32 mode {resolution}^2: max-abs {max_abs:.3e} (|image| max {float(want.abs().max()):.2f}); "
+    print(f"{mode} mode {resolution}^2: max-abs {max_abs:.3e} (|image| max {float(want.abs().max()):.2f}); "
           f"uint8 exact {exact:.5f} within1 {within:.5f} worst {worst}")
     assert max_abs < 1e-3
     assert within >= 0.999
