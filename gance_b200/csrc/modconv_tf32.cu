@@ -6,9 +6,16 @@
 // the 16-bit tensor path, so parity at 1024^2 costs seconds. A single tf32 pass (10-bit significand, inputs truncated by
 // the tensor core) is too coarse for the 1e-3 max-abs criterion over 18 layers, so every operand is split:
 //     x = x_hi + x_lo,   x_hi = x with its low 13 significand bits cleared (exactly a tf32 value), x_lo = x - x_hi (exact)
-// and D += A_lo*B_hi + A_hi*B_lo + A_hi*B_hi with fp32 accumulation in TMEM: the dropped term A_lo*B_lo and the
-// truncation of the lo parts are both ~2^-22 relative - fp32-grade. Activations are split by gance_split_tf32 (which can
-// also apply the per-sample style), weights once at upload.
+// and D = A_lo*B_hi + A_hi*B_lo + A_hi*B_hi with fp32 accumulation in TMEM: the dropped term A_lo*B_lo and the
+// truncation of the lo parts are both ~2^-22 relative. Activations are split by gance_split_tf32 (which can also apply
+// the per-sample style), weights once at upload.
+//
+// What limits the result is the accumulation itself: the tensor core TRUNCATES when it adds a K = 8 block of products to
+// the accumulator, up to one ulp of the accumulator per instruction and always in the same direction, so a chain of n
+// instructions drifts by ~n * 2^-24 (measured with everything in one accumulator: 3.4e-5 relative at K = 4608, 3e-6 at
+// K = 288). Two thirds of those instructions are the tiny cross terms, which cost a full ulp of the LARGE sum each. So a
+// tile keeps three accumulators - cross terms (magnitude 2^-11 of the sum: their ulps are negligible), hi*hi of the even
+// K steps and hi*hi of the odd K steps - and the epilogue adds them in fp32 with round-to-nearest.
 //
 // Same structure as modconv_tc.cu: persistent CTAs, warp 0 = TMA producer (four boxes per stage: A_hi, A_lo, B_hi, B_lo,
 // 128-byte swizzled rows of 32 floats), warp 1 = MMA issuer (M = 128 pixels, N = N_TILE channels, K = 8 per instruction),
@@ -74,8 +81,10 @@ modconv3x3_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_x_hi, const __
                          const __grid_constant__ CUtensorMap tmap_w_hi, const __grid_constant__ CUtensorMap tmap_w_lo,
                          const Tf32Params p) {
     using L = Tf32Smem<N_TILE, STAGES>;
-    constexpr uint32_t kTmemCols = 2 * N_TILE < 32 ? 32 : 2 * N_TILE;
-    static_assert((kTmemCols & (kTmemCols - 1)) == 0 && kTmemCols <= 512, "TMEM columns must be a power of two");
+    // two tile buffers x three accumulators (hi*hi even K steps, hi*hi odd K steps, cross terms) of N_TILE columns
+    constexpr uint32_t kAccCols = 3 * N_TILE;
+    constexpr uint32_t kTmemCols = 2 * kAccCols <= 256 ? 256 : 512;
+    static_assert(2 * kAccCols <= 512, "TMEM holds 512 columns");
     static_assert(L::kABytes % 1024 == 0 && L::kBBytes % 1024 == 0, "operand buffers must stay 1024-byte aligned");
 
     extern __shared__ uint8_t smem_raw[];
@@ -166,7 +175,8 @@ modconv3x3_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_x_hi, const __
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
             mbar_wait(tmem_empty_bar + acc, acc_phase ^ 1u);
             tcgen05_fence_after();
-            const uint32_t d_tmem = tmem_base + (uint32_t)(acc * N_TILE);
+            const uint32_t d_hi0 = tmem_base + (uint32_t)acc * kAccCols;
+            const uint32_t d_hi1 = d_hi0 + (uint32_t)N_TILE, d_lo = d_hi0 + 2u * (uint32_t)N_TILE;
             for (int it = 0; it < k_iters; ++it) {
                 mbar_wait(full_bar + stage, phase);
                 tcgen05_fence_after();
@@ -179,10 +189,9 @@ modconv3x3_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_x_hi, const __
 #pragma unroll
                     for (int k = 0; k < kTf32BlockK / kTf32UmmaK; ++k) {
                         const uint64_t step = (uint64_t)(k * 2);  // +32 bytes along K inside the swizzle atom
-                        // small terms first, the large product last
-                        umma_tf32(d_tmem, a_lo + step, b_hi + step, idesc, (it | k) != 0 ? 1u : 0u);
-                        umma_tf32(d_tmem, a_hi + step, b_lo + step, idesc, 1u);
-                        umma_tf32(d_tmem, a_hi + step, b_hi + step, idesc, 1u);
+                        umma_tf32(d_lo, a_lo + step, b_hi + step, idesc, (it | k) != 0 ? 1u : 0u);
+                        umma_tf32(d_lo, a_hi + step, b_lo + step, idesc, 1u);
+                        umma_tf32((k & 1) ? d_hi1 : d_hi0, a_hi + step, b_hi + step, idesc, (it | (k >> 1)) != 0 ? 1u : 0u);
                     }
                     umma_commit(empty_bar + stage);
                     if (it == k_iters - 1) umma_commit(tmem_full_bar + acc);
@@ -204,7 +213,7 @@ modconv3x3_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_x_hi, const __
         const int wl = row & (p.tile_w - 1);
         const int hl = row >> p.tile_w_log2;
         uint32_t full_phase = 0;
-        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(group * N_TILE);
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)group * kAccCols;
         for (int tile = blockIdx.x + group * gridDim.x; tile < total_tiles; tile += 2 * gridDim.x) {
             int n0, b, h0, w0;
             decode(tile, n0, b, h0, w0);
@@ -218,9 +227,14 @@ modconv3x3_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_x_hi, const __
             tcgen05_fence_after();
 #pragma unroll 1
             for (int c0 = 0; c0 < N_TILE; c0 += 32) {
-                uint32_t r[32];
+                uint32_t r[32], r1[32], r2[32];
                 tmem_ld_32x32(taddr + (uint32_t)c0, r);
+                tmem_ld_32x32(taddr + (uint32_t)(N_TILE + c0), r1);
+                tmem_ld_32x32(taddr + (uint32_t)(2 * N_TILE + c0), r2);
                 tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 32; ++i)  // (hi*hi even + hi*hi odd) + cross terms, rounded to nearest
+                    r[i] = __float_as_uint(__fadd_rn(__fadd_rn(__uint_as_float(r[i]), __uint_as_float(r1[i])), __uint_as_float(r2[i])));
                 if (valid) {
                     float* dst = p.out + (((size_t)b * p.h_out + h) * p.w_out + w) * p.c_out + n0 + c0;
 #pragma unroll

@@ -37,6 +37,11 @@ def read_wav_file(wav_path: Path, convert_to_32bit_float: bool = True) -> WavFil
     if convert_to_32bit_float and wav_data.dtype != np.float32:
         if wav_data.dtype not in (np.int32, np.int16, np.int8):
             raise ValueError(f"Cannot safely convert wav data to np.float32, unknown input format: {wav_data.dtype}")
+        if wav_data.dtype == np.int8 and wav_data.size and int(wav_data.min()) < 0:
+            # the reference maps int8 through interp1d([0, 255], [-1, 1]) (music.py:197-198), which refuses values
+            # outside its x range: a negative sample is a ValueError there, so it is one here (scipy itself hands
+            # 8-bit WAVs over as uint8, which the line above already refuses, exactly like the reference)
+            raise ValueError("A value in x_new is below the interpolation range.")
         wav_data = audio_device.pcm_to_float(wav_data).cpu().numpy()
     return WavFileProperties(sample_rate=sample_rate, wav_data=wav_data, name=Path(wav_path).with_suffix("").name)
 

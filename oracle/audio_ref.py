@@ -54,6 +54,9 @@ def wav_to_float32(wav_data: np.ndarray) -> np.ndarray:
     ranges = {np.dtype(np.int32): (-2147483648, 2147483647), np.dtype(np.int16): (-32768, 32767), np.dtype(np.int8): (0, 255)}
     if wav_data.dtype not in ranges:
         raise ValueError(f"Cannot safely convert wav data to np.float32, unknown input format: {wav_data.dtype}")
+    low, high = ranges[wav_data.dtype]
+    if wav_data.size and (wav_data.min() < low or wav_data.max() > high):  # interp1d(bounds_error=True) in the reference
+        raise ValueError("A value in x_new is below the interpolation range.")
     return remap_values_into_range(wav_data, ranges[wav_data.dtype], (-1, 1)).astype(np.float32)
 
 

@@ -331,7 +331,7 @@ def test_modconv3x3_tf32x3_matches_oracle_at_fp32_grade(lib, cin, cout, side, ba
                              dev(nxt).data_ptr(), plain.data_ptr(), stream()),
         "gance_modconv3x3",
     )
-    assert rel_err(out.permute(0, 3, 1, 2), plain.permute(0, 3, 1, 2).double().cpu()) < 1e-5
+    assert rel_err(out.permute(0, 3, 1, 2), plain.permute(0, 3, 1, 2).double().cpu()) < 2e-5
 
 
 def test_modconv3x3_tcgen05_without_next_style_and_noise_per_sample(lib):

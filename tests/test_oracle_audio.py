@@ -155,3 +155,42 @@ def test_against_reference_on_fresh_input():
     mine_blend = audio_ref.alpha_blend_projection_file(projection, 0.4, True, (-1, 1), 10, mine, 512, [0, 1])
     np.testing.assert_allclose(mine_blend.combined, theirs_blend.combined.data, rtol=0, atol=1e-12)
     assert np.array_equal(mine_blend.network_indices, theirs_blend.network_indices.result.data)
+
+
+def test_eight_bit_pcm_behaves_as_the_reference_does(tmp_path):
+    """
+    `read_wav_file` (gance/vector_sources/music.py:190-205) maps int8 data through interp1d([0, 255], [-1, 1]): samples in
+    [0, 127] land in [-1, -0.004], a NEGATIVE sample is outside the interpolation range and raises ValueError; uint8 (what
+    scipy.io.wavfile actually returns for 8-bit files) is refused as an unknown format. Oracle and drop-in both do that -
+    the host-side checks run before any GPU work, so this is a CPU test.
+    """
+    from unittest import mock
+
+    from gance_b200.vector_sources import music
+
+    ok = np.array([0, 1, 64, 127], dtype=np.int8)
+    want = (2.0 / 255.0 * ok.astype(np.float64) - 1.0).astype(np.float32)
+    np.testing.assert_allclose(audio_ref.wav_to_float32(ok), want, rtol=0, atol=1e-7)
+    with pytest.raises(ValueError):
+        audio_ref.wav_to_float32(np.array([3, -1], dtype=np.int8))
+    with pytest.raises(ValueError):
+        audio_ref.wav_to_float32(np.array([3, 200], dtype=np.uint8))
+    for data, message in ((np.array([3, -1], dtype=np.int8), "interpolation range"), (np.array([3, 200], dtype=np.uint8), "unknown input format")):
+        with mock.patch.object(music.wavfile, "read", return_value=(44100, data)):
+            with pytest.raises(ValueError, match=message):
+                music.read_wav_file(tmp_path / "eight_bit.wav")
+
+
+@needs_reference
+def test_eight_bit_pcm_reference_errors(tmp_path):
+    """The reference's own `read_wav_file` on the same arrays (scipy's reader patched to hand them over)."""
+    from unittest import mock
+
+    reference_music = reference_shim.load().music
+    with mock.patch.object(reference_music.wavfile, "read", return_value=(44100, np.array([0, 64, 127], dtype=np.int8))):
+        got = reference_music.read_wav_file(tmp_path / "x.wav").wav_data
+    np.testing.assert_array_equal(got, audio_ref.wav_to_float32(np.array([0, 64, 127], dtype=np.int8)))
+    for data in (np.array([3, -1], dtype=np.int8), np.array([3, 200], dtype=np.uint8)):
+        with mock.patch.object(reference_music.wavfile, "read", return_value=(44100, data)):
+            with pytest.raises(ValueError):
+                reference_music.read_wav_file(tmp_path / "x.wav")
