@@ -57,12 +57,12 @@ def _case(resolution, seed, perturbed, batch):
 
 def fp32_grade_bound(mode: str, want: torch.Tensor) -> float:
     """
-    north_star: "fp32-mode images within 1e-3 max-abs in [-1,1]". The CUDA-core fp32 mode is held to exactly that,
-    absolute, whatever the image's range. The tensor-core validation mode ("tf32": 3xTF32, whose accumulation inside the
-    tensor core truncates - csrc/modconv_tf32.cu) is held to 1e-3 OF THE IMAGE'S RANGE: the random-init networks of these
-    tests produce images spanning +-5..7, not the +-1 of a trained network the criterion is written for.
+    north_star: "fp32-mode images within 1e-3 max-abs in [-1,1]". Both validation modes are held to exactly that,
+    ABSOLUTE, although the random-init networks of these tests produce images spanning +-5..7 rather than the +-1 of a
+    trained network: the CUDA-core fp32 mode measures 2-3e-5, the tensor-core 3xTF32 mode 1.5-5e-4.
     """
-    return 1e-3 if mode == "fp32" else 1e-3 * max(1.0, float(want.abs().max()))
+    del mode, want
+    return 1e-3
 
 
 def lsb_stats(got_u8: np.ndarray, want_u8: np.ndarray):
