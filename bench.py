@@ -76,6 +76,8 @@ def parse_args():
     ap.add_argument("--projection-seconds", type=float, default=60.0)
     ap.add_argument("--switching-seconds", type=float, default=20.0)
     ap.add_argument("--output-side", type=int, default=2160, help="output side length of the switching job")
+    ap.add_argument("--streams", type=int, default=2, choices=[1, 2],
+                    help="compute streams the timed steps alternate over (2: consecutive batches overlap on the device)")
     return ap.parse_args()
 
 
@@ -387,7 +389,7 @@ def main():
     wplus = wplus_all[start_frame: start_frame + local_frames, : generator.num_ws].contiguous()
     matrices = args.config == "matrices"
     # two output slots: with N > 1 the gather of step i runs on a communication stream while step i+1 is computed
-    slots = 2 if world > 1 else 1
+    slots = 2
     frames_slots = [torch.empty((batch, res, res, 3), dtype=torch.uint8, device=device) for _ in range(slots)]
     frames_out = frames_slots[0]
     gathered = [torch.empty((world * batch, res, res, 3), dtype=torch.uint8, device=device) if (world > 1 and rank == 0) else None
@@ -395,19 +397,27 @@ def main():
     comm_stream = torch.cuda.Stream(device=device) if world > 1 else None
     slot_free = [None] * slots
 
+    # consecutive steps alternate over two generator contexts (own work buffers / graphs, shared weights) on two streams:
+    # the tail of one batch's kernels and its small latency-bound launches overlap the next batch's
+    contexts = [generator.context(k) for k in range(args.streams)]
+    compute_streams = [torch.cuda.Stream(device=device) for _ in range(args.streams)]
+
     def render(i: int, out, use_matrices: bool):
         offset = (i * batch) % (min(local_frames, wplus.shape[0]) - batch + 1)
+        context = contexts[i % len(contexts)]
         if use_matrices:
-            generator.run_matrices_graphed(wplus[offset: offset + batch], out)
+            context.run_matrices_graphed(wplus[offset: offset + batch], out)
         else:
-            generator.run_vectors_graphed(latents[offset: offset + batch], out, truncation_psi=1.2, noise_mode="random")
+            context.run_vectors_graphed(latents[offset: offset + batch], out, truncation_psi=1.2, noise_mode="random")
 
     def step(i: int, use_matrices: bool = matrices):
         slot = i % slots
-        main = torch.cuda.current_stream(device)
+        main = compute_streams[i % len(compute_streams)]
+        main.wait_stream(torch.cuda.current_stream(device))
         if slot_free[slot] is not None:
             main.wait_event(slot_free[slot])  # the gather that last read this slot has finished
-        render(i, frames_slots[slot], use_matrices)
+        with torch.cuda.stream(main):
+            render(i, frames_slots[slot], use_matrices)
         if world > 1:
             computed = torch.cuda.Event()
             computed.record(main)
@@ -429,13 +439,15 @@ def main():
         start_event.record()
         for i in range(args.steps):
             step(args.warmup + i, use_matrices)
+        for stream in compute_streams:
+            torch.cuda.current_stream(device).wait_stream(stream)
         if comm_stream is not None:
             torch.cuda.current_stream(device).wait_stream(comm_stream)  # the last gathers are inside the timed region
         stop_event.record()
         barrier()
         elapsed = max_over_ranks(start_event.elapsed_time(stop_event))
         # a step is one CUDA-graph replay: our kernels inside it were counted when the graph was captured
-        launched = (_lib.launch_count() - before) + generator.launches_per_replay * args.steps
+        launched = (_lib.launch_count() - before) + contexts[0].launches_per_replay * args.steps
         return elapsed, launched
 
     with ClockSampler(local_rank) as clocks:
@@ -614,7 +626,8 @@ def main():
                 "workload": workload,
                 "global_batch": batch * world, "frames_per_rank_per_step": batch, "track_frames": int(total_frames),
                 "parallelism": f"frame-range x{world}, weights replicated" + (", NCCL gather of uint8 frames to rank 0 each step (on a communication stream, overlapped with the next step; all gathers complete inside the timed region)" if world > 1 else ""),
-                "launch": "one CUDA-graph replay per step (captured once from the same C-ABI calls)",
+                "launch": "one CUDA-graph replay per step (captured once from the same C-ABI calls)"
+                          + (f"; steps alternate over {args.streams} streams with separate work buffers, so consecutive batches overlap" if args.streams > 1 else ""),
                 "l2": "per-step working set (activations of 32 frames, > 10 GB) far exceeds the 126 MB L2; no flush needed",
                 "realtime_multiple_at_60fps": value / 60.0,
             },

@@ -908,7 +908,7 @@ static int configure_halo() {
     }
 }
 
-static bool g_use_halo = true;
+static const bool g_use_halo = true;
 
 // used by upconv_phase.cu
 int encode_tensor_map(CUtensorMap* map, const void* base, bool half_operands, int rank, const cuuint64_t* dims,
@@ -953,8 +953,6 @@ int init_tensor_core_path() {
     if ((rc = tc::configure_halo<32, 32, 4>()) != GANCE_OK) return rc;
     if ((rc = tc::configure_phase_kernels()) != GANCE_OK) return rc;
     if ((rc = tc::configure_fused_kernels()) != GANCE_OK) return rc;
-    const char* halo = getenv("GANCE_HALO");  // GANCE_HALO=0 forces the per-tap kernel (A/B measurements)
-    tc::g_use_halo = !(halo != nullptr && halo[0] == '0');
     return GANCE_OK;
 }
 

@@ -18,6 +18,7 @@ Data flow per batch (NHWC activations, `mode` = "bf16" | "fp16" | "fp32"; DESIGN
       ToRGB + skip (+ uint8)        gance_torgb_skip
 """
 
+import copy
 import os
 from typing import Dict, Iterable, Iterator, List, Optional, Sequence
 
@@ -115,8 +116,10 @@ class GeneratorOnDevice:
     """One generator's weights resident in HBM in kernel layout, plus per-batch work buffers."""
 
     def __init__(self, spec: GeneratorSpec, variables: Dict[str, np.ndarray], device: torch.device, mode: str = "fp16",
-                 noise_seed: Optional[int] = None) -> None:
+                 noise_seed: Optional[int] = None, up_form: Optional[str] = None) -> None:
         """
+        up_form: None picks the measured-best kernel per up-convolution (`_up_form`); "folded" | "phase" | "fused" forces
+        one where the shape is eligible - an A/B switch for tools/profile_layers.py, not something a run needs.
         noise_seed: Philox key of the "random" noise mode (the vector path's fresh noise per call). None draws one from
         os.urandom, so two processes - or two ranks started from the same script - never share a noise stream; pass an
         integer for a reproducible run (mix the rank in yourself when every rank passes the same number).
@@ -125,6 +128,9 @@ class GeneratorOnDevice:
             raise ValueError(f"mode must be one of {sorted(MODES)}, got {mode!r}")
         if device.type != "cuda":
             raise _lib.GanceError("GeneratorOnDevice needs a CUDA device: there is no CPU fallback")
+        if up_form not in (None, "folded", "phase", "fused"):
+            raise ValueError(f"up_form must be None, 'folded', 'phase' or 'fused', got {up_form!r}")
+        self.forced_up_form = up_form or ""
         self.spec = spec
         self.device = device
         self.mode = mode
@@ -143,6 +149,7 @@ class GeneratorOnDevice:
         self.noise_counter = torch.zeros(1, dtype=torch.int64, device=device)
         self._graphs: Dict[tuple, tuple] = {}
         self._renderers: Dict[tuple, "BatchRenderer"] = {}
+        self._contexts: Dict[int, "GeneratorOnDevice"] = {}
         self.launches_per_replay = 0
         self.graph_captures = 0  # how many CUDA graphs this generator has captured (tests: switching must not re-capture)
         self._upload(variables)
@@ -205,8 +212,7 @@ class GeneratorOnDevice:
 
         self._build_style_tables()
 
-    @staticmethod
-    def _up_form(conv) -> str:
+    def _up_form(self, conv) -> str:
         """
         Which kernel an up-convolution runs as (include/gance_b200.h):
           "fused"  - 4-phase GEMM with the FIR applied on chip (upconv_fused.cu): one launch, x read once, output written
@@ -216,9 +222,9 @@ class GeneratorOnDevice:
           "phase"  - 4-phase GEMM + separate FIR pass through a 16-bit scratch tensor (upconv_phase.cu).
           "folded" - one N = 4*Cout SAME convolution at the input resolution, 4x the algorithmic MACs: the small layers
                      (latency-bound) and 512->1024 (Cout = 32: the fused epilogue is issue-bound there, 1756 vs 1118 us).
-        GANCE_UP=folded|phase|fused forces a form where the shape is eligible (A/B measurements).
+        The constructor's `up_form` forces a form where the shape is eligible (A/B measurements).
         """
-        forced = os.environ.get("GANCE_UP", "")
+        forced = self.forced_up_form
         phase_ok = conv.in_resolution >= 32 and conv.in_channels % 64 == 0 and conv.out_channels % 64 == 0
         fused_ok = (conv.in_resolution >= 16 and conv.in_channels % 64 == 0
                     and (conv.out_channels % 64 == 0 or conv.out_channels == 32))
@@ -290,6 +296,32 @@ class GeneratorOnDevice:
         self._graphs.clear()  # captured graphs hold the work buffers' addresses
         self._renderers.clear()
         self._buffers.clear()
+        for context in self._contexts.values():
+            context.release_buffers()
+
+    def graph_capture_count(self) -> int:
+        """CUDA graphs captured by this generator and its contexts so far (tests: switching must not re-capture)."""
+        return self.graph_captures + sum(context.graph_capture_count() for context in self._contexts.values())
+
+    def context(self, index: int) -> "GeneratorOnDevice":
+        """
+        A view of this generator with its OWN work buffers, captured graphs and noise stream, sharing the resident
+        weights: batches rendered through different contexts do not touch each other's memory, so they can run
+        concurrently on different CUDA streams (the tail of one batch's kernels and its small latency-bound launches
+        overlap the next batch's). Context 0 is the generator itself.
+        """
+        if index == 0:
+            return self
+        found = self._contexts.get(index)
+        if found is None:
+            found = copy.copy(self)
+            found._buffers, found._graphs, found._renderers, found._contexts = {}, {}, {}, {}
+            found.profile_events = None
+            found.graph_captures, found.launches_per_replay = 0, 0
+            found.noise_counter = torch.zeros(1, dtype=torch.int64, device=self.device)
+            found.noise_seed = (self.noise_seed + index * 0x9E37_79B9_7F4A_7C15) & 0x7FFF_FFFF_FFFF_FFFF
+            self._contexts[index] = found
+        return found
 
     def renderer(self, max_batch: int = 32, truncation_psi: float = 1.2, output_side_length: Optional[int] = None,
                  noise_mode: Optional[str] = None) -> "BatchRenderer":
@@ -681,6 +713,9 @@ class BatchRenderer:
         self.noise_mode = noise_mode
         dev, res = generator.device, generator.resolution
         self.copy_stream = torch.cuda.Stream(device=dev)
+        # one generator context and one compute stream per slot: consecutive batches overlap on the device
+        self.contexts = [generator.context(slot) for slot in range(self.depth)]
+        self.streams = [torch.cuda.Stream(device=dev) for _ in range(self.depth)]
         self.frames_dev = [torch.empty((max_batch, res, res, 3), dtype=torch.uint8, device=dev) for _ in range(self.depth)]
         self.output_side = res if output_side_length is None else int(output_side_length)
         self.resizer = None
@@ -703,56 +738,66 @@ class BatchRenderer:
 
     def _compute(self, slot: int, latents, vector_noise_mode: str = "random"):
         """
-        H2D of one batch's latents, the generator pass and the optional resize, all on the current stream, into this
-        slot's device buffers. Returns (n, device frames [n,S,S,3]).
+        H2D of one batch's latents, the generator pass and the optional resize into this slot's device buffers, on this
+        slot's compute stream and generator context (so that consecutive batches overlap on the device). Returns
+        (n, device frames [n,S,S,3], event recorded when they are complete).
 
         (512,) / (N,512) are vectors, (N,rows,512) are matrices - the kind of a batch is its number of dimensions, never
         its length (a batch of exactly num_ws vectors is num_ws frames). A single (num_ws,512) matrix must arrive as
         (1,num_ws,512). `latents` may be a numpy array (staged through this slot's pinned buffer) or a CUDA tensor.
         """
-        gen = self.generator
+        gen = self.contexts[slot]
         on_gpu = isinstance(latents, torch.Tensor) and latents.is_cuda
-        array = latents.to(torch.float32) if on_gpu else np.asarray(latents, dtype=np.float32)
-        if array.ndim == 1:
-            array = array[None]
-        if array.ndim not in (2, 3) or array.shape[-1] != 512:
-            raise ValueError(f"a batch is (N,512) vectors or (N,rows,512) matrices, got shape {tuple(array.shape)}")
-        is_vectors = array.ndim == 2
-        n = array.shape[0]
+        shape = tuple(latents.shape)
+        if len(shape) == 1:
+            shape = (1,) + shape
+        if len(shape) not in (2, 3) or shape[-1] != 512:
+            raise ValueError(f"a batch is (N,512) vectors or (N,rows,512) matrices, got shape {tuple(latents.shape)}")
+        is_vectors = len(shape) == 2
+        n = shape[0]
         if n > self.max_batch:
             raise ValueError(f"batch of {n} exceeds max_batch {self.max_batch}")
-        if not is_vectors:
-            if array.shape[1] < gen.num_ws:
-                raise ValueError(f"latents have {array.shape[1]} rows, this network needs {gen.num_ws}")
-            array = array[:, : gen.num_ws]
-        stream = torch.cuda.current_stream(gen.device)
-        stream.wait_event(self.done[slot])  # the frames of the batch that last used this slot have left the device
-        if on_gpu:
-            on_device = array.contiguous()
-        else:
-            self.staged[slot].synchronize()  # host side: the H2D that last read this slot's staging buffer has run
-            staged = self.latents_host[slot][: array.size].view(array.shape)
-            staged.copy_(torch.from_numpy(np.ascontiguousarray(array)))
-            on_device = staged.to(gen.device, non_blocking=True)
-            self.staged[slot].record(stream)
-            self.bytes_h2d += array.size * 4
-        out = self.frames_dev[slot][:n]
-        # full batches and multiples of 8 replay a captured graph; the odd-sized groups a model-switching window leaves
-        # over run eagerly (same C-ABI calls), so a run never holds more than a handful of graphs per network
-        graphed = n == self.max_batch or n % 8 == 0
-        if is_vectors:
-            noise_mode = self.noise_mode or vector_noise_mode
-            if graphed:
-                gen.run_vectors_graphed(on_device, out, truncation_psi=self.truncation_psi, noise_mode=noise_mode)
+        if not is_vectors and shape[1] < gen.num_ws:
+            raise ValueError(f"latents have {shape[1]} rows, this network needs {gen.num_ws}")
+        stream = self.streams[slot]
+        stream.wait_stream(torch.cuda.current_stream(gen.device))  # device latents were produced on the caller's stream
+        with torch.cuda.stream(stream):
+            stream.wait_event(self.done[slot])  # the frames of the batch that last used this slot have left the device
+            if on_gpu:
+                latents.record_stream(stream)
+                on_device = latents.reshape(shape).to(torch.float32)
+                if not is_vectors:
+                    on_device = on_device[:, : gen.num_ws]
+                on_device = on_device.contiguous()
             else:
-                gen.run_vectors(on_device, truncation_psi=self.truncation_psi, noise_mode=noise_mode, out=out)
-        elif graphed:
-            gen.run_matrices_graphed(on_device, out, noise_mode=self.noise_mode or "const")
-        else:
-            gen.synthesis(on_device, noise_mode=self.noise_mode or "const", out=out)
-        if self.resizer is not None:
-            out = self.resizer.resize(out, self.output_side, self.output_side, out=self.scaled_dev[slot][:n])
-        return n, out
+                array = np.asarray(latents, dtype=np.float32).reshape(shape)
+                if not is_vectors:
+                    array = array[:, : gen.num_ws]
+                self.staged[slot].synchronize()  # host side: the H2D that last read this slot's staging buffer has run
+                staged = self.latents_host[slot][: array.size].view(array.shape)
+                staged.copy_(torch.from_numpy(np.ascontiguousarray(array)))
+                on_device = staged.to(gen.device, non_blocking=True)
+                self.staged[slot].record(stream)
+                self.bytes_h2d += array.size * 4
+            out = self.frames_dev[slot][:n]
+            # full batches and multiples of 8 replay a captured graph; the odd-sized groups a model-switching window
+            # leaves over run eagerly (same C-ABI calls), so a run never holds more than a handful of graphs per network
+            graphed = n == self.max_batch or n % 8 == 0
+            if is_vectors:
+                noise_mode = self.noise_mode or vector_noise_mode
+                if graphed:
+                    gen.run_vectors_graphed(on_device, out, truncation_psi=self.truncation_psi, noise_mode=noise_mode)
+                else:
+                    gen.run_vectors(on_device, truncation_psi=self.truncation_psi, noise_mode=noise_mode, out=out)
+            elif graphed:
+                gen.run_matrices_graphed(on_device, out, noise_mode=self.noise_mode or "const")
+            else:
+                gen.synthesis(on_device, noise_mode=self.noise_mode or "const", out=out)
+            if self.resizer is not None:
+                out = self.resizer.resize(out, self.output_side, self.output_side, out=self.scaled_dev[slot][:n])
+            computed = torch.cuda.Event()
+            computed.record(stream)
+        return n, out, computed
 
     def _submit(self, slot: int, latents, vector_noise_mode: str = "random") -> int:
         """One batch through `_compute`, then its frames to this slot's pinned host buffer on the copy stream."""
@@ -761,9 +806,7 @@ class BatchRenderer:
             side = self.output_side
             self.frames_host = [torch.empty((self.max_batch, side, side, 3), dtype=torch.uint8).pin_memory()
                                 for _ in range(self.depth)]
-        n, out = self._compute(slot, latents, vector_noise_mode)
-        computed = torch.cuda.Event()
-        computed.record(torch.cuda.current_stream(gen.device))
+        n, out, computed = self._compute(slot, latents, vector_noise_mode)
         self.copy_stream.wait_event(computed)
         with torch.cuda.stream(self.copy_stream):
             self.frames_host[slot][:n].copy_(out, non_blocking=True)
@@ -786,15 +829,13 @@ class BatchRenderer:
         indices = np.asarray(dest_indices, dtype=np.int64).reshape(-1)
         slot = self._next_slot
         self._next_slot = (slot + 1) % self.depth
-        n, out = self._compute(slot, latents, vector_noise_mode)
+        n, out, computed = self._compute(slot, latents, vector_noise_mode)
         if len(indices) != n:
             raise ValueError(f"{n} latents but {len(indices)} destination indices")
         if tuple(dest.shape[1:]) != tuple(out.shape[1:]) or dest.dtype != torch.uint8:
             raise ValueError(f"dest must be uint8 [T,{out.shape[1]},{out.shape[2]},3], got {tuple(dest.shape)} {dest.dtype}")
         if n and (int(indices.min()) < 0 or int(indices.max()) >= dest.shape[0]):
             raise IndexError("destination index outside dest")
-        computed = torch.cuda.Event()
-        computed.record(torch.cuda.current_stream(gen.device))
         self.copy_stream.wait_event(computed)
         arrived = torch.cuda.Event()
         with torch.cuda.stream(self.copy_stream):

@@ -186,7 +186,7 @@ def test_eight_bit_pcm_reference_errors(tmp_path):
     """The reference's own `read_wav_file` on the same arrays (scipy's reader patched to hand them over)."""
     from unittest import mock
 
-    reference_music = reference_shim.load().music
+    reference_music = reference_shim.load()["music"]
     with mock.patch.object(reference_music.wavfile, "read", return_value=(44100, np.array([0, 64, 127], dtype=np.int8))):
         got = reference_music.read_wav_file(tmp_path / "x.wav").wav_data
     np.testing.assert_array_equal(got, audio_ref.wav_to_float32(np.array([0, 64, 127], dtype=np.int8)))
