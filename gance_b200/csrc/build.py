@@ -13,8 +13,14 @@ from typing import List
 
 CSRC = Path(__file__).resolve().parent
 SOURCES = ["runtime.cu", "synthesis_kernels.cu", "modconv_tc.cu", "modconv_tf32.cu", "upconv_phase.cu", "upconv_fused.cu", "audio_kernels.cu", "resize_kernels.cu"]
-LIBRARY = CSRC / "libgance_b200.so"
-STAMP = CSRC / "libgance_b200.stamp"
+# Measurement builds, never the product: GANCE_PIPE_STATS=1 -> libgance_b200_stats.so (cycle counters per warp role,
+# tools/pipe_stats.py); GANCE_VARIANT=name:MACRO[,MACRO...] -> libgance_b200_<name>.so with -DMACRO... (ablations of the
+# epilogues, tools/ablate.sh).
+PIPE_STATS = os.environ.get("GANCE_PIPE_STATS") == "1"
+VARIANT, _, VARIANT_MACROS = os.environ.get("GANCE_VARIANT", "").partition(":")
+SUFFIX = "_stats" if PIPE_STATS else (f"_{VARIANT}" if VARIANT else "")
+LIBRARY = CSRC / f"libgance_b200{SUFFIX}.so"
+STAMP = CSRC / f"libgance_b200{SUFFIX}.stamp"
 
 NVCC_FLAGS = [
     "-gencode",
@@ -24,7 +30,7 @@ NVCC_FLAGS = [
     "-lineinfo",
     "-Xcompiler",
     "-fPIC",
-]
+] + (["-DGANCE_PIPE_STATS"] if PIPE_STATS else []) + [f"-D{macro}" for macro in VARIANT_MACROS.split(",") if macro]
 
 
 def _nvcc() -> str:
@@ -56,7 +62,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
         return LIBRARY
     nvcc = _nvcc()
     objects = []
-    build_dir = CSRC / "build"
+    build_dir = CSRC / f"build{SUFFIX}"
     build_dir.mkdir(exist_ok=True)
     procs = []
     for source in _existing_sources():

@@ -46,13 +46,9 @@ struct TileCoord {
     int n0, b0, h0, w0;
 };
 
-__device__ __forceinline__ TileCoord decode_tile(const ConvParams& p, int tile, int n_tile_size) {
+// m-tile index -> (sample, first row, first column) of the tile
+__device__ __forceinline__ TileCoord decode_m_tile(const ConvParams& p, int m, int nt, int n_tile_size) {
     TileCoord t;
-    int nt = 0, m = tile;
-    if (p.n_tiles != 1) {
-        nt = tile % p.n_tiles;
-        m = tile / p.n_tiles;
-    }
     int tw, th;
     if (p.tiles_w_log2 >= 0) {  // every 2^k-sized image: three runtime divisions (~60 instructions per warp and tile) become shifts
         tw = m & (p.tiles_w - 1);
@@ -69,6 +65,29 @@ __device__ __forceinline__ TileCoord decode_tile(const ConvParams& p, int tile, 
     t.w0 = tw << p.tile_w_log2;
     t.h0 = th * p.tile_h;
     return t;
+}
+
+__device__ __forceinline__ TileCoord decode_tile(const ConvParams& p, int tile, int n_tile_size) {
+    int nt = 0, m = tile;
+    if (p.n_tiles != 1) {
+        nt = tile % p.n_tiles;
+        m = tile / p.n_tiles;
+    }
+    return decode_m_tile(p, m, nt, n_tile_size);
+}
+
+// CTA-pair kernels: work item = (pair of consecutive m-tiles, n-tile); CTA `rank` of the pair owns m-tile 2 * pair + rank.
+// With an odd number of m-tiles the last pair's second tile is a GHOST: its sample index is the batch size, so the TMA
+// unit zero-fills its A operand (the byte counts of the pipeline stay the same) and the epilogue stores nothing.
+__device__ __forceinline__ TileCoord decode_pair_item(const ConvParams& p, int item, int rank, int n_tile_size, bool& ghost) {
+    int nt = 0, mp = item;
+    if (p.n_tiles != 1) {
+        nt = item % p.n_tiles;
+        mp = item / p.n_tiles;
+    }
+    const int m = 2 * mp + rank;
+    ghost = m >= p.tiles_b * p.tiles_h * p.tiles_w;
+    return decode_m_tile(p, m, nt, n_tile_size);
 }
 
 // Epilogue shared by both kernels. Two groups of four warps; group g drains TMEM accumulator buffer g, i.e. the
@@ -90,10 +109,19 @@ __device__ __forceinline__ void epilogue_bar_sync(int group) {
     asm volatile("bar.sync %0, 128;" ::"r"(group + 1) : "memory");
 }
 
-template <typename T, int N_TILE, bool UP, bool RGB, int GROUPS, int CACHE_F4>
+// APG = TMEM accumulator buffers per epilogue group (1 or 2). The n-th tile of group g lives in buffer g + GROUPS * (n % APG).
+// With one buffer per group the MMAs of tile i + GROUPS cannot start before the epilogue of tile i has drained its
+// buffer: a tile's epilogue latency must fit inside (GROUPS - 1) tiles of MMA time. With two, only its THROUGHPUT has to.
+template <typename T, int N_TILE, bool UP, bool RGB, int GROUPS, int CACHE_F4, bool PAIR = false, int APG = 1>
 __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int group, int warp, int lane, int total_tiles,
                                               uint32_t tmem_base, uint64_t* tmem_full_bar, uint64_t* tmem_empty_bar,
                                               float4* cache_all) {
+    // PAIR: `total_tiles` counts pair items, walked cluster by cluster; the drained accumulator is reported to the
+    // LEADER's barrier (the leader's MMA warp issues for both CTAs)
+    const int pair_rank = PAIR ? (int)cluster_ctarank() : 0;
+    const int walk_first = PAIR ? (int)cluster_id_x() : (int)blockIdx.x;
+    const int walk_stride = PAIR ? (int)cluster_count_x() : (int)gridDim.x;
+    const uint32_t leader_empty_base = PAIR ? cluster_map(smem_u32(tmem_empty_bar), 0) : 0u;
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
     const int wl = row & (p.tile_w - 1);
@@ -105,13 +133,24 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int group, in
     const uint32_t coef_a_addr = smem_u32(coef_a);
     const int tid = quarter * 32 + lane;
     int cached_b = -1;
-    uint32_t full_phase = 0;
+    int visit = 0;  // tiles this group has handled
     float3 rgb_bias = make_float3(0.f, 0.f, 0.f);
     if (RGB) rgb_bias = make_float3(__ldg(p.rgb_bias), __ldg(p.rgb_bias + 1), __ldg(p.rgb_bias + 2));
-    const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(group * N_TILE);
 
-    for (int tile = blockIdx.x + group * gridDim.x; tile < total_tiles; tile += GROUPS * gridDim.x) {
-        const TileCoord t = decode_tile(p, tile, N_TILE);
+    for (int tile = walk_first + group * walk_stride; tile < total_tiles; tile += GROUPS * walk_stride, ++visit) {
+        const int acc = group + GROUPS * (visit % APG);
+        const uint32_t full_phase = (uint32_t)(visit / APG) & 1u;
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * N_TILE);
+        bool ghost = false;
+        const TileCoord t = PAIR ? decode_pair_item(p, tile, pair_rank, N_TILE, ghost) : decode_tile(p, tile, N_TILE);
+        if (PAIR && ghost) {  // CTA-uniform: keep the accumulator hand-shake going, touch nothing else
+            mbar_wait(tmem_full_bar + acc, full_phase);
+            tcgen05_fence_after();
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(leader_empty_base + (uint32_t)(acc * 8));
+            continue;
+        }
         const int b = t.b0, h = t.h0 + hl, w = t.w0 + wl;
         const bool valid = hl < p.tile_h && h < p.h_out && w < p.w_out;
         const int hv = valid ? h : 0, wv = valid ? w : 0;
@@ -147,8 +186,7 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int group, in
         }
         float red = 0.f, green = 0.f, blue = 0.f;
 
-        mbar_wait(tmem_full_bar + group, full_phase);
-        full_phase ^= 1u;
+        mbar_wait(tmem_full_bar + acc, full_phase);
         tcgen05_fence_after();
 #pragma unroll 1
         for (int c0 = 0; c0 < N_TILE; c0 += 32) {
@@ -198,7 +236,10 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int group, in
         }
         tcgen05_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(tmem_empty_bar + group);  // accumulator drained: the MMAs of tile+2 may start
+        if (lane == 0) {  // accumulator drained: the MMAs of the tile that takes this buffer next may start
+            if (PAIR) mbar_arrive_cluster(leader_empty_base + (uint32_t)(acc * 8));
+            else mbar_arrive(tmem_empty_bar + acc);
+        }
         if (RGB && valid) {
             red += rgb_bias.x + skip.x; green += rgb_bias.y + skip.y; blue += rgb_bias.z + skip.z;
             const size_t pixel = ((size_t)b * p.h_out + hv) * p.w_out + wv;
@@ -212,11 +253,13 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int group, in
     }
 }
 
-__device__ __forceinline__ void store_pair(__half* dst, float a, float b) {
-    *reinterpret_cast<__half2*>(dst) = __floats2half2_rn(a, b);
+__device__ __forceinline__ uint32_t pack_pair(float a, float b, __half*) {
+    const __half2 h = __floats2half2_rn(a, b);
+    return *reinterpret_cast<const uint32_t*>(&h);
 }
-__device__ __forceinline__ void store_pair(__nv_bfloat16* dst, float a, float b) {
-    *reinterpret_cast<__nv_bfloat162*>(dst) = __floats2bfloat162_rn(a, b);
+__device__ __forceinline__ uint32_t pack_pair(float a, float b, __nv_bfloat16*) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<const uint32_t*>(&h);
 }
 
 // ---- epilogue of the halo kernels: accumulators read in the mma-fragment layout ------------------------------------
@@ -230,10 +273,20 @@ __device__ __forceinline__ void store_pair(__nv_bfloat16* dst, float a, float b)
 //   channels 32*chunk + 8*j + 2*(t%4) + e    (j in 0..3, e in {0,1})
 // The ToRGB sum over channels is finished with a two-step reduce-scatter over the four lanes that share a row
 // (9 shuffles), which leaves row rr on lane t%4 == rr: every lane then adds the skip connection for ONE pixel.
-template <typename T, int N_TILE, int C, bool UP, bool RGB, int GROUPS, int TILE_W_LOG2 = -1>
+template <typename T, int N_TILE, int C, bool UP, bool RGB, int GROUPS, int TILE_W_LOG2 = -1, bool PAIR = false, int APG = 1>
 __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int group, int warp, int lane, int total_tiles,
                                                    uint32_t tmem_base, uint64_t* tmem_full_bar,
                                                    uint64_t* tmem_empty_bar) {
+    // PAIR: `total_tiles` counts pair items (the host guarantees an even m-tile count: no ghost tiles here), walked
+    // cluster by cluster; the drained accumulator is reported to the leader's barrier
+    const int pair_rank = PAIR ? (int)cluster_ctarank() : 0;
+    const int walk_first = PAIR ? (int)cluster_id_x() : (int)blockIdx.x;
+    const int walk_stride = PAIR ? (int)cluster_count_x() : (int)gridDim.x;
+    const uint32_t leader_empty_base = PAIR ? cluster_map(smem_u32(tmem_empty_bar), 0) : 0u;
+    auto decode = [&](int tile) {
+        bool ghost;
+        return PAIR ? decode_pair_item(p, tile, pair_rank, N_TILE, ghost) : decode_tile(p, tile, N_TILE);
+    };
     static_assert(C % 32 == 0 && C <= 64, "register-resident coefficients: at most 16 channels per thread");
     static_assert(N_TILE == (UP ? 4 * C : C), "GEMM columns = channels (x 4 phases for the folded up-convolution)");
     constexpr int CPT = C / 4;           // channels per thread
@@ -241,7 +294,11 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
     const int quarter = warp & 3;
     const int q4 = lane & 3, r8 = lane >> 2;
     const int out_w = UP ? 2 * p.w_out : p.w_out, out_h = UP ? 2 * p.h_out : p.h_out;
+#ifdef GANCE_ABL_NOSTORE
+    const bool has_out = p.out != nullptr && p.batch < 0;  // ablation: no activation stores
+#else
     const bool has_out = p.out != nullptr;
+#endif
 
     float cd[CPT], cb[CPT], cs[CPT], cw0[CPT], cw1[CPT], cw2[CPT];
     float3 rgb_bias = make_float3(0.f, 0.f, 0.f);
@@ -260,7 +317,7 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
         }
     }
     int cached_b = -1;
-    uint32_t full_phase = 0;
+    int visit = 0;  // tiles this group has handled (accumulator buffer and barrier parity follow from it, see conv_epilogue)
 
     // Noise and skip-connection values of a tile do not depend on its accumulator: they are requested one tile AHEAD
     // (while the current tile is being computed) so their global-memory latency never sits on the tile's critical path.
@@ -276,7 +333,21 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
     };
     auto request = [&](int tile) {
         Ahead n;
-        n.t = decode_tile(p, tile, N_TILE);
+        n.t = decode(tile);
+#ifdef GANCE_ABL_NOLOADS
+        if (p.batch > 0) {  // ablation: no noise / skip fetches
+#pragma unroll
+            for (int rr = 0; rr < 4; ++rr)
+#pragma unroll
+                for (int ph = 0; ph < NP; ++ph) n.nz[rr][ph] = 0.f;
+            n.p00 = n.p01 = n.p10 = n.p11 = make_float4(0.f, 0.f, 0.f, 0.f);
+            n.w01 = n.w10 = n.w11 = 0.f;
+            n.skip = make_float3(0.f, 0.f, 0.f);
+            n.own_h = n.t.h0 + (q4 == 0 ? hl[0] : q4 == 1 ? hl[1] : q4 == 2 ? hl[2] : hl[3]);
+            n.own_w = n.t.w0 + (q4 == 0 ? wl[0] : q4 == 1 ? wl[1] : q4 == 2 ? wl[2] : wl[3]);
+            return n;
+        }
+#endif
         const float* noise_b = p.noise ? p.noise + (size_t)n.t.b0 * p.noise_batch_stride : nullptr;
 #pragma unroll
         for (int rr = 0; rr < 4; ++rr) {
@@ -289,7 +360,10 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
                 }
                 n.nz[rr][0] = top.x; n.nz[rr][1 % NP] = top.y; n.nz[rr][2 % NP] = bot.x; n.nz[rr][3 % NP] = bot.y;
             } else {
-                n.nz[rr][0] = noise_b ? __ldg(noise_b + (size_t)h * out_w + w) : 0.f;
+                // unconditional load from a valid address (the bias vector when there is no noise, multiplied by a zero
+                // strength below): `noise_b ? __ldg(..) : 0` became LDG + FSEL, and the select waited out the whole fetch
+                // latency right here instead of one tile later (ncu, round 2: 23 % of this kernel's stall samples)
+                n.nz[rr][0] = __ldg(noise_b ? noise_b + (size_t)h * out_w + w : p.bias);
             }
         }
         n.p00 = n.p01 = n.p10 = n.p11 = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -331,7 +405,7 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
     // only PREFETCHES the next tile's operands into L2 and loads them at the top of its own iteration, where the L2-hit
     // latency hides behind the wait for the accumulator.
     auto prefetch = [&](int next) {
-        const TileCoord n = decode_tile(p, next, N_TILE);
+        const TileCoord n = decode(next);
         if (p.noise != nullptr) {
             const float* noise_b = p.noise + (size_t)n.b0 * p.noise_batch_stride;
 #pragma unroll
@@ -354,19 +428,25 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
         }
     };
 
-    int tile = blockIdx.x + group * gridDim.x;
+#ifdef GANCE_PIPE_STATS
+    long long stat_wait = 0;
+    const long long stat_begin = clock64();
+#endif
+    int tile = walk_first + group * walk_stride;
     Ahead ahead;
     if (kAheadInRegisters && tile < total_tiles) ahead = request(tile);
-    for (; tile < total_tiles; tile += GROUPS * gridDim.x) {
-        const bool more = tile + GROUPS * (int)gridDim.x < total_tiles;
+    for (; tile < total_tiles; tile += GROUPS * walk_stride, ++visit) {
+        const int acc = group + GROUPS * (visit % APG);
+        const uint32_t full_phase = (uint32_t)(visit / APG) & 1u;
+        const bool more = tile + GROUPS * walk_stride < total_tiles;
         if (!kAheadInRegisters) {
             ahead = request(tile);
-            if (more) prefetch(tile + GROUPS * gridDim.x);
+            if (more) prefetch(tile + GROUPS * walk_stride);
         }
         const Ahead cur = ahead;
         const TileCoord t = cur.t;
         const int b = t.b0;
-        if (kAheadInRegisters && more) ahead = request(tile + GROUPS * gridDim.x);
+        if (kAheadInRegisters && more) ahead = request(tile + GROUPS * walk_stride);
         if (b != cached_b) {  // per-sample coefficients of this thread's channels -> registers
 #pragma unroll
             for (int k = 0; k < CPT; ++k) {
@@ -388,15 +468,31 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
 #pragma unroll
         for (int rr = 0; rr < 4; ++rr)
 #pragma unroll
-            for (int ph = 0; ph < NP; ++ph) nz[rr][ph] = cur.nz[rr][ph] * p.noise_strength;
+            for (int ph = 0; ph < NP; ++ph) nz[rr][ph] = cur.nz[rr][ph] * (p.noise ? p.noise_strength : 0.f);
         const int own_h = cur.own_h, own_wp = cur.own_w;
         float rgb[4][3];
 #pragma unroll
         for (int rr = 0; rr < 4; ++rr) rgb[rr][0] = rgb[rr][1] = rgb[rr][2] = 0.f;
 
-        mbar_wait(tmem_full_bar + group, full_phase);
-        full_phase ^= 1u;
+#ifdef GANCE_PIPE_STATS
+        const long long stat_w0 = clock64();
+#endif
+        mbar_wait(tmem_full_bar + acc, full_phase);
+#ifdef GANCE_PIPE_STATS
+        stat_wait += clock64() - stat_w0;
+#endif
         tcgen05_fence_after();
+#ifdef GANCE_ABL_NOEPI
+        if (p.batch > 0) {  // ablation: the epilogue only hands the accumulator back
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                if (PAIR) mbar_arrive_cluster(leader_empty_base + (uint32_t)(acc * 8));
+                else mbar_arrive(tmem_empty_bar + acc);
+            }
+            continue;
+        }
+#endif
 #pragma unroll
         for (int chunk = 0; chunk < CHUNKS; ++chunk) {
             const int phase = UP ? (chunk * 32) / C : 0;
@@ -405,7 +501,7 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
             for (int h2 = 0; h2 < 2; ++h2) {
                 uint32_t r[16];
                 tmem_ld_16x256b_x4(tmem_base + ((uint32_t)(quarter * 32 + 16 * h2) << 16) +
-                                       (uint32_t)(group * N_TILE + chunk * 32), r);
+                                       (uint32_t)(acc * N_TILE + chunk * 32), r);
                 tmem_ld_wait();
 #pragma unroll
                 for (int s = 0; s < 2; ++s) {
@@ -430,17 +526,33 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
                     if (has_out) {
                         const int h = t.h0 + hl[rr], w = t.w0 + wl[rr];
                         const int oh = UP ? 2 * h + (phase >> 1) : h, ow = UP ? 2 * w + (phase & 1) : w;
+                        // The fragment layout leaves a lane with one channel PAIR (4 bytes) of each of four 8-channel groups.
+                        // Stored as they are, a warp store covers 16 bytes in each of 8 pixels - half a 32-byte sector at a
+                        // time, and the L1 store path handles one sector per clock whether it is full or not (ablation,
+                        // round 2: the 4-byte stores were 0.49 of the 1.12 ms of the 1024^2 up-convolution). Lane pairs
+                        // swap one word so that the even lane holds 8 contiguous bytes of group j, the odd lane of
+                        // group j + 1: every store instruction then writes whole sectors.
+                        const bool odd = (q4 & 1) != 0;
                         T* dst = reinterpret_cast<T*>(p.out) + (((size_t)b * out_h + oh) * out_w + ow) * C +
-                                 ((chunk * 32) % C) + 2 * q4;
+                                 ((chunk * 32) % C) + 2 * (q4 & 2);
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) store_pair(dst + 8 * j, v[2 * j], v[2 * j + 1]);
+                        for (int j = 0; j < 4; j += 2) {
+                            const uint32_t w0 = pack_pair(v[2 * j], v[2 * j + 1], (T*)nullptr);
+                            const uint32_t w1 = pack_pair(v[2 * j + 2], v[2 * j + 3], (T*)nullptr);
+                            const uint32_t got = __shfl_xor_sync(0xffffffffu, odd ? w0 : w1, 1);
+                            const uint2 both = odd ? make_uint2(got, w1) : make_uint2(w0, got);
+                            *reinterpret_cast<uint2*>(dst + 8 * (j + (odd ? 1 : 0))) = both;
+                        }
                     }
                 }
             }
         }
         tcgen05_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(tmem_empty_bar + group);  // accumulator drained
+        if (lane == 0) {  // accumulator drained
+            if (PAIR) mbar_arrive_cluster(leader_empty_base + (uint32_t)(acc * 8));
+            else mbar_arrive(tmem_empty_bar + acc);
+        }
         if (RGB) {
             // reduce-scatter over the 4 lanes of a row group: xor 1 settles s, xor 2 settles h2
             float keep[2][3], mine[3];
@@ -469,13 +581,23 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
             }
             const size_t pixel = ((size_t)b * p.h_out + own_h) * p.w_out + own_wp;
             if (p.y_out != nullptr) reinterpret_cast<float4*>(p.y_out)[pixel] = make_float4(red, green, blue, 0.f);
+#ifdef GANCE_ABL_NOFRAMES
+            if (p.frames != nullptr && red == 12345.678f) {  // ablation: (practically) no frame stores
+#else
             if (p.frames != nullptr) {
+#endif
                 uint8_t* f = p.frames + pixel * 3;
                 f[0] = to_u8(red); f[1] = to_u8(green); f[2] = to_u8(blue);
                 flag_nonfinite(p.nonfinite, red, green, blue);
             }
         }
     }
+#ifdef GANCE_PIPE_STATS
+    if (!PAIR && p.pipe_stats != nullptr && (warp & 3) == 0 && lane == 0 && group < 2) {
+        p.pipe_stats[blockIdx.x * 8 + 5 + group] = stat_wait;  // epilogue group: waiting for a finished accumulator
+        if (group == 0) p.pipe_stats[blockIdx.x * 8 + 7] = clock64() - stat_begin;  // ... whole epilogue loop
+    }
+#endif
 }
 
 template <typename T, int N_TILE, int BLOCK_K, int STAGES, bool UP, bool RGB>
@@ -605,6 +727,155 @@ modconv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
     }
 }
 
+// ---- CTA-pair flavour of the kernel above (cta_group::2) -----------------------------------------------------------------
+// At N = 128 one 128 x N x 16 MMA reads 4 KB of A + 4 KB of B from shared memory (64 clk at 128 B/clk) for 64 clk of math:
+// the operand port ties with the tensor pipe and neither is ever saturated (ncu, round 2: tensor pipe 54 % at N = 128,
+// 76 % at N = 256). Two CTAs on the two SMs of a TPC share ONE M = 256 MMA: each supplies its own 128 pixels of A and
+// HALF of the weight tile, so every SM reads A + B/2 (48 clk at N = 128) and fetches half the weight bytes through L2.
+// Same roles as above in both CTAs; the leader's (rank 0) MMA warp issues for the pair, the peer's MMA warp only owns its
+// CTA's TMEM allocation. Barriers: full[] lives in the leader (both CTAs' TMA bytes are counted there), empty[] and
+// tmem_full[] are signalled in both CTAs by multicast commits, tmem_empty[] lives in the leader and collects the
+// epilogue warps of both CTAs.
+template <int N_TILE, int BLOCK_K, int STAGES>
+struct PairSmemLayout {
+    static constexpr int kABytes = kTileM * BLOCK_K * 2;
+    static constexpr int kBBytes = (N_TILE / 2) * BLOCK_K * 2;  // this CTA's half of the weight tile
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kBarrierOffset = STAGES * kStageBytes;
+    static constexpr int kCacheOffset = kBarrierOffset + (2 * STAGES + 4) * 8 + 16;
+    static constexpr int kBytes = kCacheOffset + kCacheBytes + 1024;
+};
+
+template <typename T, int N_TILE, int BLOCK_K, int STAGES, bool RGB>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+modconv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
+                       const ConvParams p) {
+    using L = PairSmemLayout<N_TILE, BLOCK_K, STAGES>;
+    constexpr int kSwizzle = BLOCK_K * 2;
+    constexpr uint32_t kTmemCols = 2 * N_TILE;
+    static_assert((kTmemCols & (kTmemCols - 1)) == 0 && kTmemCols <= 512 && kTmemCols >= 32, "TMEM columns must be a power of two");
+    static_assert(L::kABytes % 1024 == 0 && L::kBBytes % 1024 == 0, "stage buffers must stay 1024-byte aligned");
+    static_assert(N_TILE % 32 == 0 && N_TILE <= 256, "cta_group::2: N in steps of 16 up to 256");
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarrierOffset);
+    uint64_t* empty_bar = full_bar + STAGES;
+    uint64_t* tmem_full_bar = empty_bar + STAGES;
+    uint64_t* tmem_empty_bar = tmem_full_bar + 2;
+    uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
+    const int lane = threadIdx.x & 31;
+    const int rank = (int)cluster_ctarank();
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmap_x);
+        prefetch_tmap(&tmap_w);
+        for (int i = 0; i < STAGES; ++i) {
+            mbar_init(full_bar + i, 1);   // the leader's expect_tx arrival; the bytes of both CTAs
+            mbar_init(empty_bar + i, 1);  // one multicast commit
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(tmem_full_bar + i, 1);
+            mbar_init(tmem_empty_bar + i, 8);  // four epilogue warps of each CTA (used in the leader only)
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc_pair(tmem_base_slot, kTmemCols);
+    tcgen05_fence_before();
+    cluster_sync_all();  // barriers of BOTH CTAs are initialised before any remote arrival or TMA byte count
+    tcgen05_fence_after();
+    const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_base_slot, 0);
+
+    const int m_tiles = p.tiles_b * p.tiles_h * p.tiles_w;
+    const int total_items = ((m_tiles + 1) >> 1) * p.n_tiles;
+    const int k_iters = 9 * p.k_chunks;
+    const int first_item = (int)cluster_id_x(), item_stride = (int)cluster_count_x();
+
+    if (warp == 0) {
+        // ===== TMA producer (both CTAs): own A tile + own half of the weight tile, bytes counted on the leader's barrier =====
+        const bool leader_lane = elect_one_sync();
+        int stage = 0;
+        uint32_t phase = 0;
+        const uint32_t full_leader = cluster_map(smem_u32(full_bar), 0);
+        for (int item = first_item; item < total_items; item += item_stride) {
+            bool ghost;
+            const TileCoord t = decode_pair_item(p, item, rank, N_TILE, ghost);
+            for (int tap = 0; tap < 9; ++tap) {
+                const int dy = tap / 3 - p.pad, dx = tap % 3 - p.pad;
+                for (int kc = 0; kc < p.k_chunks; ++kc) {
+                    mbar_wait(empty_bar + stage, phase ^ 1u);
+                    uint8_t* a_dst = smem + stage * L::kStageBytes;
+                    uint8_t* b_dst = a_dst + L::kABytes;
+                    if (leader_lane) {
+                        if (rank == 0) mbar_expect_tx(full_bar + stage, 2u * ((uint32_t)p.a_tx_bytes + L::kBBytes));
+                        const uint32_t bar = full_leader + (uint32_t)(stage * 8);
+                        tma_load_4d_pair(a_dst, &tmap_x, bar, kc * BLOCK_K, t.w0 + dx, t.h0 + dy, t.b0);
+                        tma_load_2d_pair(b_dst, &tmap_w, bar, tap * p.c_in + kc * BLOCK_K, t.n0 + rank * (N_TILE / 2));
+                    }
+                    __syncwarp();
+                    if (++stage == STAGES) {
+                        stage = 0;
+                        phase ^= 1u;
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (rank == 0) {
+            // ===== MMA issuer (leader CTA only) =====
+            const bool leader_lane = elect_one_sync();
+            constexpr uint32_t idesc = make_instr_desc(2 * kTileM, N_TILE, sizeof(T) == 2 && !std::is_same<T, __nv_bfloat16>::value);
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            const uint32_t smem_base = smem_u32(smem);
+            for (int item = first_item; item < total_items; item += item_stride) {
+                mbar_wait(tmem_empty_bar + acc, acc_phase ^ 1u);  // both CTAs' epilogues have drained this accumulator
+                tcgen05_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * N_TILE);
+                for (int it = 0; it < k_iters; ++it) {
+                    mbar_wait(full_bar + stage, phase);  // the TMA bytes of both CTAs have landed
+                    tcgen05_fence_after();
+                    const uint32_t a_addr = smem_base + (uint32_t)(stage * L::kStageBytes);
+                    const uint64_t a_desc = make_smem_desc<kSwizzle>(a_addr);
+                    const uint64_t b_desc = a_desc + (uint64_t)(L::kABytes >> 4);
+                    if (leader_lane) {
+#pragma unroll
+                        for (int k = 0; k < BLOCK_K / kUmmaK; ++k)
+                            umma_bf16_pair(d_tmem, a_desc + (uint64_t)(k * 2), b_desc + (uint64_t)(k * 2), idesc,
+                                           (it | k) != 0 ? 1u : 0u);
+                        umma_commit_pair(empty_bar + stage);  // frees this stage in both CTAs
+                        if (it == k_iters - 1) umma_commit_pair(tmem_full_bar + acc);
+                    }
+                    __syncwarp();
+                    if (++stage == STAGES) {
+                        stage = 0;
+                        phase ^= 1u;
+                    }
+                }
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1u;
+            }
+        }
+    } else {
+        conv_epilogue<T, N_TILE, false, RGB, kEpilogueGroups, kCacheFloat4PerGroup, true>(
+            p, (warp - 2) >> 2, warp, lane, total_items, tmem_base, tmem_full_bar, tmem_empty_bar,
+            reinterpret_cast<float4*>(smem + L::kCacheOffset));
+    }
+
+    // Neither CTA may leave (or free its TMEM) while its partner can still read its shared memory, write its TMEM or
+    // signal its barriers.
+    tcgen05_fence_before();
+    cluster_sync_all();
+    if (warp == 1) {
+        tcgen05_fence_after();
+        tmem_dealloc_pair(tmem_base, kTmemCols);
+    }
+}
+
 // ====================================================================================================
 // Halo variant for the narrow layers (Cin = 32 or 64, SAME padding): the layers of 512^2 and 1024^2.
 //
@@ -623,8 +894,15 @@ constexpr int kHaloTileW = 8, kHaloTileH = 16;
 constexpr int kHaloW = kHaloTileW + 2, kHaloH = kHaloTileH + 2;
 // A tile of these layers is 18-36 tensor-core instructions: four epilogue groups (= four TMEM accumulator buffers,
 // four tiles in flight) hide the global-memory latency of the noise / skip-connection fetches behind one another.
-__host__ __device__ constexpr int halo_groups(int n_gemm) { return n_gemm == 32 ? 3 : 2; }  // bounded by registers (65536 / threads)
+// Measured with cycle counters in the warp roles (tools/pipe_stats.py, round 2): in all three instances the epilogue
+// groups are busy > 90 % of the time while the MMA issuer waits 20-25 % for a drained accumulator - the epilogue warps are
+// latency-bound (one instruction every ~5 cycles per warp), so the remedy is more of them where registers allow:
+// the folded up-convolution (N = 128, 112 registers) runs four groups; the fused-ToRGB flavours need 128-168 registers.
+__host__ __device__ constexpr int halo_groups(int n_gemm) { return n_gemm == 128 ? 4 : (n_gemm == 32 ? 3 : 2); }  // bounded by registers (65536 / threads)
 __host__ __device__ constexpr int halo_threads(int n_gemm) { return 64 + halo_groups(n_gemm) * kEpilogueThreads; }
+constexpr int kHaloApg = 2;  // TMEM accumulator buffers per epilogue group (see conv_epilogue); 1 where 512 columns are full
+__host__ __device__ constexpr int halo_apg(int n_gemm) { return n_gemm == 128 ? 1 : kHaloApg; }
+__host__ __device__ constexpr int halo_accs(int n_gemm) { return halo_apg(n_gemm) * halo_groups(n_gemm); }
 
 template <int N_GEMM, int CIN, int STAGES>
 struct HaloSmem {
@@ -633,7 +911,7 @@ struct HaloSmem {
     static constexpr int kHaloBytes = kHaloH * kHaloW * kRowBytes;
     static constexpr int kHaloStride = (kHaloBytes + 1023) / 1024 * 1024;
     static constexpr int kBarrierOffset = kWeightBytes + STAGES * kHaloStride;
-    static constexpr int kCacheOffset = kBarrierOffset + ((2 * STAGES + 2 * halo_groups(N_GEMM) + 1) * 8 + 16 + 15) / 16 * 16;
+    static constexpr int kCacheOffset = kBarrierOffset + ((2 * STAGES + 2 * halo_accs(N_GEMM) + 1) * 8 + 16 + 15) / 16 * 16;
     static constexpr int kBytes = kCacheOffset + 1024;
 };
 
@@ -651,7 +929,9 @@ modconv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_
     using L = HaloSmem<N_GEMM, CIN, STAGES>;
     constexpr int kSwizzle = CIN * 2;  // 128 or 64 bytes per pixel row
     constexpr int kHaloGroups = halo_groups(N_GEMM);
-    constexpr uint32_t kTmemCols = kHaloGroups * N_GEMM <= 128 ? 128 : (kHaloGroups * N_GEMM <= 256 ? 256 : 512);
+    constexpr int kAccs = halo_accs(N_GEMM);
+    constexpr uint32_t kTmemCols = kAccs * N_GEMM <= 128 ? 128 : (kAccs * N_GEMM <= 256 ? 256 : 512);
+    static_assert(kAccs * N_GEMM <= 512, "TMEM columns");
     static_assert((kTmemCols & (kTmemCols - 1)) == 0 && kTmemCols <= 512, "TMEM columns must be a power of two");
     static_assert(CIN == 32 || CIN == 64, "one swizzled row per pixel");
 
@@ -662,8 +942,8 @@ modconv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarrierOffset);
     uint64_t* empty_bar = full_bar + STAGES;
     uint64_t* tmem_full_bar = empty_bar + STAGES;
-    uint64_t* tmem_empty_bar = tmem_full_bar + kHaloGroups;
-    uint64_t* weight_bar = tmem_empty_bar + kHaloGroups;
+    uint64_t* tmem_empty_bar = tmem_full_bar + kAccs;
+    uint64_t* weight_bar = tmem_empty_bar + kAccs;
     uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(weight_bar + 1);
 
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // shfl result = provably warp-uniform
@@ -675,7 +955,7 @@ modconv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_
             mbar_init(full_bar + i, 1);
             mbar_init(empty_bar + i, 1);
         }
-        for (int i = 0; i < kHaloGroups; ++i) {
+        for (int i = 0; i < kAccs; ++i) {
             mbar_init(tmem_full_bar + i, 1);
             mbar_init(tmem_empty_bar + i, 4);
         }
@@ -700,9 +980,18 @@ modconv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_
             __syncwarp();
             int stage = 0;
             uint32_t phase = 0;
+#ifdef GANCE_PIPE_STATS
+            long long waited = 0;
+#endif
             for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
                 const TileCoord t = decode_tile(p, tile, N_GEMM);
+#ifdef GANCE_PIPE_STATS
+                const long long w0 = clock64();
+#endif
                 mbar_wait(empty_bar + stage, phase ^ 1u);
+#ifdef GANCE_PIPE_STATS
+                waited += clock64() - w0;
+#endif
                 if (leader) {
                     mbar_expect_tx(full_bar + stage, L::kHaloBytes);
                     tma_load_4d(smem_halo + stage * L::kHaloStride, &tmap_x, full_bar + stage, 0, t.w0 - 1, t.h0 - 1, t.b0);
@@ -713,6 +1002,9 @@ modconv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_
                     phase ^= 1u;
                 }
             }
+#ifdef GANCE_PIPE_STATS
+            if (p.pipe_stats != nullptr && lane == 0) p.pipe_stats[blockIdx.x * 8 + 4] = waited;
+#endif
         }
     } else if (warp == 1) {
         const bool leader = elect_one_sync();
@@ -725,9 +1017,23 @@ modconv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_
             uint32_t acc_phase = 0;
             const uint32_t w_addr = smem_u32(smem_w);
             const uint64_t b_desc0 = make_smem_desc<kSwizzle>(w_addr);
+#ifdef GANCE_PIPE_STATS
+            long long wait_acc = 0, wait_data = 0;
+            const long long begin = clock64();
+#endif
             for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+#ifdef GANCE_PIPE_STATS
+                const long long w0 = clock64();
+#endif
                 mbar_wait(tmem_empty_bar + acc, acc_phase ^ 1u);
+#ifdef GANCE_PIPE_STATS
+                const long long w1 = clock64();
+#endif
                 mbar_wait(full_bar + stage, phase);
+#ifdef GANCE_PIPE_STATS
+                wait_acc += w1 - w0;
+                wait_data += clock64() - w1;
+#endif
                 tcgen05_fence_after();
                 const uint32_t d_tmem = tmem_base + (uint32_t)(acc * N_GEMM);
                 // descriptors differ from these two only by constants: tap shift / K step, in 16-byte units
@@ -736,12 +1042,25 @@ modconv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_
                 if (leader) {
 #pragma unroll
                     for (int tap = 0; tap < 9; ++tap) {
+#ifdef GANCE_ABL_NOSWZ
+                        // experiment (timing only, the data is NOT in this layout): A read as un-swizzled 8 x 16-byte core
+                        // matrices, [K chunk][h][w][8 channels]: LBO = one K chunk (18 x 10 x 16 B), SBO = one halo row
+                        const uint32_t halo_addr = w_addr + (uint32_t)(L::kWeightBytes + stage * L::kHaloStride);
+                        const uint64_t a_desc = (uint64_t)(((halo_addr + (uint32_t)(((tap / 3) * kHaloW + (tap % 3)) * 16)) & 0x3FFFFu) >> 4) |
+                                                ((uint64_t)((kHaloH * kHaloW * 16) >> 4) << 16) | ((uint64_t)((kHaloW * 16) >> 4) << 32) | (1ull << 46);
+                        const uint64_t b_desc = b_desc0 + (uint64_t)((tap * N_GEMM * L::kRowBytes) >> 4);
+#pragma unroll
+                        for (int k = 0; k < CIN / kUmmaK; ++k)
+                            umma_bf16(d_tmem, a_desc + (uint64_t)((k * 2 * kHaloH * kHaloW * 16) >> 4), b_desc + (uint64_t)(k * 2), idesc,
+                                      (tap | k) != 0 ? 1u : 0u);
+#else
                         const uint64_t a_desc = a_desc0 + (uint64_t)((((tap / 3) * kHaloW + (tap % 3)) * L::kRowBytes) >> 4);
                         const uint64_t b_desc = b_desc0 + (uint64_t)((tap * N_GEMM * L::kRowBytes) >> 4);
 #pragma unroll
                         for (int k = 0; k < CIN / kUmmaK; ++k)
                             umma_bf16(d_tmem, a_desc + (uint64_t)(k * 2), b_desc + (uint64_t)(k * 2), idesc,
                                       (tap | k) != 0 ? 1u : 0u);
+#endif
                     }
                     umma_commit(empty_bar + stage);
                     umma_commit(tmem_full_bar + acc);
@@ -751,14 +1070,21 @@ modconv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_
                     stage = 0;
                     phase ^= 1u;
                 }
-                if (++acc == kHaloGroups) {
+                if (++acc == kAccs) {
                     acc = 0;
                     acc_phase ^= 1u;
                 }
             }
+#ifdef GANCE_PIPE_STATS
+            if (p.pipe_stats != nullptr && lane == 0) {
+                p.pipe_stats[blockIdx.x * 8 + 0] = clock64() - begin;  // MMA warp: whole loop (issue side; the tensor pipe runs behind)
+                p.pipe_stats[blockIdx.x * 8 + 1] = wait_acc;           // ... of which waiting for a drained accumulator
+                p.pipe_stats[blockIdx.x * 8 + 2] = wait_data;          // ... of which waiting for TMA data
+            }
+#endif
         }
     } else {
-        conv_epilogue_frag<T, N_GEMM, (UP ? N_GEMM / 4 : N_GEMM), UP, RGB, kHaloGroups, 3>(
+        conv_epilogue_frag<T, N_GEMM, (UP ? N_GEMM / 4 : N_GEMM), UP, RGB, kHaloGroups, 3, false, halo_apg(N_GEMM)>(
             p, (warp - 2) >> 2, warp, lane, total_tiles, tmem_base, tmem_full_bar, tmem_empty_bar);
     }
 
@@ -770,7 +1096,178 @@ modconv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_
     }
 }
 
+// ---- CTA-pair flavour of the halo kernel (cta_group::2), Cin = 64 or 128 ----------------------------------------------------
+// Each CTA of the pair keeps HALF of the weight matrix resident ([K chunk][tap][N/2 rows][64 channels]), which
+//   * halves the B-operand shared-memory reads per SM (N = 128: A 32 + B 32 clk per MMA -> 32 + 16 against 64 clk of math:
+//     the folded 1024^2 up-convolution leaves the operand-port tie), and
+//   * makes the 128 -> 128 channel layer (256^2 Conv1: 295 KB of weights) fit: 147 KB per CTA. That layer ran on the generic
+//     kernel, which re-fetches every activation tile once per filter tap through L2 and sat at the L2 -> SM limit (ncu,
+//     round 2: 7.3 GB through L2 in 640 us); here a tile's activations cross L2 once (two 18 x 10-pixel halo boxes).
+// Halo boxes are per 64-channel K chunk (one 128-byte swizzled row per pixel); the ring is counted in K chunks.
+template <int N_GEMM, int CIN, int STAGES>
+struct HaloPairSmem {
+    static constexpr int kChunks = CIN / 64;
+    static constexpr int kRowBytes = 128;
+    static constexpr int kTapBytes = (N_GEMM / 2) * kRowBytes;     // one tap, one K chunk, this CTA's half of the rows
+    static constexpr int kWeightBytes = kChunks * 9 * kTapBytes;
+    static constexpr int kHaloBytes = kHaloH * kHaloW * kRowBytes;
+    static constexpr int kHaloStride = (kHaloBytes + 1023) / 1024 * 1024;
+    static constexpr int kBarrierOffset = kWeightBytes + STAGES * kHaloStride;
+    static constexpr int kAccs = kHaloApg * kEpilogueGroups;        // TMEM accumulator buffers
+    static constexpr int kCacheOffset = kBarrierOffset + ((2 * STAGES + 2 * kAccs + 1) * 8 + 16 + 15) / 16 * 16;
+    static constexpr int kCacheFloat4 = 2 * N_GEMM;                 // per epilogue group (row-per-thread epilogue only)
+    static constexpr int kBytes = kCacheOffset + kEpilogueGroups * kCacheFloat4 * 16 + 1024;
+};
+
+template <typename T, int N_GEMM, int CIN, int STAGES, bool UP, bool RGB>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+modconv3x3_halo_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
+                            const ConvParams p) {
+    using L = HaloPairSmem<N_GEMM, CIN, STAGES>;
+    constexpr int C = UP ? N_GEMM / 4 : N_GEMM;  // channels of the output tensor
+    constexpr bool kFrag = C <= 64;              // register-resident coefficients (fragment-layout epilogue)
+    constexpr uint32_t kTmemCols = L::kAccs * N_GEMM;
+    static_assert(CIN == 64 || CIN == 128, "64-channel K chunks");
+    static_assert((kTmemCols & (kTmemCols - 1)) == 0 && kTmemCols <= 512 && kTmemCols >= 32, "TMEM columns must be a power of two");
+    static_assert(L::kTapBytes % 1024 == 0, "weight blocks must stay 1024-byte aligned");
+    static_assert(L::kBytes <= 227 * 1024, "shared memory");
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem_w = smem;
+    uint8_t* smem_halo = smem + L::kWeightBytes;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarrierOffset);
+    uint64_t* empty_bar = full_bar + STAGES;
+    uint64_t* tmem_full_bar = empty_bar + STAGES;
+    uint64_t* tmem_empty_bar = tmem_full_bar + L::kAccs;
+    uint64_t* weight_bar = tmem_empty_bar + L::kAccs;
+    uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(weight_bar + 1);
+
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
+    const int lane = threadIdx.x & 31;
+    const int rank = (int)cluster_ctarank();
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmap_x);
+        prefetch_tmap(&tmap_w);
+        for (int i = 0; i < STAGES; ++i) {
+            mbar_init(full_bar + i, 1);
+            mbar_init(empty_bar + i, 1);
+        }
+        for (int i = 0; i < L::kAccs; ++i) {
+            mbar_init(tmem_full_bar + i, 1);
+            mbar_init(tmem_empty_bar + i, 8);  // four epilogue warps of each CTA (used in the leader only)
+        }
+        mbar_init(weight_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc_pair(tmem_base_slot, kTmemCols);
+    tcgen05_fence_before();
+    cluster_sync_all();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_base_slot, 0);
+    const int total_items = (p.tiles_b * p.tiles_h * p.tiles_w) >> 1;  // even m-tile count (host)
+    const int first_item = (int)cluster_id_x(), item_stride = (int)cluster_count_x();
+
+    if (warp == 0) {
+        const bool leader_lane = elect_one_sync();
+        if (leader_lane) {  // this CTA's half of the weights; both halves are counted on the leader's barrier
+            if (rank == 0) mbar_expect_tx(weight_bar, 2u * L::kWeightBytes);
+            const uint32_t bar = cluster_map(smem_u32(weight_bar), 0);
+            for (int kc = 0; kc < L::kChunks; ++kc)
+                for (int tap = 0; tap < 9; ++tap)
+                    tma_load_2d_pair(smem_w + (kc * 9 + tap) * L::kTapBytes, &tmap_w, bar, tap * CIN + kc * 64,
+                                     rank * (N_GEMM / 2));
+        }
+        __syncwarp();
+        int stage = 0;
+        uint32_t phase = 0;
+        const uint32_t full_leader = cluster_map(smem_u32(full_bar), 0);
+        for (int item = first_item; item < total_items; item += item_stride) {
+            bool ghost;
+            const TileCoord t = decode_pair_item(p, item, rank, N_GEMM, ghost);
+#pragma unroll
+            for (int kc = 0; kc < L::kChunks; ++kc) {
+                mbar_wait(empty_bar + stage, phase ^ 1u);
+                if (leader_lane) {
+                    if (rank == 0) mbar_expect_tx(full_bar + stage, 2u * L::kHaloBytes);
+                    tma_load_4d_pair(smem_halo + stage * L::kHaloStride, &tmap_x, full_leader + (uint32_t)(stage * 8), kc * 64,
+                                     t.w0 - 1, t.h0 - 1, t.b0);
+                }
+                __syncwarp();
+                if (++stage == STAGES) {
+                    stage = 0;
+                    phase ^= 1u;
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (rank == 0) {
+            const bool leader_lane = elect_one_sync();
+            constexpr uint32_t idesc = make_instr_desc(2 * kTileM, N_GEMM, sizeof(T) == 2 && !std::is_same<T, __nv_bfloat16>::value);
+            mbar_wait(weight_bar, 0);
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            const uint32_t w_addr = smem_u32(smem_w);
+            const uint64_t b_desc0 = make_smem_desc<128>(w_addr);
+            for (int item = first_item; item < total_items; item += item_stride) {
+                mbar_wait(tmem_empty_bar + acc, acc_phase ^ 1u);
+                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * N_GEMM);
+#pragma unroll
+                for (int kc = 0; kc < L::kChunks; ++kc) {
+                    mbar_wait(full_bar + stage, phase);
+                    tcgen05_fence_after();
+                    const uint64_t a_desc0 = make_smem_desc_sbo<128>(w_addr + (uint32_t)(L::kWeightBytes + stage * L::kHaloStride),
+                                                                     kHaloW * L::kRowBytes);
+                    if (leader_lane) {
+#pragma unroll
+                        for (int tap = 0; tap < 9; ++tap) {
+                            const uint64_t a_desc = a_desc0 + (uint64_t)((((tap / 3) * kHaloW + (tap % 3)) * L::kRowBytes) >> 4);
+                            const uint64_t b_desc = b_desc0 + (uint64_t)(((kc * 9 + tap) * L::kTapBytes) >> 4);
+#pragma unroll
+                            for (int k = 0; k < 64 / kUmmaK; ++k)
+                                umma_bf16_pair(d_tmem, a_desc + (uint64_t)(k * 2), b_desc + (uint64_t)(k * 2), idesc,
+                                               (kc | tap | k) != 0 ? 1u : 0u);
+                        }
+                        umma_commit_pair(empty_bar + stage);
+                        if (kc == L::kChunks - 1) umma_commit_pair(tmem_full_bar + acc);
+                    }
+                    __syncwarp();
+                    if (++stage == STAGES) {
+                        stage = 0;
+                        phase ^= 1u;
+                    }
+                }
+                if (++acc == L::kAccs) {
+                    acc = 0;
+                    acc_phase ^= 1u;
+                }
+            }
+        }
+    } else {
+        if constexpr (kFrag)
+            conv_epilogue_frag<T, N_GEMM, C, UP, RGB, kEpilogueGroups, 3, true, kHaloApg>(p, (warp - 2) >> 2, warp, lane, total_items, tmem_base,
+                                                                               tmem_full_bar, tmem_empty_bar);
+        else
+            conv_epilogue<T, N_GEMM, UP, RGB, kEpilogueGroups, L::kCacheFloat4, true, kHaloApg>(
+                p, (warp - 2) >> 2, warp, lane, total_items, tmem_base, tmem_full_bar, tmem_empty_bar,
+                reinterpret_cast<float4*>(smem + L::kCacheOffset));
+    }
+
+    tcgen05_fence_before();
+    cluster_sync_all();
+    if (warp == 1) {
+        tcgen05_fence_after();
+        tmem_dealloc_pair(tmem_base, kTmemCols);
+    }
+}
+
 // ---- host side -------------------------------------------------------------------------------------
+#ifdef GANCE_PIPE_STATS
+static long long* g_pipe_stats = nullptr;  // [launch slot][CTA][8], advanced by every single-CTA halo launch
+static int g_pipe_slot = 0;
+#endif
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -854,6 +1351,86 @@ static int launch(bool half_operands, const ConvParams& p, const void* x, const 
     return launch_typed<__nv_bfloat16, N_TILE, BLOCK_K, STAGES>(p, x, weight, h_in, w_in, stream);
 }
 
+// ---- CTA-pair launches ----
+static int g_pair_mode = 1;         // gance_set_conv_pairing(): 0 never, 1 when a layer fills a wave of CTA pairs, 2 whenever eligible
+static int g_pair_clusters[2] = {0, 0};  // co-resident 2-CTA clusters for the <256,64,6> / <128,64,8> instances (0 = not usable)
+
+template <typename T, int N_TILE, int BLOCK_K, int STAGES, bool RGB>
+static int configure_pair_one(int* clusters) {
+    using L = PairSmemLayout<N_TILE, BLOCK_K, STAGES>;
+    auto kernel = modconv3x3_pair_kernel<T, N_TILE, BLOCK_K, STAGES, RGB>;
+    int rc = raise_smem_limit(kernel, L::kBytes, "modconv3x3_pair");
+    if (rc != GANCE_OK) return rc;
+    cudaLaunchConfig_t config = {};
+    config.gridDim = dim3(2 * g_num_sms, 1, 1);
+    config.blockDim = dim3(kThreads, 1, 1);
+    config.dynamicSmemBytes = L::kBytes;
+    cudaLaunchAttribute attribute;
+    attribute.id = cudaLaunchAttributeClusterDimension;
+    attribute.val.clusterDim.x = 2; attribute.val.clusterDim.y = 1; attribute.val.clusterDim.z = 1;
+    config.attrs = &attribute;
+    config.numAttrs = 1;
+    int n = 0;
+    cudaError_t err = cudaOccupancyMaxActiveClusters(&n, kernel, &config);
+    if (err != cudaSuccess) {
+        cudaGetLastError();
+        n = 0;  // pairing stays off for this instance; the single-CTA kernel serves it
+    }
+    if (*clusters == 0 || n < *clusters) *clusters = n;
+    return GANCE_OK;
+}
+
+template <int N_TILE, int BLOCK_K, int STAGES>
+static int configure_pair(int* clusters) {
+    int rc, n = 1 << 30;
+    if ((rc = configure_pair_one<__half, N_TILE, BLOCK_K, STAGES, false>(&n)) != GANCE_OK) return rc;
+    if ((rc = configure_pair_one<__half, N_TILE, BLOCK_K, STAGES, true>(&n)) != GANCE_OK) return rc;
+    if ((rc = configure_pair_one<__nv_bfloat16, N_TILE, BLOCK_K, STAGES, false>(&n)) != GANCE_OK) return rc;
+    if ((rc = configure_pair_one<__nv_bfloat16, N_TILE, BLOCK_K, STAGES, true>(&n)) != GANCE_OK) return rc;
+    *clusters = n == (1 << 30) ? 0 : n;
+    return GANCE_OK;
+}
+
+template <typename T, int N_TILE, int BLOCK_K, int STAGES>
+static int launch_pair_typed(const ConvParams& p, const void* x, const void* weight, int h_in, int w_in, int max_clusters,
+                             cudaStream_t stream) {
+    using L = PairSmemLayout<N_TILE, BLOCK_K, STAGES>;
+    constexpr bool kHalf = std::is_same<T, __half>::value;
+    CUtensorMap tmap_x, tmap_w;
+    {
+        cuuint64_t dims[4] = {(cuuint64_t)p.c_in, (cuuint64_t)w_in, (cuuint64_t)h_in, (cuuint64_t)p.batch};
+        cuuint64_t strides[3] = {(cuuint64_t)p.c_in * 2, (cuuint64_t)w_in * p.c_in * 2,
+                                 (cuuint64_t)h_in * w_in * p.c_in * 2};
+        cuuint32_t box[4] = {(cuuint32_t)BLOCK_K, (cuuint32_t)p.tile_w, (cuuint32_t)p.tile_h, 1u};
+        int rc = make_tmap(&tmap_x, x, kHalf, 4, dims, strides, box, BLOCK_K * 2);
+        if (rc != GANCE_OK) return rc;
+    }
+    {
+        cuuint64_t dims[2] = {(cuuint64_t)9 * p.c_in, (cuuint64_t)p.c_out};
+        cuuint64_t strides[1] = {(cuuint64_t)9 * p.c_in * 2};
+        cuuint32_t box[2] = {(cuuint32_t)BLOCK_K, (cuuint32_t)(N_TILE / 2)};
+        int rc = make_tmap(&tmap_w, weight, kHalf, 2, dims, strides, box, BLOCK_K * 2);
+        if (rc != GANCE_OK) return rc;
+    }
+    ConvParams q = p;
+    q.a_tx_bytes = p.tile_w * p.tile_h * BLOCK_K * 2;
+    const int m_tiles = p.tiles_b * p.tiles_h * p.tiles_w;
+    const int items = ((m_tiles + 1) / 2) * p.n_tiles;
+    const int clusters = items < max_clusters ? items : max_clusters;
+    if (p.rgb_weight != nullptr)
+        modconv3x3_pair_kernel<T, N_TILE, BLOCK_K, STAGES, true><<<2 * clusters, kThreads, L::kBytes, stream>>>(tmap_x, tmap_w, q);
+    else
+        modconv3x3_pair_kernel<T, N_TILE, BLOCK_K, STAGES, false><<<2 * clusters, kThreads, L::kBytes, stream>>>(tmap_x, tmap_w, q);
+    return check_launch("modconv3x3_pair_kernel");
+}
+
+template <int N_TILE, int BLOCK_K, int STAGES>
+static int launch_pair(bool half_operands, const ConvParams& p, const void* x, const void* weight, int h_in, int w_in,
+                       int max_clusters, cudaStream_t stream) {
+    if (half_operands) return launch_pair_typed<__half, N_TILE, BLOCK_K, STAGES>(p, x, weight, h_in, w_in, max_clusters, stream);
+    return launch_pair_typed<__nv_bfloat16, N_TILE, BLOCK_K, STAGES>(p, x, weight, h_in, w_in, max_clusters, stream);
+}
+
 // The halo instances that exist: <N_GEMM, CIN> = <128,64> is the folded 1024^2 up-convolution (and plain 64->128),
 // <64,64> the 512^2 Conv1 (plain / fused ToRGB), <32,32> the 1024^2 Conv1 (plain / fused ToRGB).
 template <typename T, int N_GEMM, int CIN, int STAGES>
@@ -877,12 +1454,19 @@ static int launch_halo_typed(const ConvParams& p, const void* x, const void* wei
     }
     const int total_tiles = p.tiles_b * p.tiles_h * p.tiles_w;
     const int grid = total_tiles < g_num_sms ? total_tiles : g_num_sms;
+#ifdef GANCE_PIPE_STATS
+    ConvParams q = p;
+    q.pipe_stats = g_pipe_stats ? g_pipe_stats + (size_t)(g_pipe_slot++) * 256 * 8 : nullptr;
+    const ConvParams& launch_params = q;
+#else
+    const ConvParams& launch_params = p;
+#endif
     if constexpr (N_GEMM == 128) {  // only the folded up-convolution 64 -> 4 x 32
-        modconv3x3_halo_kernel<T, N_GEMM, CIN, STAGES, true, false><<<grid, halo_threads(N_GEMM), L::kBytes, stream>>>(tmap_x, tmap_w, p);
+        modconv3x3_halo_kernel<T, N_GEMM, CIN, STAGES, true, false><<<grid, halo_threads(N_GEMM), L::kBytes, stream>>>(tmap_x, tmap_w, launch_params);
     } else if (p.rgb_weight != nullptr) {
-        modconv3x3_halo_kernel<T, N_GEMM, CIN, STAGES, false, true><<<grid, halo_threads(N_GEMM), L::kBytes, stream>>>(tmap_x, tmap_w, p);
+        modconv3x3_halo_kernel<T, N_GEMM, CIN, STAGES, false, true><<<grid, halo_threads(N_GEMM), L::kBytes, stream>>>(tmap_x, tmap_w, launch_params);
     } else {
-        modconv3x3_halo_kernel<T, N_GEMM, CIN, STAGES, false, false><<<grid, halo_threads(N_GEMM), L::kBytes, stream>>>(tmap_x, tmap_w, p);
+        modconv3x3_halo_kernel<T, N_GEMM, CIN, STAGES, false, false><<<grid, halo_threads(N_GEMM), L::kBytes, stream>>>(tmap_x, tmap_w, launch_params);
     }
     return check_launch("modconv3x3_halo_kernel");
 }
@@ -906,6 +1490,91 @@ static int configure_halo() {
         if ((rc = raise_smem_limit(modconv3x3_halo_kernel<__nv_bfloat16, N_GEMM, CIN, STAGES, false, true>, L::kBytes, "modconv3x3_halo<rgb>")) != GANCE_OK) return rc;
         return raise_smem_limit(modconv3x3_halo_kernel<__half, N_GEMM, CIN, STAGES, false, true>, L::kBytes, "modconv3x3_halo<rgb>");
     }
+}
+
+// ---- CTA-pair halo launches: <N_GEMM, CIN> = <128,64> folded 1024^2 up-convolution, <64,64> 512^2 Conv1, <128,128> 256^2 Conv1
+static int g_halo_pair_clusters[3] = {0, 0, 0};
+
+template <typename K>
+static int pair_cluster_capacity(K kernel, int smem_bytes) {
+    cudaLaunchConfig_t config = {};
+    config.gridDim = dim3(2 * g_num_sms, 1, 1);
+    config.blockDim = dim3(kThreads, 1, 1);
+    config.dynamicSmemBytes = smem_bytes;
+    cudaLaunchAttribute attribute;
+    attribute.id = cudaLaunchAttributeClusterDimension;
+    attribute.val.clusterDim.x = 2; attribute.val.clusterDim.y = 1; attribute.val.clusterDim.z = 1;
+    config.attrs = &attribute;
+    config.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, kernel, &config) != cudaSuccess) {
+        cudaGetLastError();
+        n = 0;
+    }
+    return n;
+}
+
+template <typename T, int N_GEMM, int CIN, int STAGES, bool UP, bool RGB>
+static int configure_halo_pair_one(int* clusters) {
+    using L = HaloPairSmem<N_GEMM, CIN, STAGES>;
+    auto kernel = modconv3x3_halo_pair_kernel<T, N_GEMM, CIN, STAGES, UP, RGB>;
+    int rc = raise_smem_limit(kernel, L::kBytes, "modconv3x3_halo_pair");
+    if (rc != GANCE_OK) return rc;
+    const int n = pair_cluster_capacity(kernel, L::kBytes);
+    if (n < *clusters) *clusters = n;
+    return GANCE_OK;
+}
+
+template <int N_GEMM, int CIN, int STAGES, bool UP>
+static int configure_halo_pair(int* clusters) {
+    int rc, n = 1 << 30;
+    if ((rc = configure_halo_pair_one<__half, N_GEMM, CIN, STAGES, UP, false>(&n)) != GANCE_OK) return rc;
+    if ((rc = configure_halo_pair_one<__nv_bfloat16, N_GEMM, CIN, STAGES, UP, false>(&n)) != GANCE_OK) return rc;
+    if constexpr (!UP) {
+        if ((rc = configure_halo_pair_one<__half, N_GEMM, CIN, STAGES, UP, true>(&n)) != GANCE_OK) return rc;
+        if ((rc = configure_halo_pair_one<__nv_bfloat16, N_GEMM, CIN, STAGES, UP, true>(&n)) != GANCE_OK) return rc;
+    }
+    *clusters = n == (1 << 30) ? 0 : n;
+    return GANCE_OK;
+}
+
+template <typename T, int N_GEMM, int CIN, int STAGES, bool UP>
+static int launch_halo_pair_typed(const ConvParams& p, const void* x, const void* weight, int max_clusters, cudaStream_t stream) {
+    using L = HaloPairSmem<N_GEMM, CIN, STAGES>;
+    constexpr bool kHalf = std::is_same<T, __half>::value;
+    CUtensorMap tmap_x, tmap_w;
+    {
+        cuuint64_t dims[4] = {(cuuint64_t)CIN, (cuuint64_t)p.w_out, (cuuint64_t)p.h_out, (cuuint64_t)p.batch};
+        cuuint64_t strides[3] = {(cuuint64_t)CIN * 2, (cuuint64_t)p.w_out * CIN * 2, (cuuint64_t)p.h_out * p.w_out * CIN * 2};
+        cuuint32_t box[4] = {64u, (cuuint32_t)kHaloW, (cuuint32_t)kHaloH, 1u};
+        int rc = make_tmap(&tmap_x, x, kHalf, 4, dims, strides, box, 128);
+        if (rc != GANCE_OK) return rc;
+    }
+    {
+        cuuint64_t dims[2] = {(cuuint64_t)9 * CIN, (cuuint64_t)N_GEMM};
+        cuuint64_t strides[1] = {(cuuint64_t)9 * CIN * 2};
+        cuuint32_t box[2] = {64u, (cuuint32_t)(N_GEMM / 2)};
+        int rc = make_tmap(&tmap_w, weight, kHalf, 2, dims, strides, box, 128);
+        if (rc != GANCE_OK) return rc;
+    }
+    const int items = (p.tiles_b * p.tiles_h * p.tiles_w) / 2;
+    const int clusters = items < max_clusters ? items : max_clusters;
+    if constexpr (UP) {
+        modconv3x3_halo_pair_kernel<T, N_GEMM, CIN, STAGES, true, false><<<2 * clusters, kThreads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
+    } else {
+        if (p.rgb_weight != nullptr)
+            modconv3x3_halo_pair_kernel<T, N_GEMM, CIN, STAGES, false, true><<<2 * clusters, kThreads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
+        else
+            modconv3x3_halo_pair_kernel<T, N_GEMM, CIN, STAGES, false, false><<<2 * clusters, kThreads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
+    }
+    return check_launch("modconv3x3_halo_pair_kernel");
+}
+
+template <int N_GEMM, int CIN, int STAGES, bool UP>
+static int launch_halo_pair(bool half_operands, const ConvParams& p, const void* x, const void* weight, int max_clusters,
+                            cudaStream_t stream) {
+    if (half_operands) return launch_halo_pair_typed<__half, N_GEMM, CIN, STAGES, UP>(p, x, weight, max_clusters, stream);
+    return launch_halo_pair_typed<__nv_bfloat16, N_GEMM, CIN, STAGES, UP>(p, x, weight, max_clusters, stream);
 }
 
 static const bool g_use_halo = true;
@@ -948,6 +1617,11 @@ int init_tensor_core_path() {
     if ((rc = tc::configure<64, 64, 8>()) != GANCE_OK) return rc;
     if ((rc = tc::configure<32, 64, 8>()) != GANCE_OK) return rc;
     if ((rc = tc::configure<32, 32, 8>()) != GANCE_OK) return rc;
+    if ((rc = tc::configure_pair<256, 64, 6>(&tc::g_pair_clusters[0])) != GANCE_OK) return rc;
+    if ((rc = tc::configure_pair<128, 64, 8>(&tc::g_pair_clusters[1])) != GANCE_OK) return rc;
+    if ((rc = tc::configure_halo_pair<128, 64, 4, true>(&tc::g_halo_pair_clusters[0])) != GANCE_OK) return rc;
+    if ((rc = tc::configure_halo_pair<64, 64, 4, false>(&tc::g_halo_pair_clusters[1])) != GANCE_OK) return rc;
+    if ((rc = tc::configure_halo_pair<128, 128, 3, false>(&tc::g_halo_pair_clusters[2])) != GANCE_OK) return rc;
     if ((rc = tc::configure_halo<128, 64, 2>()) != GANCE_OK) return rc;
     if ((rc = tc::configure_halo<64, 64, 3>()) != GANCE_OK) return rc;
     if ((rc = tc::configure_halo<32, 32, 4>()) != GANCE_OK) return rc;
@@ -1017,6 +1691,7 @@ static int launch_tensor_core_conv(const char* who, const void* x, int dtype, in
     p.rgb_bias = rgb ? rgb->bias : nullptr; p.y_prev = rgb ? rgb->y_prev : nullptr;
     p.y_out = rgb ? rgb->y_out : nullptr; p.frames = rgb ? rgb->frames : nullptr;
     p.nonfinite = nonfinite_flag();
+    p.pipe_stats = nullptr;
     const bool one_n_tile = rgb != nullptr;  // the fused ToRGB needs every channel of a pixel in one tile
     GANCE_REQUIRE(!one_n_tile || (up == 0 && (c_out == 256 || c_out == 128 || c_out == 64 || c_out == 32)), GANCE_E_SHAPE,
                   "%s: fused ToRGB needs Cout in {32,64,128,256} (got %d)", who, c_out);
@@ -1029,14 +1704,33 @@ static int launch_tensor_core_conv(const char* who, const void* x, int dtype, in
     };
     set_tile_logs();
 
-    // Narrow layers (512^2 / 1024^2): halo kernel, whole weight resident, one activation fetch per tile.
-    if (tc::g_use_halo && pad == 1 && w_out % tc::kHaloTileW == 0 && h_out % tc::kHaloTileH == 0 &&
-        ((c_in == 64 && ((c_out == 128 && up && c_real == 32) || (c_out == 64 && !up))) || (c_in == 32 && c_out == 32 && !up))) {
+    // Narrow layers (512^2 / 1024^2): halo kernel, whole weight resident, one activation fetch per tile. As CTA pairs
+    // (half of the weights per CTA) also the 128 -> 128 channel layer (256^2 Conv1).
+    const bool halo_shape = tc::g_use_halo && pad == 1 && w_out % tc::kHaloTileW == 0 && h_out % tc::kHaloTileH == 0;
+    const int halo_m_tiles = halo_shape ? batch * (w_out / tc::kHaloTileW) * (h_out / tc::kHaloTileH) : 0;
+    // CTA pairs for the halo layers: even m-tile count, and (unless forced) one work item per co-resident pair. Measured
+    // (round 2, batch 32): the 128 -> 128 layer gains 14 % (660 -> 580 us: it leaves the L2-bound generic kernel), but the
+    // two 64-channel layers LOSE (512^2 Conv1 690 -> 810 us, folded 1024^2 up-convolution 990 -> 1050 us): their tiles are
+    // 18-36 MMAs long and every accumulator hand-over now crosses the SM pair. Those two pair only when forced (mode 2).
+    auto halo_pair_ok = [&](int which) {
+        const int clusters = tc::g_halo_pair_clusters[which];
+        if (tc::g_pair_mode == 0 || clusters <= 0 || halo_m_tiles % 2 != 0) return false;
+        if (tc::g_pair_mode == 2) return true;
+        return which == 2 && halo_m_tiles / 2 >= clusters;
+    };
+    const bool wide_halo = halo_shape && c_in == 128 && c_out == 128 && !up && halo_pair_ok(2);
+    if (wide_halo || (halo_shape &&
+        ((c_in == 64 && ((c_out == 128 && up && c_real == 32) || (c_out == 64 && !up))) || (c_in == 32 && c_out == 32 && !up)))) {
         p.tile_w = tc::kHaloTileW; p.tile_h = tc::kHaloTileH; p.tile_b = 1;
         p.tile_w_log2 = ilog2(p.tile_w); p.tile_hw_log2 = ilog2(p.tile_w * p.tile_h);
         p.tiles_w = w_out / p.tile_w; p.tiles_h = h_out / p.tile_h; p.tiles_b = batch;
         set_tile_logs();
         p.n_tiles = 1; p.k_chunks = 1;
+        if (wide_halo) return tc::launch_halo_pair<128, 128, 3, false>(half_operands, p, x, weight, tc::g_halo_pair_clusters[2], s);
+        if (c_in == 64 && c_out == 128 && halo_pair_ok(0))
+            return tc::launch_halo_pair<128, 64, 4, true>(half_operands, p, x, weight, tc::g_halo_pair_clusters[0], s);
+        if (c_in == 64 && c_out == 64 && halo_pair_ok(1))
+            return tc::launch_halo_pair<64, 64, 4, false>(half_operands, p, x, weight, tc::g_halo_pair_clusters[1], s);
         if (c_in == 32) return tc::launch_halo<32, 32, 4>(half_operands, p, x, weight, s);
         if (c_out == 128) return tc::launch_halo<128, 64, 2>(half_operands, p, x, weight, s);
         return tc::launch_halo<64, 64, 3>(half_operands, p, x, weight, s);
@@ -1046,12 +1740,19 @@ static int launch_tensor_core_conv(const char* who, const void* x, int dtype, in
         return tc::launch<32, 32, 8>(half_operands, p, x, weight, h_in, w_in, s);
     }
     p.k_chunks = c_in / 64;
+    // CTA pairs (cta_group::2) for the plain / fused-ToRGB layers with at least one full wave of pair items
+    const bool pairable = tc::g_pair_mode != 0 && !up;
+    const int pair_items_needed = tc::g_pair_mode == 2 ? 1 : 0;  // 0: at least one item per co-resident cluster
     if (c_out % 256 == 0 && (m_tiles >= 148 || one_n_tile)) {
         p.n_tiles = c_out / 256;
+        if (pairable && tc::g_pair_clusters[0] > 0 && ((m_tiles + 1) / 2) * p.n_tiles >= (pair_items_needed ? pair_items_needed : tc::g_pair_clusters[0]))
+            return tc::launch_pair<256, 64, 6>(half_operands, p, x, weight, h_in, w_in, tc::g_pair_clusters[0], s);
         return tc::launch<256, 64, 4>(half_operands, p, x, weight, h_in, w_in, s);
     }
     if (c_out % 128 == 0 && !(one_n_tile && c_out != 128)) {
         p.n_tiles = c_out / 128;
+        if (pairable && tc::g_pair_clusters[1] > 0 && ((m_tiles + 1) / 2) * p.n_tiles >= (pair_items_needed ? pair_items_needed : tc::g_pair_clusters[1]))
+            return tc::launch_pair<128, 64, 8>(half_operands, p, x, weight, h_in, w_in, tc::g_pair_clusters[1], s);
         return tc::launch<128, 64, 6>(half_operands, p, x, weight, h_in, w_in, s);
     }
     if (c_out % 64 == 0 && !(one_n_tile && c_out != 64)) {
@@ -1060,6 +1761,21 @@ static int launch_tensor_core_conv(const char* who, const void* x, int dtype, in
     }
     p.n_tiles = c_out / 32;
     return tc::launch<32, 64, 8>(half_operands, p, x, weight, h_in, w_in, s);
+}
+
+#ifdef GANCE_PIPE_STATS
+// tools/pipe_stats.py only: device buffer [slots][256][8] of int64, filled by the next single-CTA halo launches
+extern "C" int gance_debug_pipe_stats(long long* buffer) {
+    tc::g_pipe_stats = buffer;
+    tc::g_pipe_slot = 0;
+    return GANCE_OK;
+}
+#endif
+
+extern "C" int gance_set_conv_pairing(int mode) {
+    const int before = tc::g_pair_mode;
+    tc::g_pair_mode = mode < 0 ? 0 : (mode > 2 ? 2 : mode);
+    return before;
 }
 
 extern "C" int gance_modconv3x3(const void* x, int dtype, int batch, int h_out, int w_out, int c_in, int c_out,

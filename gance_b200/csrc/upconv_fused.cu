@@ -258,6 +258,9 @@ upconv_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
             mbar_wait(tmem_full_bar + acc, full_phase);
             tcgen05_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * 4 * CC + half * 2 * CC);
+#ifdef GANCE_ABL_FU_NODRAIN
+            if (p.batch < 0)  // ablation: the accumulator is not copied to the patch
+#endif
 #pragma unroll
             for (int blk = 0; blk < 2; ++blk) {
                 const int block = half * 2 + blk;                      // P01, P00 | P10, P11
@@ -288,7 +291,11 @@ upconv_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
             if (lane == 0) mbar_arrive(tmem_empty_bar + acc);
             epilogue_barrier();
             // ---- (c) FIR + demod + noise + bias + lrelu + next style from the patch ----
+#ifdef GANCE_ABL_FU_NOFILTER
+            if (rows_valid > 0 && p.batch < 0) {  // ablation: drain only
+#else
             if (rows_valid > 0) {
+#endif
                 const float bs[4] = {b4.x, b4.y, b4.z, b4.w};
                 const float coef[4] = {d4.x * 0.0625f, d4.y * 0.0625f, d4.z * 0.0625f, d4.w * 0.0625f};
                 // lrelu(v) * g = v * 0.6 g + |v| * 0.4 g  (alpha = 0.2), g = sqrt(2) * next style
@@ -333,6 +340,9 @@ upconv_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
                                     const float value = fmaf(sum, coef[q], nzv + bs[q]);
                                     o[q] = fmaf(fabsf(value), neg[q], value * pos[q]);
                                 }
+#ifdef GANCE_ABL_FU_NOSTORE
+                                if (o[0] == 12345.678f)  // ablation: (practically) no global stores
+#endif
                                 *reinterpret_cast<uint2*>(out_ptr + px * p.c_out) = pack4(o, (T*)nullptr);
                             }
                         }

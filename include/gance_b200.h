@@ -73,6 +73,12 @@ unsigned long long gance_launch_count(void);
  * CUDA graph keeps the pointer it was captured with).
  * The host reads the flag back with the frames and reports GANCE_E_NONFINITE. */
 int gance_set_nonfinite_flag(int* device_flag);
+/* Tuning switch (no counterpart in the reference): how the generic 3x3 implicit GEMM (Cout % 128 == 0, plain or fused
+ * ToRGB) is scheduled. 0 = one CTA per tile (tcgen05 cta_group::1); 1 (default) = CTA pairs on the two SMs of a TPC
+ * sharing one M = 256 MMA (cta_group::2: each SM reads its own pixels and HALF of the weight tile) for layers with at
+ * least one work item per co-resident pair; 2 = CTA pairs whenever the shape is eligible (tests: small shapes, odd tile
+ * counts). Results are the same in every mode. Process-wide, read at launch time; returns the previous mode. */
+int gance_set_conv_pairing(int mode);
 
 /* ---- G_mapping + truncation ------------------------------------------------------------------
  * networks_stylegan2.G_mapping + the 'Truncation' block of G_main, as run by Gs.run

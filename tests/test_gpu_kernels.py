@@ -7,6 +7,8 @@ bf16 mode - the inputs are rounded to bf16 first and the oracle evaluated on the
 what remains is fp32 accumulation order plus the final bf16 rounding of the output (2^-8 relative).
 """
 
+import contextlib
+
 import numpy as np
 import pytest
 import torch
@@ -200,6 +202,8 @@ CONV_CASES = [
     (64, 64, 32, 3, 1, "halo kernel N=64 (512^2 Conv1 shape)"),
     (64, 128, 16, 2, 1, "halo kernel N=128"),
     (64, 64, 48, 1, 1, "halo kernel, 3x6 tiles"),
+    (128, 128, 32, 2, 1, "128 -> 128 channels, halo-shaped image (CTA-pair halo kernel when pairing is on)"),
+    (128, 128, 48, 1, 1, "128 -> 128 channels, 3x6 halo tiles"),
     (64, 64, 32, 2, 0, "VALID (up-conv second half)"),
     (512, 512, 8, 2, 0, "VALID 8x8"),
 ]
@@ -251,10 +255,12 @@ def test_modconv3x3_fp32_matches_oracle(lib, cin, cout, side, batch, pad, name):
     assert rel_err(got, want) < 2e-5, name
 
 
+@pytest.mark.parametrize("pairing", [0, 2])  # single-CTA kernels / CTA pairs (cta_group::2) wherever a shape is eligible
 @pytest.mark.parametrize("mode", ["bf16", "fp16"])
 @pytest.mark.parametrize("cin,cout,side,batch,pad,name", CONV_CASES)
-def test_modconv3x3_tcgen05_matches_oracle(lib, mode, cin, cout, side, batch, pad, name):
-    got, want = _run_modconv(lib, mode, cin, cout, side, batch, pad)
+def test_modconv3x3_tcgen05_matches_oracle(lib, mode, cin, cout, side, batch, pad, name, pairing):
+    with conv_pairing(lib, pairing):
+        got, want = _run_modconv(lib, mode, cin, cout, side, batch, pad)
     assert not torch.isnan(got.float()).any(), "kernel left output unwritten"
     ulp = 2.0 ** -8 if mode == "bf16" else 2.0 ** -11  # half an output ulp, relative
     err = rel_err(got, want)
@@ -263,6 +269,52 @@ def test_modconv3x3_tcgen05_matches_oracle(lib, mode, cin, cout, side, batch, pa
     diff = (got.double().cpu() - want).abs()
     bound = want.abs() * ulp + 2e-5 * float(want.abs().max())
     assert bool((diff <= bound).all()), f"{name}: {int((diff > bound).sum())} elements out of bound"
+
+
+@contextlib.contextmanager
+def conv_pairing(lib, mode):
+    """gance_set_conv_pairing(mode) for the duration of a block (0 single CTA, 1 default, 2 CTA pairs whenever eligible)."""
+    before = lib.gance_set_conv_pairing(mode)
+    try:
+        yield
+    finally:
+        lib.gance_set_conv_pairing(before)
+
+
+PAIR_CASES = [
+    # cin, cout, side, batch, pad, name
+    (512, 512, 4, 9, 1, "9 one-tile samples: odd m-tile count, the last pair holds a ghost tile; N=256 x 2 n-tiles"),
+    (256, 512, 8, 1, 1, "ONE m-tile: the whole second CTA of the pair is a ghost"),
+    (512, 256, 16, 2, 1, "N=256, 4 m-tiles"),
+    (256, 256, 64, 5, 1, "N=256, 160 m-tiles: more pair items than co-resident clusters"),
+    (128, 128, 24, 2, 1, "N=128, tiles that overhang the image (24 = 16 + 8)"),
+    (128, 128, 64, 3, 1, "N=128, 96 m-tiles"),
+    (512, 512, 8, 2, 0, "VALID 8x8"),
+    (128, 128, 32, 3, 1, "CTA-pair halo kernel, two 64-channel K chunks per tile"),
+    (128, 128, 64, 5, 1, "CTA-pair halo kernel, 320 m-tiles: more pair items than co-resident clusters"),
+    (64, 64, 64, 5, 1, "CTA-pair halo kernel N=64"),
+]
+
+
+@pytest.mark.parametrize("mode", ["bf16", "fp16"])
+@pytest.mark.parametrize("cin,cout,side,batch,pad,name", PAIR_CASES)
+def test_modconv3x3_cta_pair_matches_oracle_and_the_single_cta_kernel(lib, mode, cin, cout, side, batch, pad, name):
+    """The cta_group::2 flavour (two CTAs, one M=256 MMA) against float64 and against the cta_group::1 kernel."""
+    with conv_pairing(lib, 2):
+        launches = lib.gance_launch_count()
+        got, want = _run_modconv(lib, mode, cin, cout, side, batch, pad)
+        assert lib.gance_launch_count() == launches + 1
+    with conv_pairing(lib, 0):
+        single, _ = _run_modconv(lib, mode, cin, cout, side, batch, pad)
+    assert not torch.isnan(got.float()).any(), "kernel left output unwritten"
+    ulp = 2.0 ** -8 if mode == "bf16" else 2.0 ** -11
+    diff = (got.double().cpu() - want).abs()
+    bound = want.abs() * ulp + 2e-5 * float(want.abs().max())
+    assert bool((diff <= bound).all()), f"{name}: {int((diff > bound).sum())} elements out of bound"
+    # same K order, same fp32 accumulation: the two schedules agree to the last bit - except 128 -> 128 channels on a
+    # halo-shaped image, where the pair kernel walks K as (chunk, tap) and the single-CTA generic kernel as (tap, chunk)
+    if not (cin == 128 and cout == 128 and side % 16 == 0):
+        assert torch.equal(got, single), f"{name}: {int((got != single).sum())} elements differ from the single-CTA kernel"
 
 
 def _split_tf32(lib, tensor, styles=None):
@@ -340,8 +392,14 @@ def test_modconv3x3_tcgen05_without_next_style_and_noise_per_sample(lib):
 
 
 @pytest.mark.parametrize("mode", ["bf16", "fp16"])
-@pytest.mark.parametrize("cin,cout,side,batch", [(512, 512, 4, 3), (512, 512, 16, 2), (256, 512, 8, 1), (128, 128, 24, 2)])
-def test_modconv3x3_dual_writes_the_layer_output_and_the_next_modulated_input(lib, mode, cin, cout, side, batch):
+@pytest.mark.parametrize("cin,cout,side,batch", [(512, 512, 4, 3), (512, 512, 16, 2), (256, 512, 8, 1), (128, 128, 24, 2), (128, 128, 32, 2)])
+@pytest.mark.parametrize("pairing", [0, 2])
+def test_modconv3x3_dual_writes_the_layer_output_and_the_next_modulated_input(lib, mode, cin, cout, side, batch, pairing):
+    with conv_pairing(lib, pairing):
+        _dual_case(lib, mode, cin, cout, side, batch)
+
+
+def _dual_case(lib, mode, cin, cout, side, batch):
     """gance_modconv3x3_dual: `out` = the activated layer output (what ToRGB reads), `out_scaled` = out * next styles
     (what the next block's Conv0_up reads), both from one epilogue; each against the fp64 computation."""
     code, dt = MODE_CODES[mode]
@@ -412,7 +470,13 @@ def test_up_convolution_matches_oracle(lib, mode):
 
 @pytest.mark.parametrize("mode", ["bf16", "fp16"])
 @pytest.mark.parametrize("cin,cout,side,batch", [(64, 32, 16, 2), (512, 512, 4, 3), (128, 64, 32, 1), (256, 128, 8, 5)])
-def test_folded_up_convolution_matches_oracle(lib, mode, cin, cout, side, batch):
+@pytest.mark.parametrize("pairing", [0, 2])
+def test_folded_up_convolution_matches_oracle(lib, mode, cin, cout, side, batch, pairing):
+    with conv_pairing(lib, pairing):
+        _folded_up_case(lib, mode, cin, cout, side, batch)
+
+
+def _folded_up_case(lib, mode, cin, cout, side, batch):
     """gance_scale_channels + gance_modconv3x3_up2_folded against the transposed-conv + upfirdn oracle."""
     from gance_b200.synthesis import fold_up_weight
 
@@ -452,8 +516,22 @@ def test_folded_up_convolution_matches_oracle(lib, mode, cin, cout, side, batch)
 @pytest.mark.parametrize("cin,cout,side,batch,last", [(64, 64, 32, 2, False), (32, 32, 32, 3, True), (128, 128, 16, 2, False),
                                                      (256, 256, 16, 1, False), (64, 32, 16, 2, True),
                                                      (64, 64, 32, 2, True), (64, 64, 16, 3, True)])  # last block of a 512^2 network
-def test_fused_conv_torgb_matches_oracle(lib, mode, cin, cout, side, batch, last):
+@pytest.mark.parametrize("pairing", [0, 2])
+def test_fused_conv_torgb_matches_oracle(lib, mode, cin, cout, side, batch, last, pairing):
     """gance_modconv3x3_torgb: Conv1 epilogue + ToRGB + skip upsample (+ uint8) against float64 arithmetic."""
+    with conv_pairing(lib, pairing):
+        _fused_conv_torgb_case(lib, mode, cin, cout, side, batch, last)
+
+
+@pytest.mark.parametrize("mode", ["bf16", "fp16"])
+@pytest.mark.parametrize("cin,cout,side,batch", [(128, 128, 16, 2), (256, 256, 16, 1), (128, 128, 32, 3), (256, 256, 8, 3)])
+def test_fused_conv_torgb_cta_pair_matches_oracle(lib, mode, cin, cout, side, batch):
+    """The same through the cta_group::2 kernel (N = 128 / 256 with the fused ToRGB), incl. an odd m-tile count (8x8 x 3)."""
+    with conv_pairing(lib, 2):
+        _fused_conv_torgb_case(lib, mode, cin, cout, side, batch, False)
+
+
+def _fused_conv_torgb_case(lib, mode, cin, cout, side, batch, last):
     code, dt = MODE_CODES[mode]
     g = torch.Generator().manual_seed(21)
     x = torch.randn(batch, cin, side, side, dtype=F64, generator=g)

@@ -7,6 +7,7 @@ import numpy as np
 import torch
 
 sys.path.insert(0, str(Path(__file__).resolve().parents[1]))
+from gance_b200 import _lib  # noqa: E402
 from gance_b200.networks.generator_spec import GeneratorSpec, random_init_variables  # noqa: E402
 from gance_b200.synthesis import GeneratorOnDevice  # noqa: E402
 
@@ -21,7 +22,14 @@ def main() -> None:
     ap.add_argument("--iters", type=int, default=5)
     ap.add_argument("--perturbed", action="store_true", help="non-zero noise strengths / biases (what bench.py runs)")
     ap.add_argument("--noise", default="const", choices=["const", "random", "none"])
+    ap.add_argument("--library", default=None, help="an alternative build of the library (measurement variants of csrc/build.py)")
+    ap.add_argument("--pairing", type=int, default=None, choices=[0, 1, 2], help="gance_set_conv_pairing")
+    ap.add_argument("--only", default=None, help="print only layers whose name contains this")
     args = ap.parse_args()
+    if args.library:
+        _lib.LIBRARY_PATH = Path(args.library).resolve()
+    if args.pairing is not None:
+        _lib.load_library().gance_set_conv_pairing(args.pairing)
     device = torch.device("cuda", 0)
     torch.cuda.set_device(device)
     spec = GeneratorSpec(args.resolution)
@@ -58,6 +66,8 @@ def main() -> None:
     for name, samples in totals.items():
         ms = float(np.median(samples))
         total_ms += ms
+        if args.only and args.only not in name:
+            continue
         flops, traffic = layer_info.get(name, (0, 0))
         tf = flops * args.batch / (ms * 1e-3) / 1e12
         gbs = traffic * args.batch / (ms * 1e-3) / 1e9
