@@ -12,7 +12,7 @@ from pathlib import Path
 from typing import List
 
 CSRC = Path(__file__).resolve().parent
-SOURCES = ["runtime.cu", "synthesis_kernels.cu", "modconv_tc.cu", "modconv_tf32.cu", "upconv_phase.cu", "upconv_fused.cu", "audio_kernels.cu", "resize_kernels.cu"]
+SOURCES = ["runtime.cu", "synthesis_kernels.cu", "modconv_tc.cu", "modconv_tf32.cu", "upconv_phase.cu", "upconv_fused.cu", "upconv_fused_pair.cu", "audio_kernels.cu", "resize_kernels.cu"]
 # Measurement builds, never the product: GANCE_PIPE_STATS=1 -> libgance_b200_stats.so (cycle counters per warp role,
 # tools/pipe_stats.py); GANCE_VARIANT=name:MACRO[,MACRO...] -> libgance_b200_<name>.so with -DMACRO... (ablations of the
 # epilogues, tools/ablate.sh).

@@ -273,10 +273,19 @@ __device__ __forceinline__ uint32_t pack_pair(float a, float b, __nv_bfloat16*) 
 //   channels 32*chunk + 8*j + 2*(t%4) + e    (j in 0..3, e in {0,1})
 // The ToRGB sum over channels is finished with a two-step reduce-scatter over the four lanes that share a row
 // (9 shuffles), which leaves row rr on lane t%4 == rr: every lane then adds the skip connection for ONE pixel.
-template <typename T, int N_TILE, int C, bool UP, bool RGB, int GROUPS, int TILE_W_LOG2 = -1, bool PAIR = false, int APG = 1>
+// STAGED (folded up-convolution with C = 32 on 8-wide tiles only): the warp's 8 x 16 output pixels are written to its own
+// 8 KB shared-memory tile and leave with ONE TMA store per tile instead of 32 sector-sized global stores per thread (the
+// L1 store path takes one sector per clock; ablation, round 2: 0.36 of that layer's 0.99 ms were its global stores).
+// The tile is addressed as 8 rows x 8 pixel PAIRS of 128 bytes under the 128-byte swizzle - `tmap_out` views the
+// [B,H,W,32] tensor as [B,H,W/2,64] - which spreads a store instruction's 32 x 8 bytes over all banks twice (optimal).
+template <typename T, int N_TILE, int C, bool UP, bool RGB, int GROUPS, int TILE_W_LOG2 = -1, bool PAIR = false, int APG = 1,
+          bool STAGED = false>
 __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int group, int warp, int lane, int total_tiles,
                                                    uint32_t tmem_base, uint64_t* tmem_full_bar,
-                                                   uint64_t* tmem_empty_bar) {
+                                                   uint64_t* tmem_empty_bar, uint8_t* stage_tile = nullptr,
+                                                   const CUtensorMap* tmap_out = nullptr) {
+    static_assert(!STAGED || (UP && C == 32 && TILE_W_LOG2 == 3 && !RGB), "staged output: folded up-convolution, 32 channels");
+    const uint32_t stage_addr = STAGED ? smem_u32(stage_tile) : 0u;
     // PAIR: `total_tiles` counts pair items (the host guarantees an even m-tile count: no ghost tiles here), walked
     // cluster by cluster; the drained accumulator is reported to the leader's barrier
     const int pair_rank = PAIR ? (int)cluster_ctarank() : 0;
@@ -474,6 +483,10 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
 #pragma unroll
         for (int rr = 0; rr < 4; ++rr) rgb[rr][0] = rgb[rr][1] = rgb[rr][2] = 0.f;
 
+        if (STAGED) {  // the previous tile's TMA store has read the staging tile
+            if (lane == 0) tma_store_wait_read();
+            __syncwarp();
+        }
 #ifdef GANCE_PIPE_STATS
         const long long stat_w0 = clock64();
 #endif
@@ -523,7 +536,22 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
                             v[2 * j + e] = o * cs[k];
                         }
                     }
-                    if (has_out) {
+                    if (STAGED) {
+                        // tile-local output pixel (2 * rr + py, 2 * r8 + px): row of the staging tile = 8 * (2 rr + py) + r8,
+                        // 16-byte chunk = 4 * px + channel group, XOR-swizzled by the row's low three bits (= r8)
+                        const bool odd = (q4 & 1) != 0;
+                        const uint32_t row_addr = stage_addr + (uint32_t)((8 * (2 * rr + (phase >> 1)) + r8) * 128 + 4 * (q4 & 2));
+#pragma unroll
+                        for (int j = 0; j < 4; j += 2) {
+                            const uint32_t w0 = pack_pair(v[2 * j], v[2 * j + 1], (T*)nullptr);
+                            const uint32_t w1 = pack_pair(v[2 * j + 2], v[2 * j + 3], (T*)nullptr);
+                            const uint32_t got = __shfl_xor_sync(0xffffffffu, odd ? w0 : w1, 1);
+                            const uint32_t c16 = (uint32_t)((4 * (phase & 1) + j + (odd ? 1 : 0)) ^ r8);
+                            asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(row_addr + (c16 << 4)), "r"(odd ? got : w0),
+                                         "r"(odd ? w1 : got)
+                                         : "memory");
+                        }
+                    } else if (has_out) {
                         const int h = t.h0 + hl[rr], w = t.w0 + wl[rr];
                         const int oh = UP ? 2 * h + (phase >> 1) : h, ow = UP ? 2 * w + (phase & 1) : w;
                         // The fragment layout leaves a lane with one channel PAIR (4 bytes) of each of four 8-channel groups.
@@ -548,10 +576,15 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
             }
         }
         tcgen05_fence_before();
+        if (STAGED) fence_proxy_async_smem();  // this thread's st.shared -> visible to the TMA unit
         __syncwarp();
         if (lane == 0) {  // accumulator drained
             if (PAIR) mbar_arrive_cluster(leader_empty_base + (uint32_t)(acc * 8));
             else mbar_arrive(tmem_empty_bar + acc);
+            if (STAGED) {  // the warp's 8 output rows x 16 pixels x 32 channels: rows 2 * (h0 + 4 * quarter) .., pixel pair w0 ..
+                tma_store_4d(tmap_out, stage_tile, 0, t.w0, 2 * (t.h0 + 4 * quarter), b);
+                tma_store_commit();
+            }
         }
         if (RGB) {
             // reduce-scatter over the 4 lanes of a row group: xor 1 settles s, xor 2 settles h2
@@ -592,6 +625,7 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
             }
         }
     }
+    if (STAGED && lane == 0) tma_store_wait_read();  // shared memory must outlive the last store's read
 #ifdef GANCE_PIPE_STATS
     if (!PAIR && p.pipe_stats != nullptr && (warp & 3) == 0 && lane == 0 && group < 2) {
         p.pipe_stats[blockIdx.x * 8 + 5 + group] = stat_wait;  // epilogue group: waiting for a finished accumulator
@@ -654,9 +688,12 @@ modconv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             uint32_t phase = 0;
             for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
                 const TileCoord t = decode_tile(p, tile, N_TILE);
-                for (int tap = 0; tap < 9; ++tap) {
-                    const int dy = tap / 3 - p.pad, dx = tap % 3 - p.pad;
-                    for (int kc = 0; kc < p.k_chunks; ++kc) {
+                // K is walked channel chunk by channel chunk, the nine taps inside: the order of every 3x3 kernel of this
+                // library (generic, CTA-pair and halo flavours accumulate in the same order, so a frame's bits do not
+                // depend on which flavour the batch size selects)
+                for (int kc = 0; kc < p.k_chunks; ++kc) {
+                    for (int tap = 0; tap < 9; ++tap) {
+                        const int dy = tap / 3 - p.pad, dx = tap % 3 - p.pad;
                         mbar_wait(empty_bar + stage, phase ^ 1u);
                         uint8_t* a_dst = smem + stage * L::kStageBytes;
                         uint8_t* b_dst = a_dst + L::kABytes;
@@ -802,9 +839,9 @@ modconv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_
         for (int item = first_item; item < total_items; item += item_stride) {
             bool ghost;
             const TileCoord t = decode_pair_item(p, item, rank, N_TILE, ghost);
-            for (int tap = 0; tap < 9; ++tap) {
-                const int dy = tap / 3 - p.pad, dx = tap % 3 - p.pad;
-                for (int kc = 0; kc < p.k_chunks; ++kc) {
+            for (int kc = 0; kc < p.k_chunks; ++kc) {
+                for (int tap = 0; tap < 9; ++tap) {
+                    const int dy = tap / 3 - p.pad, dx = tap % 3 - p.pad;
                     mbar_wait(empty_bar + stage, phase ^ 1u);
                     uint8_t* a_dst = smem + stage * L::kStageBytes;
                     uint8_t* b_dst = a_dst + L::kABytes;
@@ -1116,13 +1153,18 @@ struct HaloPairSmem {
     static constexpr int kAccs = kHaloApg * kEpilogueGroups;        // TMEM accumulator buffers
     static constexpr int kCacheOffset = kBarrierOffset + ((2 * STAGES + 2 * kAccs + 1) * 8 + 16 + 15) / 16 * 16;
     static constexpr int kCacheFloat4 = 2 * N_GEMM;                 // per epilogue group (row-per-thread epilogue only)
-    static constexpr int kBytes = kCacheOffset + kEpilogueGroups * kCacheFloat4 * 16 + 1024;
+    // after the barriers: the coefficient cache of the row-per-thread epilogue (UP = false, 128 channels) or the staging
+    // tiles of the TMA-stored output (folded up-convolution: 8 KB per epilogue warp, 1024-byte aligned)
+    static constexpr int kStageTileBytes = 8 * 8 * 128;
+    static constexpr int kStageOffset = (kCacheOffset + 1023) / 1024 * 1024;
+    static constexpr int kBytesCache = kCacheOffset + kEpilogueGroups * kCacheFloat4 * 16 + 1024;
+    static constexpr int kBytesStaged = kStageOffset + kEpilogueGroups * 4 * kStageTileBytes + 1024;
 };
 
 template <typename T, int N_GEMM, int CIN, int STAGES, bool UP, bool RGB>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 modconv3x3_halo_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
-                            const ConvParams p) {
+                            const __grid_constant__ CUtensorMap tmap_out, const ConvParams p) {
     using L = HaloPairSmem<N_GEMM, CIN, STAGES>;
     constexpr int C = UP ? N_GEMM / 4 : N_GEMM;  // channels of the output tensor
     constexpr bool kFrag = C <= 64;              // register-resident coefficients (fragment-layout epilogue)
@@ -1130,7 +1172,8 @@ modconv3x3_halo_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __
     static_assert(CIN == 64 || CIN == 128, "64-channel K chunks");
     static_assert((kTmemCols & (kTmemCols - 1)) == 0 && kTmemCols <= 512 && kTmemCols >= 32, "TMEM columns must be a power of two");
     static_assert(L::kTapBytes % 1024 == 0, "weight blocks must stay 1024-byte aligned");
-    static_assert(L::kBytes <= 227 * 1024, "shared memory");
+    constexpr bool kStaged = UP && C == 32;      // output through shared memory + TMA store (see conv_epilogue_frag)
+    static_assert((kStaged ? L::kBytesStaged : L::kBytesCache) <= 227 * 1024, "shared memory");
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -1149,6 +1192,7 @@ modconv3x3_halo_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tmap_x);
         prefetch_tmap(&tmap_w);
+        if (kStaged) prefetch_tmap(&tmap_out);
         for (int i = 0; i < STAGES; ++i) {
             mbar_init(full_bar + i, 1);
             mbar_init(empty_bar + i, 1);
@@ -1247,8 +1291,9 @@ modconv3x3_halo_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __
         }
     } else {
         if constexpr (kFrag)
-            conv_epilogue_frag<T, N_GEMM, C, UP, RGB, kEpilogueGroups, 3, true, kHaloApg>(p, (warp - 2) >> 2, warp, lane, total_items, tmem_base,
-                                                                               tmem_full_bar, tmem_empty_bar);
+            conv_epilogue_frag<T, N_GEMM, C, UP, RGB, kEpilogueGroups, 3, true, kHaloApg, kStaged>(
+                p, (warp - 2) >> 2, warp, lane, total_items, tmem_base, tmem_full_bar, tmem_empty_bar,
+                smem + L::kStageOffset + (warp - 2) * L::kStageTileBytes, &tmap_out);
         else
             conv_epilogue<T, N_GEMM, UP, RGB, kEpilogueGroups, L::kCacheFloat4, true, kHaloApg>(
                 p, (warp - 2) >> 2, warp, lane, total_items, tmem_base, tmem_full_bar, tmem_empty_bar,
@@ -1514,13 +1559,19 @@ static int pair_cluster_capacity(K kernel, int smem_bytes) {
     return n;
 }
 
+template <int N_GEMM, int CIN, int STAGES, bool UP>
+constexpr int halo_pair_smem_bytes() {
+    using L = HaloPairSmem<N_GEMM, CIN, STAGES>;
+    return (UP && N_GEMM == 128) ? L::kBytesStaged : L::kBytesCache;
+}
+
 template <typename T, int N_GEMM, int CIN, int STAGES, bool UP, bool RGB>
 static int configure_halo_pair_one(int* clusters) {
-    using L = HaloPairSmem<N_GEMM, CIN, STAGES>;
+    constexpr int kBytes = halo_pair_smem_bytes<N_GEMM, CIN, STAGES, UP>();
     auto kernel = modconv3x3_halo_pair_kernel<T, N_GEMM, CIN, STAGES, UP, RGB>;
-    int rc = raise_smem_limit(kernel, L::kBytes, "modconv3x3_halo_pair");
+    int rc = raise_smem_limit(kernel, kBytes, "modconv3x3_halo_pair");
     if (rc != GANCE_OK) return rc;
-    const int n = pair_cluster_capacity(kernel, L::kBytes);
+    const int n = pair_cluster_capacity(kernel, kBytes);
     if (n < *clusters) *clusters = n;
     return GANCE_OK;
 }
@@ -1540,14 +1591,25 @@ static int configure_halo_pair(int* clusters) {
 
 template <typename T, int N_GEMM, int CIN, int STAGES, bool UP>
 static int launch_halo_pair_typed(const ConvParams& p, const void* x, const void* weight, int max_clusters, cudaStream_t stream) {
-    using L = HaloPairSmem<N_GEMM, CIN, STAGES>;
+    constexpr int kBytes = halo_pair_smem_bytes<N_GEMM, CIN, STAGES, UP>();
     constexpr bool kHalf = std::is_same<T, __half>::value;
-    CUtensorMap tmap_x, tmap_w;
+    CUtensorMap tmap_x, tmap_w, tmap_out;
     {
         cuuint64_t dims[4] = {(cuuint64_t)CIN, (cuuint64_t)p.w_out, (cuuint64_t)p.h_out, (cuuint64_t)p.batch};
         cuuint64_t strides[3] = {(cuuint64_t)CIN * 2, (cuuint64_t)p.w_out * CIN * 2, (cuuint64_t)p.h_out * p.w_out * CIN * 2};
         cuuint32_t box[4] = {64u, (cuuint32_t)kHaloW, (cuuint32_t)kHaloH, 1u};
         int rc = make_tmap(&tmap_x, x, kHalf, 4, dims, strides, box, 128);
+        if (rc != GANCE_OK) return rc;
+    }
+    tmap_out = tmap_x;  // unused unless the output is staged
+    if constexpr (UP && N_GEMM == 128) {
+        // output [B, 2H, 2W, 32] seen as [B, 2H, W, 64]: one 128-byte row = two neighbouring pixels; a warp's tile is
+        // 8 rows x 8 pixel pairs
+        const cuuint64_t oh = 2ull * p.h_out, ow_pairs = (cuuint64_t)p.w_out;
+        cuuint64_t dims[4] = {64ull, ow_pairs, oh, (cuuint64_t)p.batch};
+        cuuint64_t strides[3] = {128ull, ow_pairs * 128ull, oh * ow_pairs * 128ull};
+        cuuint32_t box[4] = {64u, 8u, 8u, 1u};
+        int rc = make_tmap(&tmap_out, p.out, kHalf, 4, dims, strides, box, 128);
         if (rc != GANCE_OK) return rc;
     }
     {
@@ -1560,12 +1622,12 @@ static int launch_halo_pair_typed(const ConvParams& p, const void* x, const void
     const int items = (p.tiles_b * p.tiles_h * p.tiles_w) / 2;
     const int clusters = items < max_clusters ? items : max_clusters;
     if constexpr (UP) {
-        modconv3x3_halo_pair_kernel<T, N_GEMM, CIN, STAGES, true, false><<<2 * clusters, kThreads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
+        modconv3x3_halo_pair_kernel<T, N_GEMM, CIN, STAGES, true, false><<<2 * clusters, kThreads, kBytes, stream>>>(tmap_x, tmap_w, tmap_out, p);
     } else {
         if (p.rgb_weight != nullptr)
-            modconv3x3_halo_pair_kernel<T, N_GEMM, CIN, STAGES, false, true><<<2 * clusters, kThreads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
+            modconv3x3_halo_pair_kernel<T, N_GEMM, CIN, STAGES, false, true><<<2 * clusters, kThreads, kBytes, stream>>>(tmap_x, tmap_w, tmap_out, p);
         else
-            modconv3x3_halo_pair_kernel<T, N_GEMM, CIN, STAGES, false, false><<<2 * clusters, kThreads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
+            modconv3x3_halo_pair_kernel<T, N_GEMM, CIN, STAGES, false, false><<<2 * clusters, kThreads, kBytes, stream>>>(tmap_x, tmap_w, tmap_out, p);
     }
     return check_launch("modconv3x3_halo_pair_kernel");
 }
@@ -1597,6 +1659,8 @@ int encode_tensor_map_f32(CUtensorMap* map, const void* base, int rank, const cu
 int sm_count() { return g_num_sms; }
 int configure_phase_kernels();
 int configure_fused_kernels();
+int configure_fused_pair_kernels();
+int conv_pair_mode() { return g_pair_mode; }
 
 }  // namespace tc
 
@@ -1619,7 +1683,7 @@ int init_tensor_core_path() {
     if ((rc = tc::configure<32, 32, 8>()) != GANCE_OK) return rc;
     if ((rc = tc::configure_pair<256, 64, 6>(&tc::g_pair_clusters[0])) != GANCE_OK) return rc;
     if ((rc = tc::configure_pair<128, 64, 8>(&tc::g_pair_clusters[1])) != GANCE_OK) return rc;
-    if ((rc = tc::configure_halo_pair<128, 64, 4, true>(&tc::g_halo_pair_clusters[0])) != GANCE_OK) return rc;
+    if ((rc = tc::configure_halo_pair<128, 64, 3, true>(&tc::g_halo_pair_clusters[0])) != GANCE_OK) return rc;
     if ((rc = tc::configure_halo_pair<64, 64, 4, false>(&tc::g_halo_pair_clusters[1])) != GANCE_OK) return rc;
     if ((rc = tc::configure_halo_pair<128, 128, 3, false>(&tc::g_halo_pair_clusters[2])) != GANCE_OK) return rc;
     if ((rc = tc::configure_halo<128, 64, 2>()) != GANCE_OK) return rc;
@@ -1627,6 +1691,7 @@ int init_tensor_core_path() {
     if ((rc = tc::configure_halo<32, 32, 4>()) != GANCE_OK) return rc;
     if ((rc = tc::configure_phase_kernels()) != GANCE_OK) return rc;
     if ((rc = tc::configure_fused_kernels()) != GANCE_OK) return rc;
+    if ((rc = tc::configure_fused_pair_kernels()) != GANCE_OK) return rc;
     return GANCE_OK;
 }
 
@@ -1709,14 +1774,15 @@ static int launch_tensor_core_conv(const char* who, const void* x, int dtype, in
     const bool halo_shape = tc::g_use_halo && pad == 1 && w_out % tc::kHaloTileW == 0 && h_out % tc::kHaloTileH == 0;
     const int halo_m_tiles = halo_shape ? batch * (w_out / tc::kHaloTileW) * (h_out / tc::kHaloTileH) : 0;
     // CTA pairs for the halo layers: even m-tile count, and (unless forced) one work item per co-resident pair. Measured
-    // (round 2, batch 32): the 128 -> 128 layer gains 14 % (660 -> 580 us: it leaves the L2-bound generic kernel), but the
-    // two 64-channel layers LOSE (512^2 Conv1 690 -> 810 us, folded 1024^2 up-convolution 990 -> 1050 us): their tiles are
-    // 18-36 MMAs long and every accumulator hand-over now crosses the SM pair. Those two pair only when forced (mode 2).
+    // (round 2, batch 32): the 128 -> 128 layer gains 14 % (660 -> 580 us: it leaves the L2-bound generic kernel); the folded
+    // 1024^2 up-convolution, whose pair flavour has the shared memory to stage its output for TMA stores, 3 % (907 -> 877 us:
+    // that layer now moves its 3.3 GB at 3.8 TB/s); the 512^2 Conv1 LOSES (680 -> 800 us: its tiles are 36 short MMAs and
+    // every accumulator hand-over crosses the SM pair) and pairs only when forced (mode 2).
     auto halo_pair_ok = [&](int which) {
         const int clusters = tc::g_halo_pair_clusters[which];
         if (tc::g_pair_mode == 0 || clusters <= 0 || halo_m_tiles % 2 != 0) return false;
         if (tc::g_pair_mode == 2) return true;
-        return which == 2 && halo_m_tiles / 2 >= clusters;
+        return which != 1 && halo_m_tiles / 2 >= clusters;
     };
     const bool wide_halo = halo_shape && c_in == 128 && c_out == 128 && !up && halo_pair_ok(2);
     if (wide_halo || (halo_shape &&
@@ -1728,7 +1794,7 @@ static int launch_tensor_core_conv(const char* who, const void* x, int dtype, in
         p.n_tiles = 1; p.k_chunks = 1;
         if (wide_halo) return tc::launch_halo_pair<128, 128, 3, false>(half_operands, p, x, weight, tc::g_halo_pair_clusters[2], s);
         if (c_in == 64 && c_out == 128 && halo_pair_ok(0))
-            return tc::launch_halo_pair<128, 64, 4, true>(half_operands, p, x, weight, tc::g_halo_pair_clusters[0], s);
+            return tc::launch_halo_pair<128, 64, 3, true>(half_operands, p, x, weight, tc::g_halo_pair_clusters[0], s);
         if (c_in == 64 && c_out == 64 && halo_pair_ok(1))
             return tc::launch_halo_pair<64, 64, 4, false>(half_operands, p, x, weight, tc::g_halo_pair_clusters[1], s);
         if (c_in == 32) return tc::launch_halo<32, 32, 4>(half_operands, p, x, weight, s);

@@ -172,6 +172,19 @@ __device__ __forceinline__ void tmem_ld_16x256b_x4(uint32_t taddr, uint32_t (&r)
         : "r"(taddr)
         : "memory");
 }
+// ---- TMA store (shared -> global) -----------------------------------------------------------------------------------
+// Writes of the generic proxy (st.shared) become visible to the async proxy (the TMA unit) only after this fence.
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* m, const void* src, int c0, int c1, int c2, int c3) {
+    asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(
+                     reinterpret_cast<uint64_t>(m)),
+                 "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+                 : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// the bulk stores committed by this thread have READ their shared-memory source (it may be overwritten)
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+
 // ---- CTA pair (cta_group::2): two CTAs of a cluster on the two SMs of one TPC share one M = 256 MMA -----------------
 // Pattern (CUTLASS sm100 2-SM kernels): each CTA loads its own 128 accumulator rows of A and HALF of the B tile into its
 // own shared memory; every TMA of the pair signals the LEADER's (cluster rank 0) full barrier; the leader alone issues

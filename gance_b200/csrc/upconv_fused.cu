@@ -140,12 +140,14 @@ upconv_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
             int nt, b, ty, tx;
             fused_decode(p, tile, nt, b, ty, tx);
             const int h0 = ty * (kFuCellsH - 2) - 1, w0 = tx * (kFuCellsW - 2) - 1;
+            // K chunk by K chunk, the four shifts inside: the accumulation order of upconv_fused_pair.cu, so the two forms
+            // produce the same bits
+            for (int kc = 0; kc < p.k_chunks; ++kc) {
 #pragma unroll
-            for (int sh = 0; sh < 4; ++sh) {
-                const int dy = sh & 1, dx = sh >> 1;
-                const int nblk = sh == 0 ? 4 : (sh == 3 ? 1 : 2);
-                const int row0 = (sh == 0 ? 0 : sh == 1 ? 4 : sh == 2 ? 6 : 8) * p.c_out + nt * nblk * CC;
-                for (int kc = 0; kc < p.k_chunks; ++kc) {
+                for (int sh = 0; sh < 4; ++sh) {
+                    const int dy = sh & 1, dx = sh >> 1;
+                    const int nblk = sh == 0 ? 4 : (sh == 3 ? 1 : 2);
+                    const int row0 = (sh == 0 ? 0 : sh == 1 ? 4 : sh == 2 ? 6 : 8) * p.c_out + nt * nblk * CC;
                     mbar_wait(empty_bar + stage, phase ^ 1u);
                     uint8_t* a_dst = smem + stage * L::kStageBytes;
                     if (leader) {
@@ -175,12 +177,12 @@ upconv_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
             mbar_wait(tmem_empty_bar + acc, acc_phase ^ 1u);
             tcgen05_fence_after();
+            for (int kc = 0; kc < p.k_chunks; ++kc) {
 #pragma unroll
-            for (int sh = 0; sh < 4; ++sh) {
-                const uint32_t idesc = sh == 0 ? idesc4 : (sh == 3 ? idesc1 : idesc2);
-                const int first_block = sh == 0 ? 0 : (sh == 1 ? 0 : 1);
-                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * 4 * CC + first_block * CC);
-                for (int kc = 0; kc < p.k_chunks; ++kc) {
+                for (int sh = 0; sh < 4; ++sh) {
+                    const uint32_t idesc = sh == 0 ? idesc4 : (sh == 3 ? idesc1 : idesc2);
+                    const int first_block = sh == 0 ? 0 : (sh == 1 ? 0 : 1);
+                    const uint32_t d_tmem = tmem_base + (uint32_t)(acc * 4 * CC + first_block * CC);
                     mbar_wait(full_bar + stage, phase);
                     tcgen05_fence_after();
                     const uint64_t a_desc = make_smem_desc<128>(smem_base + (uint32_t)(stage * L::kStageBytes));
@@ -423,6 +425,14 @@ int configure_fused_kernels() {
     return GANCE_OK;
 }
 
+// upconv_fused_pair.cu: CTA pairs + one activation halo box per K chunk, for the wide layers
+template <typename T>
+int launch_fused_pair(const void* x, int batch, int h_in, int w_in, int c_in, int c_out, const void* weight_phase,
+                      const float* demod, const float* noise, long long noise_batch_stride, float noise_strength,
+                      const float* bias, const float* next_styles, void* out, cudaStream_t stream);
+int fused_pair_clusters();
+int conv_pair_mode();
+
 }  // namespace tc
 }  // namespace gance
 
@@ -441,6 +451,18 @@ extern "C" int gance_modconv3x3_up2_fused(const void* x, int dtype, int batch, i
     GANCE_REQUIRE(aligned16(x) && aligned16(weight_phase) && aligned16(out), GANCE_E_ALIGN,
                   "gance_modconv3x3_up2_fused: pointers must be 16-byte aligned");
     cudaStream_t s = (cudaStream_t)stream;
+    // Wide layers (Cin >= 256) are bound by what the producer pulls through L2: CTA pairs + halo boxes (upconv_fused_pair.cu)
+    // when a layer fills the co-resident pairs (or whenever eligible in pairing mode 2)
+    if (c_in >= 256 && c_out % 64 == 0 && h_in >= 32 && w_in >= 32 && tc::conv_pair_mode() != 0 && tc::fused_pair_clusters() > 0) {
+        const long long m_tiles = (long long)batch * ((2 * h_in + 27) / 28) * ((2 * w_in + 11) / 12);
+        if (tc::conv_pair_mode() == 2 || ((m_tiles + 1) / 2) * (c_out / 64) >= tc::fused_pair_clusters()) {
+            if (dtype == GANCE_F16)
+                return tc::launch_fused_pair<__half>(x, batch, h_in, w_in, c_in, c_out, weight_phase, demod, noise,
+                                                     noise_batch_stride, noise_strength, bias, next_styles, out, s);
+            return tc::launch_fused_pair<__nv_bfloat16>(x, batch, h_in, w_in, c_in, c_out, weight_phase, demod, noise,
+                                                        noise_batch_stride, noise_strength, bias, next_styles, out, s);
+        }
+    }
     if (c_out == 32) {
         if (dtype == GANCE_F16)
             return tc::launch_fused<__half, 32>(x, batch, h_in, w_in, c_in, c_out, weight_phase, demod, noise,

@@ -677,8 +677,11 @@ class Arrival:
     def synchronize(self) -> None:
         self.event.synchronize()
         if int(self.flag[0]) != 0:
+            # batches still in flight on other streams would set the sticky device flag again after it is cleared
+            torch.cuda.synchronize(self.generator.device)
             self.flag.zero_()
             self.generator.nonfinite.zero_()
+            torch.cuda.synchronize(self.generator.device)
             raise nonfinite_error(self.generator.mode)
 
     def query(self) -> bool:
@@ -870,6 +873,10 @@ class BatchRenderer:
     def _collect(self, slot: int, n: int) -> np.ndarray:
         self.done[slot].synchronize()
         if int(self.flags_host[slot][0]) != 0:
+            # later batches of this renderer are still running on the other slots' streams and would set the (device-wide,
+            # sticky) flag again after it has been cleared: let everything finish first, so that the report leaves a clean flag
+            torch.cuda.synchronize(self.generator.device)
             self.generator.nonfinite.zero_()
+            torch.cuda.synchronize(self.generator.device)
             raise nonfinite_error(self.generator.mode)
         return self.frames_host[slot][:n].numpy()
