@@ -31,7 +31,6 @@ constexpr int kFuOutW = 2 * (kFuCellsW - 2), kFuOutH = 2 * (kFuCellsH - 2);  // 
 constexpr int kFuTW = 2 * kFuCellsW, kFuTH = 2 * kFuCellsH;    // 32 x 16 pixel patch of t
 constexpr int kFuK = 64;                                       // input channels per pipeline stage
 constexpr int kFuABytes = kTileM * kFuK * 2;                   // 16 KB
-constexpr int kFuEpilogueThreads = 256;
 
 template <int CC>
 struct FusedLayout {
@@ -87,18 +86,33 @@ __device__ __forceinline__ uint2 pack4(const float (&v)[4], __nv_bfloat16*) {
     return make_uint2(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b));
 }
 
+// Eight epilogue warps. Sixteen (each thread filtering half of the rows; -DGANCE_ABL_FU_EW16 builds it) were measured 5 %
+// SLOWER on the layer the filter step bounds (256^2 -> 512^2: 750 vs 715 us): the step is not short of warps but of
+// shared-memory bandwidth - every row group re-reads three warm-up rows of the patch (ncu: LSU + tensor-core wavefronts
+// together ~60 % of the shared-memory pipe, next to the TMA writes).
+#ifdef GANCE_ABL_FU_EW16
+__host__ __device__ constexpr int fused_epilogue_warps(int cc) { return cc == 64 ? 16 : 8; }
+#else
+__host__ __device__ constexpr int fused_epilogue_warps(int) { return 8; }
+#endif
+
+template <int THREADS>
 __device__ __forceinline__ void epilogue_barrier() {
-    asm volatile("bar.sync 1, %0;" ::"n"(kFuEpilogueThreads) : "memory");
+    asm volatile("bar.sync 1, %0;" ::"n"(THREADS) : "memory");
 }
 
-template <typename T, int CC>
-__global__ void __launch_bounds__(kThreads, 1)
+// EW = epilogue warps (8; 16 is an A/B build, see fused_epilogue_warps).
+template <typename T, int CC, int EW>
+__global__ void __launch_bounds__(64 + EW * 32, 1)
 upconv_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
                     const FusedParams p) {
     using L = FusedLayout<CC>;
+    constexpr int kEpilogueThreads = EW * 32;
     constexpr int kChunks = CC / 8;        // 16-byte chunks per patch pixel
     constexpr int kQuads = CC / 4;         // 4-channel groups per pixel
-    constexpr int kRowSplit = 64 / CC;     // CC = 32: the 12 output rows are split over 2 thread groups
+    constexpr int kRowSplit = kEpilogueThreads / (kQuads * 16);  // row groups: 1 (CC = 64, 8 warps) or 2
+    constexpr int kDrainBlocks = 16 / EW;  // 64-/32-channel phase blocks each warp copies out of TMEM (its lane quarter)
+    static_assert(EW == 8 || EW == 16, "8 or 16 epilogue warps");
     constexpr int kRowsPerThread = kFuOutH / kRowSplit;
     constexpr int kInner = kRowsPerThread % 4 == 0 ? 4 : kRowsPerThread;  // rows per rolled iteration (window slots are static)
     extern __shared__ uint8_t smem_raw[];
@@ -120,7 +134,7 @@ upconv_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(tmem_full_bar + i, 1);
-            mbar_init(tmem_empty_bar + i, kFuEpilogueThreads / 32);
+            mbar_init(tmem_empty_bar + i, EW);
         }
         fence_barrier_init();
     }
@@ -207,7 +221,7 @@ upconv_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
         }
     } else {
         // ===== epilogue =====
-        const int ew = warp - 2, quarter = warp & 3, half = ew >> 2;
+        const int ew = warp - 2, quarter = warp & 3, part = ew >> 2;  // part: which of the EW / 4 column ranges this warp drains
         const int etid = ew * 32 + lane;
         const int row = quarter * 32 + lane;            // accumulator row = cell
         const int wl = row & (kFuCellsW - 1), hl = row / kFuCellsW;
@@ -259,13 +273,13 @@ upconv_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
             //      coefficient is applied after it, folded into the filter's 1/16 normalisation) ----
             mbar_wait(tmem_full_bar + acc, full_phase);
             tcgen05_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * 4 * CC + half * 2 * CC);
+            const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * 4 * CC + part * kDrainBlocks * CC);
 #ifdef GANCE_ABL_FU_NODRAIN
             if (p.batch < 0)  // ablation: the accumulator is not copied to the patch
 #endif
 #pragma unroll
-            for (int blk = 0; blk < 2; ++blk) {
-                const int block = half * 2 + blk;                      // P01, P00 | P10, P11
+            for (int blk = 0; blk < kDrainBlocks; ++blk) {
+                const int block = part * kDrainBlocks + blk;           // P01, P00 | P10, P11
                 const int a = block >> 1, bb = (block == 0 || block == 3) ? 1 : 0;
                 const uint32_t pixel = patch + (uint32_t)(((2 * hl + a) * kFuTW + 2 * wl + bb) * L::kPixelBytes);
 #pragma unroll
@@ -291,7 +305,7 @@ upconv_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
             tcgen05_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tmem_empty_bar + acc);
-            epilogue_barrier();
+            epilogue_barrier<kEpilogueThreads>();
             // ---- (c) FIR + demod + noise + bias + lrelu + next style from the patch ----
 #ifdef GANCE_ABL_FU_NOFILTER
             if (rows_valid > 0 && p.batch < 0) {  // ablation: drain only
@@ -358,7 +372,7 @@ upconv_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
                     }
                 }
             }
-            epilogue_barrier();  // the patch is free for the next tile
+            epilogue_barrier<kEpilogueThreads>();  // the patch is free for the next tile
             acc ^= 1;
             if (acc == 0) full_phase ^= 1u;
         }
@@ -405,13 +419,13 @@ static int launch_fused(const void* x, int batch, int h_in, int w_in, int c_in, 
     }
     const long long total_tiles = (long long)batch * p.tiles_h * p.tiles_w * p.n_tiles;
     const int grid = total_tiles < sm_count() ? (int)total_tiles : sm_count();
-    upconv_fused_kernel<T, CC><<<grid, kThreads, L::kSmemBytes, stream>>>(tmap_x, tmap_w, p);
+    upconv_fused_kernel<T, CC, fused_epilogue_warps(CC)><<<grid, 64 + fused_epilogue_warps(CC) * 32, L::kSmemBytes, stream>>>(tmap_x, tmap_w, p);
     return check_launch("upconv_fused_kernel");
 }
 
 template <typename T, int CC>
 static cudaError_t configure_one() {
-    return cudaFuncSetAttribute(upconv_fused_kernel<T, CC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    return cudaFuncSetAttribute(upconv_fused_kernel<T, CC, fused_epilogue_warps(CC)>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 FusedLayout<CC>::kSmemBytes);
 }
 
