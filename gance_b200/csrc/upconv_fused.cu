@@ -467,7 +467,12 @@ extern "C" int gance_modconv3x3_up2_fused(const void* x, int dtype, int batch, i
     cudaStream_t s = (cudaStream_t)stream;
     // Wide layers (Cin >= 256) are bound by what the producer pulls through L2: CTA pairs + halo boxes (upconv_fused_pair.cu)
     // when a layer fills the co-resident pairs (or whenever eligible in pairing mode 2)
-    if (c_in >= 256 && c_out % 64 == 0 && h_in >= 32 && w_in >= 32 && tc::conv_pair_mode() != 0 && tc::fused_pair_clusters() > 0) {
+#ifdef GANCE_ABL_FP_CIN128
+    constexpr int kPairMinCin = 128;  // A/B build
+#else
+    constexpr int kPairMinCin = 256;
+#endif
+    if (c_in >= kPairMinCin && c_out % 64 == 0 && h_in >= 32 && w_in >= 32 && tc::conv_pair_mode() != 0 && tc::fused_pair_clusters() > 0) {
         const long long m_tiles = (long long)batch * ((2 * h_in + 27) / 28) * ((2 * w_in + 11) / 12);
         if (tc::conv_pair_mode() == 2 || ((m_tiles + 1) / 2) * (c_out / 64) >= tc::fused_pair_clusters()) {
             if (dtype == GANCE_F16)

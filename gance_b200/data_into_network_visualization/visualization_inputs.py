@@ -21,7 +21,7 @@ from gance_b200 import audio_device
 from gance_b200.apply_spectrogram import compute_spectrogram_smooth_scale_device
 from gance_b200.data_into_network_visualization.visualization_common import ResultLayers, VisualizationInput
 from gance_b200.vector_sources import vector_sources_common
-from gance_b200.vector_sources.primatives import Sigmas, gaussian_data
+from gance_b200.vector_sources.primatives import NoisePrefetch, Sigmas, gaussian_data
 from gance_b200.vector_sources.vector_reduction import quantize_results_layers, reduce_vector_rms_rolling_average
 from gance_b200.vector_sources.vector_types import (
     ConcatenatedMatrices,
@@ -83,10 +83,11 @@ def _create_spectrogram(
     return ConcatenatedVectors(device.reshape(-1).cpu().numpy())
 
 
-def _noise(vector_length: int, num_vectors: int) -> np.ndarray:
+def _noise(vector_length: int, num_vectors: int, prefetched: Optional[NoisePrefetch] = None) -> np.ndarray:
     """visualization_inputs.py:135-142: Gaussian-smoothed noise, min-max scaled to (-4, 4); float32, host."""
     return minmax_scale(
-        gaussian_data(vector_length=vector_length, num_vectors=num_vectors, sigmas=Sigmas(across_vectors=50, within_vectors=0)),
+        gaussian_data(vector_length=vector_length, num_vectors=num_vectors, sigmas=Sigmas(across_vectors=50, within_vectors=0),
+                      prefetched=prefetched),
         feature_range=(-4, 4),
     )
 
@@ -102,11 +103,11 @@ def _indices(time_series_audio_vectors, vector_length, network_indices, **savgol
 
 def alpha_blend_vectors_max_rms_power_audio_device(
     alpha: float, fft_roll_enabled: bool, fft_amplitude_range: Tuple[int, int], time_series_audio_vectors: np.ndarray,
-    vector_length: int, network_indices: List[int],
+    vector_length: int, network_indices: List[int], noise_prefetch: Optional[NoisePrefetch] = None,
 ) -> DeviceLatents:
     """noise-blend latents as float32 [T,512] on the device (the vector path's z)."""
     spectrogram = _create_spectrogram_device(time_series_audio_vectors, vector_length, fft_amplitude_range, fft_roll_enabled)
-    noise = _noise(vector_length, spectrogram.shape[0])
+    noise = _noise(vector_length, spectrogram.shape[0], noise_prefetch)
     _, latents = audio_device.alpha_blend_noise(spectrogram, noise, alpha, want_f64=False)
     indices = _indices(time_series_audio_vectors, vector_length, network_indices)
     return DeviceLatents(latents, np.asarray(indices.result.data), spectrogram)

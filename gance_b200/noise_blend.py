@@ -79,13 +79,35 @@ class TrackLatents(NamedTuple):
     network_indices: np.ndarray
 
 
+def prefetch_noise(wav: Sequence[WavInput], vector_length: int, output_fps: float):
+    """
+    Start drawing the noise source's random values (`primatives.NoisePrefetch`) from the WAV HEADERS alone - an upper bound
+    of the frame count is all the draw needs - so that it overlaps reading and resampling the audio. Returns None when a
+    header cannot be read (the values are then drawn where the reference draws them).
+    """
+    import wave
+
+    from gance_b200.vector_sources.primatives import NoisePrefetch
+
+    seconds = 0.0
+    try:
+        for item in wav:
+            if isinstance(item, music.WavFileProperties):
+                return None
+            with wave.open(str(item), "rb") as handle:
+                seconds += handle.getnframes() / float(handle.getframerate())
+    except (wave.Error, OSError, EOFError):
+        return None
+    return NoisePrefetch(vector_length, int(np.ceil(seconds * output_fps)) + 8)
+
+
 def noise_blend_latents(time_series_audio_vectors: ConcatenatedVectors, networks: MultiNetwork, alpha: float,
-                        fft_roll_enabled: bool, fft_amplitude_range: Tuple[int, int]) -> TrackLatents:
+                        fft_roll_enabled: bool, fft_amplitude_range: Tuple[int, int], noise_prefetch=None) -> TrackLatents:
     """z [T,512] float32 on the device + network index per frame, for the whole track (every rank computes the same)."""
     result = visualization_inputs.alpha_blend_vectors_max_rms_power_audio_device(
         alpha=alpha, fft_roll_enabled=fft_roll_enabled, fft_amplitude_range=fft_amplitude_range,
         time_series_audio_vectors=time_series_audio_vectors, vector_length=networks.expected_vector_length,
-        network_indices=networks.network_indices)
+        network_indices=networks.network_indices, noise_prefetch=noise_prefetch)
     return TrackLatents(result.latents, result.network_indices)
 
 

@@ -194,3 +194,22 @@ def test_eight_bit_pcm_reference_errors(tmp_path):
         with mock.patch.object(reference_music.wavfile, "read", return_value=(44100, data)):
             with pytest.raises(ValueError):
                 reference_music.read_wav_file(tmp_path / "x.wav")
+
+
+def test_prefetched_noise_values_are_the_serial_draw():
+    """`NoisePrefetch` (the RNG draw moved to a background thread, started from an upper bound of the track length) hands
+    `gaussian_data` bit for bit what `RandomState(1234).randn(T, 1, L)` returns - for T below, at and above the bound."""
+    from gance_b200.vector_sources import primatives
+
+    length = 64
+    for bound, count in ((40, 33), (40, 40), (40, 57), (0, 5)):
+        want = np.random.RandomState(primatives.DEFAULT_RANDOM_SEED).randn(count, 1, length).astype(np.float32)  # pylint: disable=no-member
+        got = primatives.NoisePrefetch(length, bound).take(count)
+        assert got.dtype == np.float32 and got.shape == want.shape and np.array_equal(got, want)
+        got[...] = 0  # writable, and not aliased with a later take
+    no_filter = primatives.Sigmas(across_vectors=0, within_vectors=0)
+    plain = primatives.gaussian_data(length, 33, no_filter)
+    ahead = primatives.gaussian_data(length, 33, no_filter, prefetched=primatives.NoisePrefetch(length, 48))
+    assert np.array_equal(plain, ahead)
+    other_length = primatives.gaussian_data(length, 33, no_filter, prefetched=primatives.NoisePrefetch(length * 2, 48))
+    assert np.array_equal(plain, other_length)  # a prefetch of the wrong shape is ignored

