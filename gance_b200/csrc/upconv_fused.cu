@@ -32,11 +32,13 @@ constexpr int kFuTW = 2 * kFuCellsW, kFuTH = 2 * kFuCellsH;    // 32 x 16 pixel 
 constexpr int kFuK = 64;                                       // input channels per pipeline stage
 constexpr int kFuABytes = kTileM * kFuK * 2;                   // 16 KB
 
-template <int CC>
+// PAIR: two CTAs (cta_group::2) share the MMAs of two tiles of one channel block; each holds HALF of a shift's weight rows,
+// so a stage is 16 + <= 16 KB instead of 16 + <= 32 KB and five of them fit beside the patch.
+template <int CC, bool PAIR = false>
 struct FusedLayout {
-    static constexpr int kStages = 3;  // measured at batch 32: 2 stages cost +6 % (Cin 128) to +31 % (Cin 512); a 4th (patch halved, two epilogue passes) gained < 4 % - profiles/README.md
+    static constexpr int kStages = PAIR ? 5 : 3;  // measured at batch 32 (single CTA): 2 stages cost +6 % (Cin 128) to +31 % (Cin 512); a 4th (patch halved, two epilogue passes) gained < 4 % - profiles/README.md
     static constexpr int kBBlock = CC * kFuK * 2;              // one phase block of the B operand
-    static constexpr int kStageBytes = kFuABytes + 4 * kBBlock;
+    static constexpr int kStageBytes = kFuABytes + (PAIR ? 2 : 4) * kBBlock;
     static constexpr int kPatchOffset = kStages * kStageBytes;
     static constexpr int kPixelBytes = CC * 2;
     static constexpr int kPatchBytes = kFuTW * kFuTH * kPixelBytes;
@@ -102,11 +104,15 @@ __device__ __forceinline__ void epilogue_barrier() {
 }
 
 // EW = epilogue warps (8; 16 is an A/B build, see fused_epilogue_warps).
-template <typename T, int CC, int EW>
+// PAIR (launched as 2-CTA clusters): the two CTAs take two tiles of the same channel block; TMA bytes of both are counted
+// on the leader's full barriers, the leader's MMA warp issues M = 256 MMAs for both, commits are multicast, the epilogue
+// warps of both CTAs report to the leader. Same K order, same filter arithmetic: same bits as the single-CTA flavour.
+template <typename T, int CC, int EW, bool PAIR>
 __global__ void __launch_bounds__(64 + EW * 32, 1)
 upconv_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
                     const FusedParams p) {
-    using L = FusedLayout<CC>;
+    using L = FusedLayout<CC, PAIR>;
+    static_assert(!PAIR || CC == 64, "the CTA-pair flavour exists for 64-channel blocks");
     constexpr int kEpilogueThreads = EW * 32;
     constexpr int kChunks = CC / 8;        // 16-byte chunks per patch pixel
     constexpr int kQuads = CC / 4;         // 4-channel groups per pixel
@@ -125,6 +131,7 @@ upconv_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
 
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
     const int lane = threadIdx.x & 31;
+    const int rank = PAIR ? (int)cluster_ctarank() : 0;
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tmap_x);
         prefetch_tmap(&tmap_w);
@@ -134,25 +141,48 @@ upconv_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(tmem_full_bar + i, 1);
-            mbar_init(tmem_empty_bar + i, EW);
+            mbar_init(tmem_empty_bar + i, PAIR ? 2 * EW : EW);
         }
         fence_barrier_init();
     }
-    if (warp == 1) tmem_alloc(tmem_base_slot, 512);
+    if (warp == 1) {
+        if (PAIR) tmem_alloc_pair(tmem_base_slot, 512);
+        else tmem_alloc(tmem_base_slot, 512);
+    }
     tcgen05_fence_before();
-    __syncthreads();
+    if (PAIR) cluster_sync_all();
+    else __syncthreads();
     tcgen05_fence_after();
     const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_base_slot, 0);
-    const int total_tiles = p.batch * p.tiles_h * p.tiles_w * p.n_tiles;
+    // work items: tiles (single CTA) or pairs of tiles of one channel block (PAIR), walked CTA by CTA / cluster by cluster
+    const int m_tiles = p.batch * p.tiles_h * p.tiles_w;
+    const int total_tiles = PAIR ? ((m_tiles + 1) >> 1) * p.n_tiles : m_tiles * p.n_tiles;
+    const int walk_first = PAIR ? (int)cluster_id_x() : (int)blockIdx.x;
+    const int walk_stride = PAIR ? (int)cluster_count_x() : (int)gridDim.x;
+    // item -> this CTA's tile; a PAIR's odd tile out is a ghost (sample index = batch: TMA zero-fills, nothing is stored)
+    auto decode = [&](int item, int& nt, int& b, int& ty, int& tx) {
+        if (!PAIR) {
+            fused_decode(p, item, nt, b, ty, tx);
+            return false;
+        }
+        nt = item % p.n_tiles;
+        int m = 2 * (item / p.n_tiles) + rank;
+        tx = m % p.tiles_w;
+        m /= p.tiles_w;
+        ty = m % p.tiles_h;
+        b = m / p.tiles_h;
+        return b >= p.batch;
+    };
 
     if (warp == 0) {
         // ===== TMA producer: per (shift, K chunk) one activation box + 4/2/2/1 weight blocks =====
         const bool leader = elect_one_sync();
         int stage = 0;
         uint32_t phase = 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const uint32_t full_leader = PAIR ? cluster_map(smem_u32(full_bar), 0) : 0u;
+        for (int tile = walk_first; tile < total_tiles; tile += walk_stride) {
             int nt, b, ty, tx;
-            fused_decode(p, tile, nt, b, ty, tx);
+            decode(tile, nt, b, ty, tx);
             const int h0 = ty * (kFuCellsH - 2) - 1, w0 = tx * (kFuCellsW - 2) - 1;
             // K chunk by K chunk, the four shifts inside: the accumulation order of upconv_fused_pair.cu, so the two forms
             // produce the same bits
@@ -165,11 +195,20 @@ upconv_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
                     mbar_wait(empty_bar + stage, phase ^ 1u);
                     uint8_t* a_dst = smem + stage * L::kStageBytes;
                     if (leader) {
-                        mbar_expect_tx(full_bar + stage, (uint32_t)(kFuABytes + nblk * L::kBBlock));
-                        tma_load_4d(a_dst, &tmap_x, full_bar + stage, kc * kFuK, w0 - dx, h0 - dy, b);
-                        for (int j = 0; j < nblk; ++j)
-                            tma_load_2d(a_dst + kFuABytes + j * L::kBBlock, &tmap_w, full_bar + stage, kc * kFuK,
-                                        row0 + j * CC);
+                        if (PAIR) {  // own activation box + own half of the shift's weight rows (in boxes of CC / 2 rows)
+                            if (rank == 0) mbar_expect_tx(full_bar + stage, 2u * (uint32_t)(kFuABytes + nblk * L::kBBlock / 2));
+                            const uint32_t bar = full_leader + (uint32_t)(stage * 8);
+                            tma_load_4d_pair(a_dst, &tmap_x, bar, kc * kFuK, w0 - dx, h0 - dy, b);
+                            for (int j = 0; j < nblk; ++j)
+                                tma_load_2d_pair(a_dst + kFuABytes + j * (L::kBBlock / 2), &tmap_w, bar, kc * kFuK,
+                                                 row0 + rank * (nblk * CC / 2) + j * (CC / 2));
+                        } else {
+                            mbar_expect_tx(full_bar + stage, (uint32_t)(kFuABytes + nblk * L::kBBlock));
+                            tma_load_4d(a_dst, &tmap_x, full_bar + stage, kc * kFuK, w0 - dx, h0 - dy, b);
+                            for (int j = 0; j < nblk; ++j)
+                                tma_load_2d(a_dst + kFuABytes + j * L::kBBlock, &tmap_w, full_bar + stage, kc * kFuK,
+                                            row0 + j * CC);
+                        }
                     }
                     __syncwarp();
                     if (++stage == L::kStages) {
@@ -179,16 +218,17 @@ upconv_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
                 }
             }
         }
-    } else if (warp == 1) {
-        // ===== MMA issuer =====
+    } else if (warp == 1 && rank == 0) {
+        // ===== MMA issuer (PAIR: the leader CTA's, for both) =====
         const bool leader = elect_one_sync();
         constexpr bool kHalf = !std::is_same<T, __nv_bfloat16>::value;
-        constexpr uint32_t idesc4 = make_instr_desc(kTileM, 4 * CC, kHalf), idesc2 = make_instr_desc(kTileM, 2 * CC, kHalf),
-                           idesc1 = make_instr_desc(kTileM, CC, kHalf);
+        constexpr int kM = PAIR ? 2 * kTileM : kTileM;
+        constexpr uint32_t idesc4 = make_instr_desc(kM, 4 * CC, kHalf), idesc2 = make_instr_desc(kM, 2 * CC, kHalf),
+                           idesc1 = make_instr_desc(kM, CC, kHalf);
         int stage = 0, acc = 0;
         uint32_t phase = 0, acc_phase = 0;
         const uint32_t smem_base = smem_u32(smem);
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        for (int tile = walk_first; tile < total_tiles; tile += walk_stride) {
             mbar_wait(tmem_empty_bar + acc, acc_phase ^ 1u);
             tcgen05_fence_after();
             for (int kc = 0; kc < p.k_chunks; ++kc) {
@@ -203,11 +243,17 @@ upconv_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
                     const uint64_t b_desc = a_desc + (uint64_t)(kFuABytes >> 4);
                     if (leader) {
 #pragma unroll
-                        for (int k = 0; k < kFuK / kUmmaK; ++k)
-                            umma_bf16(d_tmem, a_desc + (uint64_t)(k * 2), b_desc + (uint64_t)(k * 2), idesc,
-                                      (sh | kc | k) != 0 ? 1u : 0u);  // shift (0,0) touches every column first
-                        umma_commit(empty_bar + stage);
-                        if (sh == 3 && kc == p.k_chunks - 1) umma_commit(tmem_full_bar + acc);
+                        for (int k = 0; k < kFuK / kUmmaK; ++k) {  // shift (0,0) touches every column first
+                            if (PAIR) umma_bf16_pair(d_tmem, a_desc + (uint64_t)(k * 2), b_desc + (uint64_t)(k * 2), idesc, (sh | kc | k) != 0 ? 1u : 0u);
+                            else umma_bf16(d_tmem, a_desc + (uint64_t)(k * 2), b_desc + (uint64_t)(k * 2), idesc, (sh | kc | k) != 0 ? 1u : 0u);
+                        }
+                        if (PAIR) {
+                            umma_commit_pair(empty_bar + stage);
+                            if (sh == 3 && kc == p.k_chunks - 1) umma_commit_pair(tmem_full_bar + acc);
+                        } else {
+                            umma_commit(empty_bar + stage);
+                            if (sh == 3 && kc == p.k_chunks - 1) umma_commit(tmem_full_bar + acc);
+                        }
                     }
                     __syncwarp();
                     if (++stage == L::kStages) {
@@ -219,7 +265,7 @@ upconv_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
             acc ^= 1;
             if (acc == 0) acc_phase ^= 1u;
         }
-    } else {
+    } else if (warp >= 2) {
         // ===== epilogue =====
         const int ew = warp - 2, quarter = warp & 3, part = ew >> 2;  // part: which of the EW / 4 column ranges this warp drains
         const int etid = ew * 32 + lane;
@@ -245,9 +291,19 @@ upconv_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
         const size_t out_row_stride = (size_t)w_out * p.c_out;
         int acc = 0;
         uint32_t full_phase = 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const uint32_t leader_empty_base = PAIR ? cluster_map(smem_u32(tmem_empty_bar), 0) : 0u;
+        for (int tile = walk_first; tile < total_tiles; tile += walk_stride) {
             int nt, b, ty, tx;
-            fused_decode(p, tile, nt, b, ty, tx);
+            if (decode(tile, nt, b, ty, tx)) {  // ghost tile (PAIR, CTA-uniform): only the accumulator hand-shake
+                mbar_wait(tmem_full_bar + acc, full_phase);
+                tcgen05_fence_after();
+                tcgen05_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive_cluster(leader_empty_base + (uint32_t)(acc * 8));
+                acc ^= 1;
+                if (acc == 0) full_phase ^= 1u;
+                continue;
+            }
             // per-tile global operands of the filter step, requested BEFORE the TMEM wait so their latency hides behind
             // the accumulator drain (issued inside the row loop they cost ~600 exposed cycles per output row)
             const int c0 = nt * CC + quad * 4;
@@ -304,7 +360,10 @@ upconv_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
             }
             tcgen05_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(tmem_empty_bar + acc);
+            if (lane == 0) {
+                if (PAIR) mbar_arrive_cluster(leader_empty_base + (uint32_t)(acc * 8));
+                else mbar_arrive(tmem_empty_bar + acc);
+            }
             epilogue_barrier<kEpilogueThreads>();
             // ---- (c) FIR + demod + noise + bias + lrelu + next style from the patch ----
 #ifdef GANCE_ABL_FU_NOFILTER
@@ -379,10 +438,12 @@ upconv_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
     }
 
     tcgen05_fence_before();
-    __syncthreads();
+    if (PAIR) cluster_sync_all();  // neither CTA leaves while its partner can still read its shared memory or signal its barriers
+    else __syncthreads();
     if (warp == 1) {
         tcgen05_fence_after();
-        tmem_dealloc(tmem_base, 512);
+        if (PAIR) tmem_dealloc_pair(tmem_base, 512);
+        else tmem_dealloc(tmem_base, 512);
     }
 }
 
@@ -390,12 +451,14 @@ int encode_tensor_map(CUtensorMap* map, const void* base, bool half_operands, in
                       const cuuint64_t* strides_bytes, const cuuint32_t* box, int swizzle_bytes);
 int sm_count();
 
-template <typename T, int CC>
+static int g_fused_wide_pair_clusters = 0;  // co-resident 2-CTA clusters of the PAIR flavour (0 = unusable)
+
+template <typename T, int CC, bool PAIR = false>
 static int launch_fused(const void* x, int batch, int h_in, int w_in, int c_in, int c_out, const void* weight_phase,
                         const float* demod, const float* noise, long long noise_batch_stride, float noise_strength,
                         const float* bias, const float* next_styles, void* out, cudaStream_t stream) {
     constexpr bool kHalf = std::is_same<T, __half>::value;
-    using L = FusedLayout<CC>;
+    using L = FusedLayout<CC, PAIR>;
     FusedParams p;
     p.batch = batch; p.h_in = h_in; p.w_in = w_in; p.c_in = c_in; p.c_out = c_out;
     p.k_chunks = c_in / kFuK; p.n_tiles = c_out / CC;
@@ -413,20 +476,63 @@ static int launch_fused(const void* x, int batch, int h_in, int w_in, int c_in, 
     {
         cuuint64_t dims[2] = {(cuuint64_t)c_in, (cuuint64_t)9 * c_out};
         cuuint64_t strides[1] = {(cuuint64_t)c_in * 2};
-        cuuint32_t box[2] = {(cuuint32_t)kFuK, (cuuint32_t)CC};
+        cuuint32_t box[2] = {(cuuint32_t)kFuK, (cuuint32_t)(PAIR ? CC / 2 : CC)};  // PAIR: each CTA loads half of a block's rows
         int rc = encode_tensor_map(&tmap_w, weight_phase, kHalf, 2, dims, strides, box, 128);
         if (rc != GANCE_OK) return rc;
     }
-    const long long total_tiles = (long long)batch * p.tiles_h * p.tiles_w * p.n_tiles;
-    const int grid = total_tiles < sm_count() ? (int)total_tiles : sm_count();
-    upconv_fused_kernel<T, CC, fused_epilogue_warps(CC)><<<grid, 64 + fused_epilogue_warps(CC) * 32, L::kSmemBytes, stream>>>(tmap_x, tmap_w, p);
+    constexpr int kBlock = 64 + fused_epilogue_warps(CC) * 32;
+    if constexpr (PAIR) {
+        const long long m_tiles = (long long)batch * p.tiles_h * p.tiles_w;
+        const long long items = ((m_tiles + 1) / 2) * p.n_tiles;
+        const int clusters = items < g_fused_wide_pair_clusters ? (int)items : g_fused_wide_pair_clusters;
+        cudaLaunchConfig_t config = {};
+        config.gridDim = dim3(2 * clusters, 1, 1);
+        config.blockDim = dim3(kBlock, 1, 1);
+        config.dynamicSmemBytes = L::kSmemBytes;
+        config.stream = stream;
+        cudaLaunchAttribute attribute;
+        attribute.id = cudaLaunchAttributeClusterDimension;
+        attribute.val.clusterDim.x = 2; attribute.val.clusterDim.y = 1; attribute.val.clusterDim.z = 1;
+        config.attrs = &attribute;
+        config.numAttrs = 1;
+        cudaError_t err = cudaLaunchKernelEx(&config, upconv_fused_kernel<T, CC, fused_epilogue_warps(CC), true>, tmap_x, tmap_w, p);
+        if (err != cudaSuccess) return fail(-(int)err, "cudaLaunchKernelEx(upconv_fused_kernel<pair>): %s", cudaGetErrorString(err));
+    } else {
+        const long long total_tiles = (long long)batch * p.tiles_h * p.tiles_w * p.n_tiles;
+        const int grid = total_tiles < sm_count() ? (int)total_tiles : sm_count();
+        upconv_fused_kernel<T, CC, fused_epilogue_warps(CC), false><<<grid, kBlock, L::kSmemBytes, stream>>>(tmap_x, tmap_w, p);
+    }
     return check_launch("upconv_fused_kernel");
 }
 
 template <typename T, int CC>
 static cudaError_t configure_one() {
-    return cudaFuncSetAttribute(upconv_fused_kernel<T, CC, fused_epilogue_warps(CC)>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    return cudaFuncSetAttribute(upconv_fused_kernel<T, CC, fused_epilogue_warps(CC), false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 FusedLayout<CC>::kSmemBytes);
+}
+
+template <typename T>
+static cudaError_t configure_wide_pair(int* clusters) {
+    constexpr int kBlock = 64 + fused_epilogue_warps(64) * 32;
+    auto kernel = upconv_fused_kernel<T, 64, fused_epilogue_warps(64), true>;
+    cudaError_t err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FusedLayout<64, true>::kSmemBytes);
+    if (err != cudaSuccess) return err;
+    cudaLaunchConfig_t config = {};
+    config.gridDim = dim3(2 * sm_count(), 1, 1);
+    config.blockDim = dim3(kBlock, 1, 1);
+    config.dynamicSmemBytes = FusedLayout<64, true>::kSmemBytes;
+    cudaLaunchAttribute attribute;
+    attribute.id = cudaLaunchAttributeClusterDimension;
+    attribute.val.clusterDim.x = 2; attribute.val.clusterDim.y = 1; attribute.val.clusterDim.z = 1;
+    config.attrs = &attribute;
+    config.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, kernel, &config) != cudaSuccess) {
+        cudaGetLastError();
+        n = 0;
+    }
+    if (n < *clusters) *clusters = n;
+    return cudaSuccess;
 }
 
 int configure_fused_kernels() {
@@ -434,6 +540,10 @@ int configure_fused_kernels() {
     if (err == cudaSuccess) err = configure_one<__nv_bfloat16, 64>();
     if (err == cudaSuccess) err = configure_one<__half, 32>();
     if (err == cudaSuccess) err = configure_one<__nv_bfloat16, 32>();
+    int clusters = 1 << 30;
+    if (err == cudaSuccess) err = configure_wide_pair<__half>(&clusters);
+    if (err == cudaSuccess) err = configure_wide_pair<__nv_bfloat16>(&clusters);
+    g_fused_wide_pair_clusters = clusters == (1 << 30) ? 0 : clusters;
     if (err != cudaSuccess)
         return fail(-(int)err, "cudaFuncSetAttribute(upconv_fused_kernel): %s", cudaGetErrorString(err));
     return GANCE_OK;
@@ -472,7 +582,12 @@ extern "C" int gance_modconv3x3_up2_fused(const void* x, int dtype, int batch, i
 #else
     constexpr int kPairMinCin = 256;
 #endif
-    if (c_in >= kPairMinCin && c_out % 64 == 0 && h_in >= 32 && w_in >= 32 && tc::conv_pair_mode() != 0 && tc::fused_pair_clusters() > 0) {
+#ifdef GANCE_ABL_FP_TALL512
+    constexpr int kTallMinCin = 512;  // A/B build: the Cin = 256 layer on the 16 x 8-cell pair kernel instead
+#else
+    constexpr int kTallMinCin = kPairMinCin;
+#endif
+    if (c_in >= kTallMinCin && c_out % 64 == 0 && h_in >= 32 && w_in >= 32 && tc::conv_pair_mode() != 0 && tc::fused_pair_clusters() > 0) {
         const long long m_tiles = (long long)batch * ((2 * h_in + 27) / 28) * ((2 * w_in + 11) / 12);
         if (tc::conv_pair_mode() == 2 || ((m_tiles + 1) / 2) * (c_out / 64) >= tc::fused_pair_clusters()) {
             if (dtype == GANCE_F16)
@@ -480,6 +595,21 @@ extern "C" int gance_modconv3x3_up2_fused(const void* x, int dtype, int batch, i
                                                      noise_batch_stride, noise_strength, bias, next_styles, out, s);
             return tc::launch_fused_pair<__nv_bfloat16>(x, batch, h_in, w_in, c_in, c_out, weight_phase, demod, noise,
                                                         noise_batch_stride, noise_strength, bias, next_styles, out, s);
+        }
+    }
+    // Wide layers too small for the 8 x 16-cell tiles (16^2 -> 32^2): the 16 x 8-cell kernel itself as CTA pairs - half of the
+    // weight bytes per SM through L2 and shared memory, five pipeline stages instead of three: 102 -> 79 us. Measured on
+    // the Cin = 128 layer (256^2 -> 512^2) the pair flavour LOSES (745 vs 698 us: that layer is bound by its filter step, and
+    // the accumulator hand-over across the SM pair adds to it), so narrow layers pair only when forced (mode 2, tests).
+    const bool wide_pair_wanted = tc::conv_pair_mode() == 2 || (tc::conv_pair_mode() == 1 && c_in >= kPairMinCin);
+    if (wide_pair_wanted && c_out % 64 == 0 && tc::g_fused_wide_pair_clusters > 0) {
+        const long long m_tiles = (long long)batch * ((2 * h_in + 11) / 12) * ((2 * w_in + 27) / 28);
+        if (tc::conv_pair_mode() == 2 || ((m_tiles + 1) / 2) * (c_out / 64) >= tc::g_fused_wide_pair_clusters) {
+            if (dtype == GANCE_F16)
+                return tc::launch_fused<__half, 64, true>(x, batch, h_in, w_in, c_in, c_out, weight_phase, demod, noise,
+                                                          noise_batch_stride, noise_strength, bias, next_styles, out, s);
+            return tc::launch_fused<__nv_bfloat16, 64, true>(x, batch, h_in, w_in, c_in, c_out, weight_phase, demod, noise,
+                                                             noise_batch_stride, noise_strength, bias, next_styles, out, s);
         }
     }
     if (c_out == 32) {

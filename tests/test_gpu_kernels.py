@@ -664,7 +664,13 @@ def test_phase_up_convolution_matches_oracle(lib, mode, cin, cout, side, batch):
 @pytest.mark.parametrize("cin,cout,side,batch", [(64, 64, 16, 2), (128, 64, 32, 1), (256, 128, 24, 3), (512, 256, 16, 2),
                                                  (64, 32, 40, 2), (128, 64, 64, 1)])
 def test_fused_up_convolution_matches_oracle(lib, mode, cin, cout, side, batch):
-    _fused_up_case(lib, mode, cin, cout, side, batch)
+    """Single-CTA kernel against the oracle, then the CTA-pair flavour of the same 16 x 8-cell kernel (cta_group::2, half of
+    the weight rows per CTA; side 24 x batch 3 and side 40 give odd tile counts = a ghost tile) bit for bit against it."""
+    with conv_pairing(lib, 0):
+        single = _fused_up_case(lib, mode, cin, cout, side, batch)
+    with conv_pairing(lib, 2):
+        paired = _fused_up_case(lib, mode, cin, cout, side, batch)
+    assert torch.equal(single, paired)
 
 
 @pytest.mark.parametrize("mode", ["bf16", "fp16"])
