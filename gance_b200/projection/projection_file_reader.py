@@ -90,6 +90,23 @@ class ProjectionFileReader:  # pylint: disable=too-many-instance-attributes
     def final_latents(self: "ProjectionFileReader") -> Iterator[SingleMatrix]:
         return self._final_latents
 
+    def final_latents_count(self: "ProjectionFileReader") -> int:
+        """Addition: number of final-latent datasets in the file, without decoding any."""
+        return sum(1 for _ in _types_in_group(self._file[FINAL_LATENTS_GROUP_NAME], Dataset))
+
+    def final_latents_shape(self: "ProjectionFileReader") -> tuple:
+        """Addition: (rows, vector length) of one frame's final latents, from the first dataset's header."""
+        first = next(_types_in_group(self._file[FINAL_LATENTS_GROUP_NAME], Dataset))
+        return tuple(int(v) for v in first.shape[-2:])
+
+    def final_latents_slice(self: "ProjectionFileReader", start: int, stop: int) -> Iterator[SingleMatrix]:
+        """
+        Addition: the final latents of frames [start, stop) only - the datasets outside the range are never inflated (every
+        frame is its own gzip-9 chunk stream; `itertools.islice(reader.final_latents, ...)` would decode the skipped ones).
+        """
+        datasets = list(_types_in_group(self._file[FINAL_LATENTS_GROUP_NAME], Dataset))[max(0, start): max(0, stop)]
+        return (complete_latents_to_matrix(np.array(dataset)) for dataset in datasets)
+
     @property
     def final_images(self: "ProjectionFileReader") -> ImageSourceType:
         return self._final_images
@@ -176,6 +193,54 @@ def projection_history_step_matrices_label(reader: ProjectionFileReader, project
             f"{Path(reader.projection_attributes.original_target_path).name} "
             f"proj by {Path(reader.projection_attributes.original_network_path).name} "
             f"step {projection_step}"
+        ),
+    )
+
+
+def final_latents_matrices_label_sharded(reader: ProjectionFileReader, group=None) -> MatricesLabel:
+    """
+    Addition for multi-GPU runs: the same MatricesLabel as `final_latents_matrices_label`, with the inflating shared out.
+    Decoding a projection file is pure host work (zlib + un-shuffle per 9 KB chunk: ~0.25 s for a 60 s file) that every rank
+    of a frame-sharded run would repeat; here rank r inflates the contiguous share [r*F/R, (r+1)*F/R) of the frames and
+    ONE all-gather (NCCL over NVLink on the GPUs, gloo in the CPU tests) hands every rank the whole [F, rows, 512] array.
+    Without an initialised process group (or with one rank) this is `final_latents_matrices_label`.
+    """
+    import torch
+    import torch.distributed as dist
+
+    from gance_b200.frame_sharding import all_frame_ranges
+
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return final_latents_matrices_label(reader)
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    total = reader.final_latents_count()
+    if total == 0:
+        raise StopIteration("Iterator labeled: final latents was empty!")
+    ranges = all_frame_ranges(world, total)
+    start, stop = ranges[rank]
+    mine = list(reader.final_latents_slice(start, stop))
+    longest = max(b - a for a, b in ranges)
+    rows, length = reader.final_latents_shape()
+    on_gpu = dist.get_backend(group) == "nccl"
+    device = torch.device("cuda", torch.cuda.current_device()) if on_gpu else torch.device("cpu")
+    send = torch.zeros((longest, rows, length), dtype=torch.float32)
+    if mine:
+        send[: len(mine)] = torch.from_numpy(np.stack(mine).astype(np.float32, copy=False))
+    send = send.to(device)
+    received = torch.empty((world * longest, rows, length), dtype=torch.float32, device=device)
+    if on_gpu:
+        dist.all_gather_into_tensor(received, send, group=group)
+    else:
+        dist.all_gather(list(received.split(longest, dim=0)), send, group=group)
+    pieces = [received[r * longest: r * longest + (b - a)] for r, (a, b) in enumerate(ranges)]
+    frames = torch.cat(pieces, dim=0).cpu().numpy()  # [F, rows, 512] in frame order
+    data = np.ascontiguousarray(frames.transpose(1, 0, 2)).reshape(rows, total * length)
+    return MatricesLabel(
+        data=ConcatenatedMatrices(data),
+        vector_length=length,
+        label=(
+            f"{Path(reader.projection_attributes.original_target_path).name} "
+            f"proj by {Path(reader.projection_attributes.original_network_path).name}"
         ),
     )
 

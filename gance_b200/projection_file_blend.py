@@ -49,13 +49,18 @@ def _wavs(wav: Sequence[WavInput]) -> list:
 
 
 def read_projection_blend_inputs(wav: Sequence[WavInput], projection_file_path: Union[str, Path], output_fps: float,
-                                 vector_length: int) -> ProjectionBlendInputs:
+                                 vector_length: int, share_decoding: bool = False) -> ProjectionBlendInputs:
     """
     Reference :124-157: read the final latents, refuse an incomplete file, derive the frame multiplier
     (`output_fps / projection_fps`, which must divide exactly) and scale the audio to `multiplier * frames_in_file` vectors.
+    `share_decoding` (an addition, for frame-sharded runs; every rank must make the call): each rank inflates its share of
+    the file's frames and one all-gather completes the array on every rank (`final_latents_matrices_label_sharded`).
     """
     with projection_file_reader.load_projection_file(Path(projection_file_path)) as reader:
-        final_latents = projection_file_reader.final_latents_matrices_label(reader)
+        if share_decoding:
+            final_latents = projection_file_reader.final_latents_matrices_label_sharded(reader)
+        else:
+            final_latents = projection_file_reader.final_latents_matrices_label(reader)
         final_latents_in_file = underlying_length(final_latents.data) / vector_length
         processed_frames_in_file = reader.projection_attributes.projection_frame_count
         projection_complete = reader.projection_attributes.complete

@@ -227,3 +227,43 @@ def test_shared_frame_sink_single_process(tmp_path):
         with pytest.raises(ValueError):
             SharedFrameSink("solo", 6, 3, (0, 0), create=False, register=False, directory=str(tmp_path))
     assert not (tmp_path / "solo").exists()
+
+
+def _projection_worker(rank: int, world: int, port: int, path: str, results) -> None:
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from gance_b200.projection import projection_file_reader
+
+        with projection_file_reader.load_projection_file(path) as reader:
+            label = projection_file_reader.final_latents_matrices_label_sharded(reader)
+        results[rank] = (label.data.copy(), label.vector_length, label.label)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,frames", [(2, 7), (3, 2), (2, 1)])
+def test_projection_file_decoding_shared_over_ranks_equals_the_whole_read_gloo(tmp_path, world, frames):
+    """Every rank inflates its share of the projection file's frames; one all-gather gives each the array a whole read gives
+    (ragged and empty shares included)."""
+    from pathlib import Path
+
+    from gance_b200.projection import projection_file_reader, projector_file_writer
+
+    path = Path(tmp_path) / "projection.hdf5"
+    latents = [np.random.RandomState(i).randn(18, 512).astype(np.float32) for i in range(frames)]
+    projector_file_writer.write_projection_file(path, latents, projector_file_writer.synthetic_attributes(frames, projection_fps=30.0))
+    whole = projection_file_reader.load_final_latents_matrices_label(path)
+    with projection_file_reader.load_projection_file(path) as reader:
+        assert reader.final_latents_count() == frames and reader.final_latents_shape() == (18, 512)
+        assert np.array_equal(np.concatenate(list(reader.final_latents_slice(1, 3)), axis=-1) if frames > 1 else whole.data[:, :0],
+                              whole.data[:, 512: 3 * 512])
+        single = projection_file_reader.final_latents_matrices_label_sharded(reader)  # no process group: the plain read
+    assert np.array_equal(single.data, whole.data)
+    manager = mp.Manager()
+    results = manager.dict()
+    mp.spawn(_projection_worker, args=(world, _free_port(), str(path), results), nprocs=world, join=True)
+    for rank in range(world):
+        data, vector_length, label = results[rank]
+        assert np.array_equal(data, whole.data) and data.dtype == whole.data.dtype
+        assert vector_length == whole.vector_length and label == whole.label

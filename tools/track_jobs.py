@@ -142,7 +142,8 @@ def run_track_job(kind: str, seconds: float, device: torch.device, mode: str = "
         # ---- the job: input files -> latents -> this rank's frames in the encoder's buffer ----
         t0 = time.perf_counter()
         if spec["path"] == "matrices":
-            inputs = projection_file_blend.read_projection_blend_inputs([paths["wav"]], paths["projection"], FPS, 512)
+            inputs = projection_file_blend.read_projection_blend_inputs([paths["wav"]], paths["projection"], FPS, 512,
+                                                                        share_decoding=dist.is_initialized() and os.environ.get("GANCE_TRACK_JOBS_WHOLE_READ") != "1")
             t1 = time.perf_counter()
             track = projection_file_blend.projection_blend_latents(inputs, networks, ALPHA, True, FFT_RANGE, BLEND_DEPTH)
         else:
