@@ -278,12 +278,21 @@ __device__ __forceinline__ uint32_t pack_pair(float a, float b, __nv_bfloat16*) 
 // L1 store path takes one sector per clock; ablation, round 2: 0.36 of that layer's 0.99 ms were its global stores).
 // The tile is addressed as 8 rows x 8 pixel PAIRS of 128 bytes under the 128-byte swizzle - `tmap_out` views the
 // [B,H,W,32] tensor as [B,H,W/2,64] - which spreads a store instruction's 32 x 8 bytes over all banks twice (optimal).
+// C > 64 (the 128 -> 128-channel layer): a thread's coefficients no longer fit its registers for the whole tile, so they are
+// staged per sample in the group's shared-memory cache (`cache_all`, 2 * C float4 per group, as conv_epilogue lays them out)
+// and the 8 channels of each 32-column chunk are loaded into registers at the top of the chunk: 16 LDS.128 per chunk with
+// four distinct addresses per warp (one wavefront) - against one four-wavefront BROADCAST LDS.128 per channel and per
+// accumulator element in the row-per-thread epilogue, which kept that layer's shared-memory pipe at 90 % (ncu, round 2).
+// The same staging also serves the 64-channel fused-ToRGB flavour (COEF_SMEM): 48 instead of 96 coefficient registers let it
+// keep the next tile's operands in registers and run a third epilogue group.
 template <typename T, int N_TILE, int C, bool UP, bool RGB, int GROUPS, int TILE_W_LOG2 = -1, bool PAIR = false, int APG = 1,
-          bool STAGED = false>
+          bool STAGED = false, bool COEF_SMEM = (C > 64)>
 __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int group, int warp, int lane, int total_tiles,
                                                    uint32_t tmem_base, uint64_t* tmem_full_bar,
                                                    uint64_t* tmem_empty_bar, uint8_t* stage_tile = nullptr,
-                                                   const CUtensorMap* tmap_out = nullptr) {
+                                                   const CUtensorMap* tmap_out = nullptr, float4* cache_all = nullptr) {
+    constexpr bool kCoefSmem = COEF_SMEM;
+    static_assert(C <= 64 || COEF_SMEM, "more than 64 channels need the shared-memory coefficient cache");
     static_assert(!STAGED || (UP && C == 32 && TILE_W_LOG2 == 3 && !RGB), "staged output: folded up-convolution, 32 channels");
     const uint32_t stage_addr = STAGED ? smem_u32(stage_tile) : 0u;
     // PAIR: `total_tiles` counts pair items (the host guarantees an even m-tile count: no ghost tiles here), walked
@@ -296,9 +305,10 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
         bool ghost;
         return PAIR ? decode_pair_item(p, tile, pair_rank, N_TILE, ghost) : decode_tile(p, tile, N_TILE);
     };
-    static_assert(C % 32 == 0 && C <= 64, "register-resident coefficients: at most 16 channels per thread");
+    static_assert(C % 32 == 0 && C <= 128, "register-resident coefficients: at most 16 channels per thread, or per chunk from shared memory");
     static_assert(N_TILE == (UP ? 4 * C : C), "GEMM columns = channels (x 4 phases for the folded up-convolution)");
-    constexpr int CPT = C / 4;           // channels per thread
+    static_assert(!kCoefSmem || !UP, "the shared-memory coefficient cache serves plain convolutions");
+    constexpr int CPT = kCoefSmem ? 8 : C / 4;  // coefficient registers: all of the thread's channels, or one chunk's
     constexpr int CHUNKS = N_TILE / 32;  // 32-column accumulator chunks per tile
     const int quarter = warp & 3;
     const int q4 = lane & 3, r8 = lane >> 2;
@@ -331,7 +341,7 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
     // Noise and skip-connection values of a tile do not depend on its accumulator: they are requested one tile AHEAD
     // (while the current tile is being computed) so their global-memory latency never sits on the tile's critical path.
     constexpr int NP = UP ? 4 : 1;  // noise values per input pixel
-    constexpr bool kAheadInRegisters = !(RGB && C == 64);  // see the comment above `prefetch` below
+    constexpr bool kAheadInRegisters = !(RGB && C == 64 && !kCoefSmem);  // see the comment above `prefetch` below
     struct Ahead {
         TileCoord t;
         float nz[4][NP];
@@ -456,7 +466,24 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
         const TileCoord t = cur.t;
         const int b = t.b0;
         if (kAheadInRegisters && more) ahead = request(tile + GROUPS * walk_stride);
-        if (b != cached_b) {  // per-sample coefficients of this thread's channels -> registers
+        if (kCoefSmem && b != cached_b) {  // group-uniform: per-sample coefficients of every channel -> the group's cache
+            float4* coef_a = cache_all + group * 2 * C;
+            float4* coef_b = coef_a + C;
+            epilogue_bar_sync(group);  // everyone is done reading the previous sample's
+            for (int i = (warp & 3) * 32 + lane; i < C; i += kEpilogueThreads) {
+                const size_t bc = (size_t)b * C + i;
+                coef_a[i] = make_float4(__ldg(p.demod + bc), __ldg(p.bias + i),
+                                        (p.next_styles ? __ldg(p.next_styles + bc) : 1.0f) * kLreluGain, 0.f);
+                if (RGB) {
+                    const float rs = __ldg(p.rgb_styles + bc) * kLreluGain;
+                    coef_b[i] = make_float4(rs * __ldg(p.rgb_weight + 3 * i), rs * __ldg(p.rgb_weight + 3 * i + 1),
+                                            rs * __ldg(p.rgb_weight + 3 * i + 2), 0.f);
+                }
+            }
+            epilogue_bar_sync(group);
+            cached_b = b;
+        }
+        if (!kCoefSmem && b != cached_b) {  // per-sample coefficients of this thread's channels -> registers
 #pragma unroll
             for (int k = 0; k < CPT; ++k) {
                 const int ch = (k >> 3) * 32 + ((k >> 1) & 3) * 8 + 2 * q4 + (k & 1);
@@ -509,7 +536,20 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
 #pragma unroll
         for (int chunk = 0; chunk < CHUNKS; ++chunk) {
             const int phase = UP ? (chunk * 32) / C : 0;
-            const int kbase = ((chunk * 32) % C) / 4;  // first of this thread's channels inside the chunk
+            const int kbase = kCoefSmem ? 0 : ((chunk * 32) % C) / 4;  // first of this thread's channels inside the chunk
+            if (kCoefSmem) {  // this chunk's 8 channels: 32 * chunk + 8 j + 2 q4 + e
+                const uint32_t base = smem_u32(cache_all + group * 2 * C);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const int ch = chunk * 32 + (k >> 1) * 8 + 2 * q4 + (k & 1);
+                    const float4 a = lds128(base + (uint32_t)ch * 16u);
+                    cd[k] = a.x; cb[k] = a.y; cs[k] = a.z;
+                    if (RGB) {
+                        const float4 w = lds128(base + (uint32_t)(C + ch) * 16u);
+                        cw0[k] = w.x; cw1[k] = w.y; cw2[k] = w.z;
+                    }
+                }
+            }
 #pragma unroll
             for (int h2 = 0; h2 < 2; ++h2) {
                 uint32_t r[16];
@@ -935,7 +975,11 @@ constexpr int kHaloW = kHaloTileW + 2, kHaloH = kHaloTileH + 2;
 // groups are busy > 90 % of the time while the MMA issuer waits 20-25 % for a drained accumulator - the epilogue warps are
 // latency-bound (one instruction every ~5 cycles per warp), so the remedy is more of them where registers allow:
 // the folded up-convolution (N = 128, 112 registers) runs four groups; the fused-ToRGB flavours need 128-168 registers.
+// The 64-channel fused-ToRGB flavour was also tried with shared-memory coefficients (conv_epilogue_frag's COEF_SMEM: 48
+// instead of 96 coefficient registers): with a third group it spills at the 128-register cap (775 vs 700 us for the 512^2
+// Conv1), with two groups the per-chunk reloads cost more than the registers they free (733 us). Registers stay.
 __host__ __device__ constexpr int halo_groups(int n_gemm) { return n_gemm == 128 ? 4 : (n_gemm == 32 ? 3 : 2); }  // bounded by registers (65536 / threads)
+constexpr bool kHalo64CoefSmem = false;
 __host__ __device__ constexpr int halo_threads(int n_gemm) { return 64 + halo_groups(n_gemm) * kEpilogueThreads; }
 constexpr int kHaloApg = 2;  // TMEM accumulator buffers per epilogue group (see conv_epilogue); 1 where 512 columns are full
 __host__ __device__ constexpr int halo_apg(int n_gemm) { return n_gemm == 128 ? 1 : kHaloApg; }
@@ -949,7 +993,8 @@ struct HaloSmem {
     static constexpr int kHaloStride = (kHaloBytes + 1023) / 1024 * 1024;
     static constexpr int kBarrierOffset = kWeightBytes + STAGES * kHaloStride;
     static constexpr int kCacheOffset = kBarrierOffset + ((2 * STAGES + 2 * halo_accs(N_GEMM) + 1) * 8 + 16 + 15) / 16 * 16;
-    static constexpr int kBytes = kCacheOffset + 1024;
+    static constexpr int kCacheBytes = N_GEMM == 64 ? halo_groups(N_GEMM) * 2 * N_GEMM * 16 : 0;  // coefficient cache of the 64-channel fused-ToRGB flavour
+    static constexpr int kBytes = kCacheOffset + kCacheBytes + 1024;
 };
 
 template <int SWIZZLE_BYTES>
@@ -1121,8 +1166,10 @@ modconv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_
 #endif
         }
     } else {
-        conv_epilogue_frag<T, N_GEMM, (UP ? N_GEMM / 4 : N_GEMM), UP, RGB, kHaloGroups, 3, false, halo_apg(N_GEMM)>(
-            p, (warp - 2) >> 2, warp, lane, total_tiles, tmem_base, tmem_full_bar, tmem_empty_bar);
+        conv_epilogue_frag<T, N_GEMM, (UP ? N_GEMM / 4 : N_GEMM), UP, RGB, kHaloGroups, 3, false, halo_apg(N_GEMM), false,
+                           (kHalo64CoefSmem && RGB && N_GEMM == 64)>(
+            p, (warp - 2) >> 2, warp, lane, total_tiles, tmem_base, tmem_full_bar, tmem_empty_bar, nullptr, nullptr,
+            reinterpret_cast<float4*>(smem + L::kCacheOffset));
     }
 
     tcgen05_fence_before();
@@ -1167,7 +1214,7 @@ modconv3x3_halo_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __
                             const __grid_constant__ CUtensorMap tmap_out, const ConvParams p) {
     using L = HaloPairSmem<N_GEMM, CIN, STAGES>;
     constexpr int C = UP ? N_GEMM / 4 : N_GEMM;  // channels of the output tensor
-    constexpr bool kFrag = C <= 64;              // register-resident coefficients (fragment-layout epilogue)
+    constexpr bool kFrag = C <= 64 || RGB;       // fragment-layout epilogue (the plain 128-channel flavour keeps the row-per-thread one: it can write the second, unscaled output)
     constexpr uint32_t kTmemCols = L::kAccs * N_GEMM;
     static_assert(CIN == 64 || CIN == 128, "64-channel K chunks");
     static_assert((kTmemCols & (kTmemCols - 1)) == 0 && kTmemCols <= 512 && kTmemCols >= 32, "TMEM columns must be a power of two");
@@ -1293,7 +1340,8 @@ modconv3x3_halo_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __
         if constexpr (kFrag)
             conv_epilogue_frag<T, N_GEMM, C, UP, RGB, kEpilogueGroups, 3, true, kHaloApg, kStaged>(
                 p, (warp - 2) >> 2, warp, lane, total_items, tmem_base, tmem_full_bar, tmem_empty_bar,
-                smem + L::kStageOffset + (warp - 2) * L::kStageTileBytes, &tmap_out);
+                kStaged ? smem + L::kStageOffset + (warp - 2) * L::kStageTileBytes : nullptr, &tmap_out,
+                reinterpret_cast<float4*>(smem + L::kCacheOffset));
         else
             conv_epilogue<T, N_GEMM, UP, RGB, kEpilogueGroups, L::kCacheFloat4, true, kHaloApg>(
                 p, (warp - 2) >> 2, warp, lane, total_items, tmem_base, tmem_full_bar, tmem_empty_bar,
