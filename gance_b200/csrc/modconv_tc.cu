@@ -982,7 +982,12 @@ __host__ __device__ constexpr int halo_groups(int n_gemm) { return n_gemm == 128
 constexpr bool kHalo64CoefSmem = false;
 __host__ __device__ constexpr int halo_threads(int n_gemm) { return 64 + halo_groups(n_gemm) * kEpilogueThreads; }
 constexpr int kHaloApg = 2;  // TMEM accumulator buffers per epilogue group (see conv_epilogue); 1 where 512 columns are full
-__host__ __device__ constexpr int halo_apg(int n_gemm) { return n_gemm == 128 ? 1 : kHaloApg; }
+// The 32-channel layer (1024^2 Conv1) runs four buffers per group (12 x 32 of the 512 TMEM columns) and an eight-deep halo
+// ring: its MMA pipeline alone and its epilogue alone each need ~0.82 of the kernel's time (ablations, round 2), so what is
+// left to gain is their overlap - measured 8-14 % (three A/B pairs in one run). The 64-channel layer measured 4 % SLOWER
+// with four buffers and six stages and keeps two and three.
+__host__ __device__ constexpr int halo_apg(int n_gemm) { return n_gemm == 128 ? 1 : (n_gemm == 32 ? 4 : kHaloApg); }
+constexpr int kHaloStages64 = 3, kHaloStages32 = 8;
 __host__ __device__ constexpr int halo_accs(int n_gemm) { return halo_apg(n_gemm) * halo_groups(n_gemm); }
 
 template <int N_GEMM, int CIN, int STAGES>
@@ -1122,6 +1127,9 @@ modconv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_
                 const uint64_t a_desc0 = make_smem_desc_sbo<kSwizzle>(w_addr + (uint32_t)(L::kWeightBytes + stage * L::kHaloStride),
                                                                       kHaloW * L::kRowBytes);
                 if (leader) {
+#ifdef GANCE_ABL_NOMMA
+                    if (p.batch < 0)  // ablation: no tensor-core work, the epilogue runs on whatever the accumulator holds
+#endif
 #pragma unroll
                     for (int tap = 0; tap < 9; ++tap) {
 #ifdef GANCE_ABL_NOSWZ
@@ -1735,8 +1743,8 @@ int init_tensor_core_path() {
     if ((rc = tc::configure_halo_pair<64, 64, 4, false>(&tc::g_halo_pair_clusters[1])) != GANCE_OK) return rc;
     if ((rc = tc::configure_halo_pair<128, 128, 3, false>(&tc::g_halo_pair_clusters[2])) != GANCE_OK) return rc;
     if ((rc = tc::configure_halo<128, 64, 2>()) != GANCE_OK) return rc;
-    if ((rc = tc::configure_halo<64, 64, 3>()) != GANCE_OK) return rc;
-    if ((rc = tc::configure_halo<32, 32, 4>()) != GANCE_OK) return rc;
+    if ((rc = tc::configure_halo<64, 64, tc::kHaloStages64>()) != GANCE_OK) return rc;
+    if ((rc = tc::configure_halo<32, 32, tc::kHaloStages32>()) != GANCE_OK) return rc;
     if ((rc = tc::configure_phase_kernels()) != GANCE_OK) return rc;
     if ((rc = tc::configure_fused_kernels()) != GANCE_OK) return rc;
     if ((rc = tc::configure_fused_pair_kernels()) != GANCE_OK) return rc;
@@ -1845,9 +1853,9 @@ static int launch_tensor_core_conv(const char* who, const void* x, int dtype, in
             return tc::launch_halo_pair<128, 64, 3, true>(half_operands, p, x, weight, tc::g_halo_pair_clusters[0], s);
         if (c_in == 64 && c_out == 64 && halo_pair_ok(1))
             return tc::launch_halo_pair<64, 64, 4, false>(half_operands, p, x, weight, tc::g_halo_pair_clusters[1], s);
-        if (c_in == 32) return tc::launch_halo<32, 32, 4>(half_operands, p, x, weight, s);
+        if (c_in == 32) return tc::launch_halo<32, 32, tc::kHaloStages32>(half_operands, p, x, weight, s);
         if (c_out == 128) return tc::launch_halo<128, 64, 2>(half_operands, p, x, weight, s);
-        return tc::launch_halo<64, 64, 3>(half_operands, p, x, weight, s);
+        return tc::launch_halo<64, 64, tc::kHaloStages64>(half_operands, p, x, weight, s);
     }
     if (c_in % 64 != 0) {  // Cin = 32 (1024^2 Conv1 in config-f): 64-byte rows, SWIZZLE_64B
         p.n_tiles = c_out / 32; p.k_chunks = c_in / 32;
