@@ -78,6 +78,8 @@ def parse_args():
     ap.add_argument("--output-side", type=int, default=2160, help="output side length of the switching job")
     ap.add_argument("--streams", type=int, default=2, choices=[1, 2],
                     help="compute streams the timed steps alternate over (2: consecutive batches overlap on the device)")
+    ap.add_argument("--no-noise-fork", action="store_true",
+                    help="A/B: launch the per-batch noise kernel on the compute stream instead of a forked side stream")
     ap.add_argument("--conv-pairing", type=int, default=None, choices=[0, 1, 2],
                     help="A/B: gance_set_conv_pairing (0 single-CTA implicit GEMM, 1 library default, 2 CTA pairs whenever eligible)")
     return ap.parse_args()
@@ -331,6 +333,8 @@ def main():
     peaks, peak_source = measured_peaks()
     if args.conv_pairing is not None:
         _lib.load_library().gance_set_conv_pairing(args.conv_pairing)
+    if args.no_noise_fork:
+        GeneratorOnDevice.fork_noise = False
 
     def barrier():
         if world > 1:

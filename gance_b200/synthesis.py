@@ -151,6 +151,7 @@ class GeneratorOnDevice:
         self._renderers: Dict[tuple, "BatchRenderer"] = {}
         self._contexts: Dict[int, "GeneratorOnDevice"] = {}
         self.launches_per_replay = 0
+        self._noise_stream: Optional[torch.cuda.Stream] = None  # side stream of the forked noise launch (run_vectors)
         self.graph_captures = 0  # how many CUDA graphs this generator has captured (tests: switching must not re-capture)
         self._upload(variables)
 
@@ -316,6 +317,7 @@ class GeneratorOnDevice:
         if found is None:
             found = copy.copy(self)
             found._buffers, found._graphs, found._renderers, found._contexts = {}, {}, {}, {}
+            found._noise_stream = None  # its own side stream for the forked noise launch
             found.profile_events = None
             found.graph_captures, found.launches_per_replay = 0, 0
             found.noise_counter = torch.zeros(1, dtype=torch.int64, device=self.device)
@@ -375,6 +377,7 @@ class GeneratorOnDevice:
         noise: Optional[Sequence[torch.Tensor]] = None,
         return_float_image: bool = False,
         out: Optional[torch.Tensor] = None,
+        _prelaunched_noise=None,
     ):
         """
         G_synthesis + convert_images_to_uint8: w+ [B,num_ws,512] -> uint8 frames [B,R,R,3] on the
@@ -413,19 +416,13 @@ class GeneratorOnDevice:
                       for i, r in enumerate(self.rgbs)]
         self._mark("styles")
 
-        # fresh noise of every layer in one launch (tf.random_normal per layer in the reference's graph)
+        # fresh noise of every layer in one launch: already running on the side stream (run_vectors), or launched here
         random_noise: Dict[int, torch.Tensor] = {}
         if noise_mode == "random":
-            sizes = [(i, c.out_resolution) for i, c in enumerate(self.convs) if self.conv_strength[i] != 0.0]
-            total = sum(batch * side * side for _, side in sizes)
-            if total:
-                flat = self._buffer("noise_random", ((total + 3) // 4 * 4,), torch.float32)
-                _lib.check(lib.gance_normal_noise_next(flat.data_ptr(), flat.numel(), self.noise_seed,
-                                                       self.noise_counter.data_ptr(), stream), "gance_normal_noise_next")
-                start = 0
-                for i, side in sizes:
-                    random_noise[i] = flat[start: start + batch * side * side].view(batch, side, side)
-                    start += batch * side * side
+            random_noise, noise_stream = _prelaunched_noise if _prelaunched_noise is not None else \
+                self._launch_random_noise(batch, fork=False)
+            if noise_stream is not None:
+                torch.cuda.current_stream(self.device).wait_stream(noise_stream)  # join before the first layer reads it
 
         def layer_noise(i: int, side: int):
             if noise_mode == "none" or (noise_mode != "provided" and self.conv_strength[i] == 0.0):
@@ -611,9 +608,46 @@ class GeneratorOnDevice:
             f"gance_modconv3x3_tf32x3({h_out})",
         )
 
+    fork_noise = True  # A/B switch of the forked noise launch (bench.py --no-noise-fork)
+
     def run_vectors(self, z: torch.Tensor, truncation_psi: float = 1.2, noise_mode: str = "random", **kwargs):
-        """Batched `Gs.run(z, None, truncation_psi=1.2)` (network_functions.py:151-158)."""
-        return self.synthesis(self.mapping(z, truncation_psi), noise_mode=noise_mode, **kwargs)
+        """
+        Batched `Gs.run(z, None, truncation_psi=1.2)` (network_functions.py:151-158). The fresh noise of every layer does
+        not depend on the latents: its one launch is forked onto a side stream before G_mapping, so it overlaps the eight
+        latency-bound dense layers and the style / demodulation launches (a fork-join that a CUDA-graph capture keeps).
+        """
+        batch = int(z.reshape(-1, 512).shape[0])
+        prelaunched = self._launch_random_noise(batch, fork=self.fork_noise) if noise_mode == "random" else None
+        return self.synthesis(self.mapping(z, truncation_psi), noise_mode=noise_mode, _prelaunched_noise=prelaunched, **kwargs)
+
+    def _launch_random_noise(self, batch: int, fork: bool):
+        """
+        N(0,1) noise of every layer with a non-zero strength for one batch, one launch (tf.random_normal per layer in the
+        reference's graph). Returns ({layer: [batch,side,side] view}, side stream or None). With `fork` the launch goes to
+        this generator's side stream, ordered after everything already queued on the current stream (the previous batch may
+        still be reading the noise buffer); the consumer joins with `current.wait_stream(side)`.
+        """
+        sizes = [(i, c.out_resolution) for i, c in enumerate(self.convs) if self.conv_strength[i] != 0.0]
+        total = sum(batch * side * side for _, side in sizes)
+        views: Dict[int, torch.Tensor] = {}
+        if not total:
+            return views, None
+        flat = self._buffer("noise_random", ((total + 3) // 4 * 4,), torch.float32)
+        side_stream = None
+        stream = self._stream()
+        if fork:
+            if self._noise_stream is None:
+                self._noise_stream = torch.cuda.Stream(device=self.device)
+            side_stream = self._noise_stream
+            side_stream.wait_stream(torch.cuda.current_stream(self.device))
+            stream = side_stream.cuda_stream
+        _lib.check(self.lib.gance_normal_noise_next(flat.data_ptr(), flat.numel(), self.noise_seed,
+                                                    self.noise_counter.data_ptr(), stream), "gance_normal_noise_next")
+        start = 0
+        for i, side in sizes:
+            views[i] = flat[start: start + batch * side * side].view(batch, side, side)
+            start += batch * side * side
+        return views, side_stream
 
     def _replay(self, kind: str, latents: torch.Tensor, out: torch.Tensor, truncation_psi: float, noise_mode: str) -> torch.Tensor:
         """
