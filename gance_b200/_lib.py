@@ -66,6 +66,11 @@ _SIGNATURES = {
         [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_longlong, c_float,
          c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
     ),
+    "gance_modconv3x3_up2_phase_static": (
+        c_int,
+        [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_longlong, c_float,
+         c_void_p, c_void_p, c_void_p, c_void_p],
+    ),
     "gance_modconv3x3_up2_fused": (
         c_int,
         [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_longlong, c_float,

@@ -14,6 +14,8 @@
 // coefficient and stores t as 16-bit NHWC [B, 2H+2, 2W+2, Cout] (row/column 2H+1 are the exact zeros the FIR's
 // right padding needs). Pass 2 (upfir_act_kernel): out[y,x] = lrelu(sum_ab f[a] f[b] t[y-1+a, x-1+b] + noise +
 // bias) * sqrt(2) * s_next, f = [1,3,3,1]/4.
+#include <mutex>
+
 #include "tc_ptx.cuh"
 
 namespace gance {
@@ -463,6 +465,80 @@ extern "C" int gance_modconv3x3_up2_phase(const void* x, int dtype, int batch, i
                   batch, h_in, w_in, c_in, c_out);
     GANCE_REQUIRE(aligned16(x) && aligned16(weight_phase) && aligned16(scratch) && aligned16(out), GANCE_E_ALIGN,
                   "gance_modconv3x3_up2_phase: pointers must be 16-byte aligned");
+    cudaStream_t s = (cudaStream_t)stream;
+    if (dtype == GANCE_F16)
+        return tc::launch_phase<__half>(x, batch, h_in, w_in, c_in, c_out, weight_phase, demod, noise, noise_batch_stride,
+                                        noise_strength, bias, next_styles, scratch, out, s);
+    return tc::launch_phase<__nv_bfloat16>(x, batch, h_in, w_in, c_in, c_out, weight_phase, demod, noise, noise_batch_stride,
+                                           noise_strength, bias, next_styles, scratch, out, s);
+}
+
+// ---- the same two launches for callers that cannot allocate: t lives in a file-scope device array ---------------------------
+// No counterpart in the reference; added for callers that may not call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it). Every GPU that loads the library holds
+// these kStaticScratchBytes until exit. Both kernels are the ones above, unchanged; only where t is kept differs.
+//
+// In host code `g_phase_static_scratch` is the host-side stand-in of the symbol, NOT a device address: the address the
+// kernels get is resolved with cudaGetSymbolAddress, once per device, with that device current (phase_static_scratch()).
+//
+// Every call on a device shares the array and finds the previous call's t in it. Nothing has to be cleared: pass 1
+// writes every element of [B, 2H+2, 2W+2, Cout] (the zero border included) before pass 2, next on the same stream,
+// reads exactly that range. Calls that overlap on the GPU (two streams, two host threads) race on the array.
+namespace gance {
+namespace tc {
+
+constexpr size_t kStaticScratchBytes = GANCE_PHASE_STATIC_SCRATCH_BYTES;   // 4 MiB: e.g. B=1, 32^2 -> 64^2, Cout=256 is 2.2 MB
+static __device__ __align__(256) unsigned char g_phase_static_scratch[kStaticScratchBytes];
+
+constexpr int kStaticScratchMaxDevices = 64;
+static std::mutex g_static_scratch_mutex;
+static void* g_static_scratch_address[kStaticScratchMaxDevices] = {};
+
+// device address of the array on the CURRENT device; resolved on that device's first call, no allocation
+static int phase_static_scratch(void** address) {
+    int device = -1;
+    cudaError_t err = cudaGetDevice(&device);
+    if (err != cudaSuccess) return fail(-(int)err, "gance_modconv3x3_up2_phase_static: cudaGetDevice: %s", cudaGetErrorString(err));
+    if (device < 0 || device >= kStaticScratchMaxDevices)
+        return fail(GANCE_E_SHAPE, "gance_modconv3x3_up2_phase_static: device %d is beyond the %d this entry tracks", device,
+                    kStaticScratchMaxDevices);
+    std::lock_guard<std::mutex> lock(g_static_scratch_mutex);
+    if (g_static_scratch_address[device] == nullptr) {
+        void* resolved = nullptr;
+        err = cudaGetSymbolAddress(&resolved, g_phase_static_scratch);
+        if (err != cudaSuccess || resolved == nullptr)
+            return fail(err != cudaSuccess ? -(int)err : GANCE_E_DRIVER,
+                        "gance_modconv3x3_up2_phase_static: cudaGetSymbolAddress on device %d: %s", device,
+                        cudaGetErrorString(err));
+        g_static_scratch_address[device] = resolved;
+    }
+    *address = g_static_scratch_address[device];
+    return GANCE_OK;
+}
+
+}  // namespace tc
+}  // namespace gance
+
+extern "C" int gance_modconv3x3_up2_phase_static(const void* x, int dtype, int batch, int h_in, int w_in, int c_in, int c_out,
+                                                 const void* weight_phase, const float* demod, const float* noise,
+                                                 long long noise_batch_stride, float noise_strength, const float* bias,
+                                                 const float* next_styles, void* out, void* stream) {
+    GANCE_REQUIRE(is_initialised(), GANCE_E_NOT_INIT, "gance_init() has not been called");
+    GANCE_REQUIRE(x && weight_phase && demod && bias && out, GANCE_E_NULL, "gance_modconv3x3_up2_phase_static: NULL pointer");
+    GANCE_REQUIRE(dtype == GANCE_BF16 || dtype == GANCE_F16, GANCE_E_DTYPE, "gance_modconv3x3_up2_phase_static: dtype %d", dtype);
+    GANCE_REQUIRE(batch > 0 && h_in >= 8 && w_in >= 16 && c_in > 0 && c_out > 0 && c_in % 64 == 0 && c_out % 64 == 0, GANCE_E_SHAPE,
+                  "gance_modconv3x3_up2_phase_static: shape B=%d H=%d W=%d Cin=%d Cout=%d (needs H >= 8, W >= 16, channels %% 64 == 0)",
+                  batch, h_in, w_in, c_in, c_out);
+    const unsigned long long needed = 2ull * (unsigned long long)batch * (2ull * h_in + 2) * (2ull * w_in + 2) * (unsigned long long)c_out;
+    GANCE_REQUIRE(needed <= (unsigned long long)tc::kStaticScratchBytes, GANCE_E_SHAPE,
+                  "gance_modconv3x3_up2_phase_static: t = [%d,%d,%d,%d] x 2 B needs %llu bytes, the static scratch holds %llu; "
+                  "use gance_modconv3x3_up2_phase with a caller-owned scratch",
+                  batch, 2 * h_in + 2, 2 * w_in + 2, c_out, needed, (unsigned long long)tc::kStaticScratchBytes);
+    GANCE_REQUIRE(aligned16(x) && aligned16(weight_phase) && aligned16(out), GANCE_E_ALIGN,
+                  "gance_modconv3x3_up2_phase_static: pointers must be 16-byte aligned");
+    void* scratch = nullptr;
+    const int rc = tc::phase_static_scratch(&scratch);
+    if (rc != GANCE_OK) return rc;
     cudaStream_t s = (cudaStream_t)stream;
     if (dtype == GANCE_F16)
         return tc::launch_phase<__half>(x, batch, h_in, w_in, c_in, c_out, weight_phase, demod, noise, noise_batch_stride,

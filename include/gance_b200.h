@@ -221,6 +221,23 @@ int gance_modconv3x3_up2_phase(const void* x, int dtype, int batch, int h_in, in
                                const float* bias, const float* next_styles, void* scratch, void* out,
                                void* stream);
 
+/* ---- gance_modconv3x3_up2_phase for callers that cannot allocate device memory ---------------------------------------
+ * No counterpart in the reference: added for callers that may not call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it). Same two launches, same
+ * arguments and same results as gance_modconv3x3_up2_phase without `scratch`: t is kept in a file-scope
+ * `static __device__` array of GANCE_PHASE_STATIC_SCRATCH_BYTES inside the library (every GPU that loads the library holds
+ * it until exit); its device address is resolved with cudaGetSymbolAddress on the first call on each device. The entry
+ * calls no cudaMalloc / cudaFree / allocating routine.
+ *   limit: 2 * B * (2H+2) * (2W+2) * Cout bytes <= GANCE_PHASE_STATIC_SCRATCH_BYTES, else GANCE_E_SHAPE (use the entry above);
+ *   every call on a device shares the array: pass 1 overwrites all of the range pass 2 reads, so nothing is cleared and
+ *   calls in stream order are independent, but calls that OVERLAP on the GPU (other streams / threads) race on it. */
+#define GANCE_PHASE_STATIC_SCRATCH_BYTES (4u << 20)
+int gance_modconv3x3_up2_phase_static(const void* x, int dtype, int batch, int h_in, int w_in, int c_in,
+                                      int c_out, const void* weight_phase, const float* demod,
+                                      const float* noise, long long noise_batch_stride,
+                                      float noise_strength, const float* bias, const float* next_styles,
+                                      void* out, void* stream);
+
 /* ---- the same up-convolution in ONE launch: 4-phase GEMM whose epilogue applies the FIR on chip -------------------------
  * upconv_fused.cu: tiles of 16 x 8 cells (a 32 x 16-pixel patch of t, kept as 16-bit in shared memory) produce 28 x 12 output
  * pixels each; the 2-cell halo is recomputed by the tensor core (1.52x the algorithmic MACs) and t never reaches HBM.
