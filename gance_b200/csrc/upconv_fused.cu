@@ -569,8 +569,8 @@ extern "C" int gance_modconv3x3_up2_fused(const void* x, int dtype, int batch, i
     GANCE_REQUIRE(is_initialised(), GANCE_E_NOT_INIT, "gance_init() has not been called");
     GANCE_REQUIRE(x && weight_phase && demod && bias && out, GANCE_E_NULL, "gance_modconv3x3_up2_fused: NULL pointer");
     GANCE_REQUIRE(dtype == GANCE_BF16 || dtype == GANCE_F16, GANCE_E_DTYPE, "gance_modconv3x3_up2_fused: dtype %d", dtype);
-    GANCE_REQUIRE(batch > 0 && h_in >= 8 && w_in >= 16 && c_in % 64 == 0 && (c_out % 64 == 0 || c_out == 32), GANCE_E_SHAPE,
-                  "gance_modconv3x3_up2_fused: shape B=%d H=%d W=%d Cin=%d Cout=%d (needs H >= 8, W >= 16, Cin %% 64 == 0, "
+    GANCE_REQUIRE(batch > 0 && h_in >= 4 && w_in >= 4 && c_in % 64 == 0 && (c_out % 64 == 0 || c_out == 32), GANCE_E_SHAPE,
+                  "gance_modconv3x3_up2_fused: shape B=%d H=%d W=%d Cin=%d Cout=%d (needs H >= 4, W >= 4, Cin %% 64 == 0, "
                   "Cout %% 64 == 0 or Cout == 32)", batch, h_in, w_in, c_in, c_out);
     GANCE_REQUIRE(aligned16(x) && aligned16(weight_phase) && aligned16(out), GANCE_E_ALIGN,
                   "gance_modconv3x3_up2_fused: pointers must be 16-byte aligned");

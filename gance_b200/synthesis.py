@@ -115,6 +115,12 @@ def _ptr(tensor: Optional[torch.Tensor]) -> Optional[int]:
 class GeneratorOnDevice:
     """One generator's weights resident in HBM in kernel layout, plus per-batch work buffers."""
 
+    # smallest input side run as the fused up-convolution (`_up_form`). 4 = every up-convolution with Cout % 64 == 0: at 4^2 / 8^2
+    # one 16 x 8-cell tile covers a whole sample (the TMA box is larger than the image, the rest is zero fill) and most of
+    # the tile's MMAs are wasted, but those layers are bound by the weight bytes each CTA pulls through L2 - 9 Cin Cout
+    # instead of the folded form's 36: 4->8 68 -> 26 us, 8->16 72 -> 45 us at batch 32 (tools/profile_layers.py --fused-min-side)
+    fused_min_in_resolution = 4
+
     def __init__(self, spec: GeneratorSpec, variables: Dict[str, np.ndarray], device: torch.device, mode: str = "fp16",
                  noise_seed: Optional[int] = None, up_form: Optional[str] = None) -> None:
         """
@@ -217,17 +223,17 @@ class GeneratorOnDevice:
         """
         Which kernel an up-convolution runs as (include/gance_b200.h):
           "fused"  - 4-phase GEMM with the FIR applied on chip (upconv_fused.cu): one launch, x read once, output written
-                     once, 1.52x the algorithmic MACs. Default for input sides >= 16 with Cout % 64 == 0 (measured on
+                     once, 1.52x the algorithmic MACs. Default for every input side with Cout % 64 == 0 (measured on
                      B200, batch 32: 256->512 710 us vs 1280 phase / 1080 folded; 128->256 525 vs 794; 64->128 460 vs
                      595; 32->64 282 vs 282 - profiles/README.md).
           "phase"  - 4-phase GEMM + separate FIR pass through a 16-bit scratch tensor (upconv_phase.cu).
-          "folded" - one N = 4*Cout SAME convolution at the input resolution, 4x the algorithmic MACs: the small layers
-                     (latency-bound) and 512->1024 (Cout = 32: the fused epilogue is issue-bound there, 1756 vs 1118 us).
+          "folded" - one N = 4*Cout SAME convolution at the input resolution, 4x the algorithmic MACs: 512->1024
+                     (Cout = 32: the fused epilogue is issue-bound there, 1756 vs 1118 us).
         The constructor's `up_form` forces a form where the shape is eligible (A/B measurements).
         """
         forced = self.forced_up_form
         phase_ok = conv.in_resolution >= 32 and conv.in_channels % 64 == 0 and conv.out_channels % 64 == 0
-        fused_ok = (conv.in_resolution >= 16 and conv.in_channels % 64 == 0
+        fused_ok = (conv.in_resolution >= self.fused_min_in_resolution and conv.in_channels % 64 == 0
                     and (conv.out_channels % 64 == 0 or conv.out_channels == 32))
         if forced == "folded":
             return "folded"
@@ -235,7 +241,7 @@ class GeneratorOnDevice:
             return "phase" if phase_ok else "folded"
         if forced == "fused":
             return "fused" if fused_ok else "folded"
-        if fused_ok and conv.out_channels % 64 == 0:  # in_resolution >= 16 (16->32: 100 us fused vs 132 us folded at batch 32)
+        if fused_ok and conv.out_channels % 64 == 0:  # (16->32: 100 us fused vs 132 us folded at batch 32)
             return "fused"
         return "folded"
 

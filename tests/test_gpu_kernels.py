@@ -662,7 +662,8 @@ def test_phase_up_convolution_matches_oracle(lib, mode, cin, cout, side, batch):
 
 @pytest.mark.parametrize("mode", ["bf16", "fp16"])
 @pytest.mark.parametrize("cin,cout,side,batch", [(64, 64, 16, 2), (128, 64, 32, 1), (256, 128, 24, 3), (512, 256, 16, 2),
-                                                 (64, 32, 40, 2), (128, 64, 64, 1)])
+                                                 (64, 32, 40, 2), (128, 64, 64, 1), (512, 512, 4, 3), (512, 512, 8, 2),
+                                                 (128, 64, 4, 1)])
 def test_fused_up_convolution_matches_oracle(lib, mode, cin, cout, side, batch):
     """Single-CTA kernel against the oracle, then the CTA-pair flavour of the same 16 x 8-cell kernel (cta_group::2, half of
     the weight rows per CTA; side 24 x batch 3 and side 40 give odd tile counts = a ghost tile) bit for bit against it."""
@@ -690,7 +691,8 @@ def test_fused_up_convolution_cta_pair_matches_oracle(lib, mode, cin, cout, side
 def _fused_up_case(lib, mode, cin, cout, side, batch):
     """gance_scale_channels + gance_modconv3x3_up2_fused (4-phase transposed-conv GEMM with the FIR applied from a
     shared-memory patch of t) against the transposed-conv + upfirdn oracle. Sides 24 and 40 give ragged tiles (output
-    48 / 80 pixels against 28 x 12-pixel tiles); Cout = 32 is the 1024^2 layer's single 32-channel chunk."""
+    48 / 80 pixels against 28 x 12-pixel tiles); Cout = 32 is the 1024^2 layer's single 32-channel chunk; sides 4 and 8 are
+    the 4^2 -> 8^2 / 8^2 -> 16^2 layers (one tile per sample or two, TMA boxes larger than the image)."""
     from gance_b200.synthesis import phase_up_weight
 
     code, dt = MODE_CODES[mode]
