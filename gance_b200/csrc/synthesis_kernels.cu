@@ -10,13 +10,16 @@ namespace gance {
 // G_mapping + truncation: 8 dense 512x512 layers over the batch, ONE LAUNCH PER LAYER so that every layer's 1 MB of
 // weights is pulled through all 148 SMs instead of one SM per sample (the single-launch, CTA-per-sample version spent
 // 264 us on a batch of 32 - 3 % of a step - waiting on one SM's L2 path; this one takes 8 x ~4 us).
-// CTA = 8 output features x 8 samples; 256 threads = 64 outputs x 4 slices of K, reduced through shared memory.
+// CTA = 8 output features x 8 samples; 1024 threads = 64 outputs x 16 slices of K, reduced through shared memory.
 // W is [layer][in][out]: the 8 features of a CTA are one 32-byte sector per input row.
 // The layers ping-pong between rows 0 and 1 of each sample's w+ block (no scratch argument needed); the last layer
 // applies the truncation lerp and mapping_broadcast_kernel copies the result to the remaining rows.
 // ------------------------------------------------------------------------------------------------
 constexpr int kLatent = 512;
-constexpr int kMapFeatures = 8, kMapSamples = 8, kMapSlices = 4;
+// A layer is latency-bound (1 MB of weights, 32 x 512 x 512 MACs): the 512-long dot product of one (sample, feature) is cut
+// into 16 slices of 32 so that every thread issues all of its 64 loads at once - one round trip to L2 per layer instead of
+// the 32 dependent ones of the first version (4 slices, 4 loads in flight: 14-19 us per layer).
+constexpr int kMapFeatures = 8, kMapSamples = 8, kMapSlices = 16;
 
 template <bool FIRST, bool LAST>
 __global__ void __launch_bounds__(kMapFeatures * kMapSamples * kMapSlices)
@@ -32,29 +35,44 @@ mapping_layer_kernel(const float* __restrict__ x, long long x_stride, int batch,
     const int s = min(s0 + s_local, batch - 1);
     if (FIRST) {  // normalize_2nd_moment of z: x * rsqrt(mean(x^2) + 1e-8); one warp per sample
         const int warp = tid >> 5, lane = tid & 31;
-        const float* row = x + (size_t)min(s0 + warp, batch - 1) * x_stride;
-        float sq = 0.f;
-        for (int k = lane; k < kLatent; k += 32) sq = fmaf(row[k], row[k], sq);
+        if (warp < kMapSamples) {
+            const float* row = x + (size_t)min(s0 + warp, batch - 1) * x_stride;
+            float sq = 0.f;
+            for (int k = lane; k < kLatent; k += 32) sq = fmaf(row[k], row[k], sq);
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
-        if (lane == 0) scale[warp] = rsqrtf(sq * (1.0f / kLatent) + 1e-8f);
+            for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+            if (lane == 0) scale[warp] = rsqrtf(sq * (1.0f / kLatent) + 1e-8f);
+        }
         __syncthreads();
     }
     const float* xr = x + (size_t)s * x_stride + slice * (kLatent / kMapSlices);
     const float* w = weight + (size_t)slice * (kLatent / kMapSlices) * kLatent + j;
+    constexpr int kPerSlice = kLatent / kMapSlices;  // 32, in two halves of 16 (1024 threads per CTA = 64 registers each)
     float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
-#pragma unroll 4
-    for (int k = 0; k < kLatent / kMapSlices; k += 4) {
-        acc0 = fmaf(__ldg(xr + k), __ldg(w + (size_t)k * kLatent), acc0);
-        acc1 = fmaf(__ldg(xr + k + 1), __ldg(w + (size_t)(k + 1) * kLatent), acc1);
-        acc2 = fmaf(__ldg(xr + k + 2), __ldg(w + (size_t)(k + 2) * kLatent), acc2);
-        acc3 = fmaf(__ldg(xr + k + 3), __ldg(w + (size_t)(k + 3) * kLatent), acc3);
+#pragma unroll
+    for (int half = 0; half < kPerSlice; half += 16) {
+        float xv[16], wv[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            wv[k] = __ldg(w + (size_t)(half + k) * kLatent);
+            xv[k] = __ldg(xr + half + k);
+        }
+#pragma unroll
+        for (int k = 0; k < 16; k += 4) {
+            acc0 = fmaf(xv[k], wv[k], acc0);
+            acc1 = fmaf(xv[k + 1], wv[k + 1], acc1);
+            acc2 = fmaf(xv[k + 2], wv[k + 2], acc2);
+            acc3 = fmaf(xv[k + 3], wv[k + 3], acc3);
+        }
     }
     partial[slice][tid % (kMapFeatures * kMapSamples)] = (acc0 + acc1) + (acc2 + acc3);
     __syncthreads();
     if (slice == 0 && s0 + s_local < batch) {
         const int o = tid;
-        float total = (partial[0][o] + partial[1][o]) + (partial[2][o] + partial[3][o]);
+        float total = 0.f;
+#pragma unroll
+        for (int q = 0; q < kMapSlices; q += 4)
+            total += (partial[q][o] + partial[q + 1][o]) + (partial[q + 2][o] + partial[q + 3][o]);
         if (FIRST) total *= scale[s_local];  // the normalisation is a per-sample scalar: apply it to the dot product
         float value = bias_lrelu(total + __ldg(bias + j));
         if (LAST && psi != 1.0f) {  // G_main 'Truncation': lerp(dlatent_avg, w, psi)
@@ -116,38 +134,43 @@ __global__ void __launch_bounds__(256) style_demod_kernel(const float* __restric
 // ------------------------------------------------------------------------------------------------
 // Styles and demodulation coefficients of EVERY layer of a generator in two launches.
 // The per-layer affine weights are concatenated column-wise into mod_weight_cat [512, total_cols];
-// a chunk = 32 consecutive columns of one layer. CTA = 32 columns x 4 slices of the 512-long (or
+// a chunk = 32 consecutive columns of one layer. CTA = 32 columns x 16 slices of the 512-long (or
 // Cin-long) reduction, for 8 samples at a time (the w vectors / squared styles sit in shared memory).
 // Outputs are layer-major so each layer's [B, C] block is contiguous: block of layer L starts at
 // B * col0(L).
 // ------------------------------------------------------------------------------------------------
 constexpr int kStyleSamples = 8;
 
-__global__ void __launch_bounds__(128) styles_all_kernel(const float* __restrict__ wplus, int batch, int num_ws,
-                                                         const float* __restrict__ mod_weight_cat, int total_cols,
-                                                         const float* __restrict__ mod_bias_cat,
-                                                         const int4* __restrict__ chunks,
-                                                         float* __restrict__ styles_out) {
+constexpr int kStyleSlices = 16;  // slices of the reduction: every thread has its 32 (or Cin / 16) weight loads in flight at once
+
+__global__ void __launch_bounds__(32 * kStyleSlices) styles_all_kernel(const float* __restrict__ wplus, int batch, int num_ws,
+                                                                       const float* __restrict__ mod_weight_cat, int total_cols,
+                                                                       const float* __restrict__ mod_bias_cat,
+                                                                       const int4* __restrict__ chunks,
+                                                                       float* __restrict__ styles_out) {
     __shared__ float w[kStyleSamples][kLatent];
-    __shared__ float part[4][kStyleSamples][32];
+    __shared__ float part[kStyleSlices][kStyleSamples][32];
     const int4 chunk = chunks[blockIdx.x];  // x: w_index, y: first column of the layer, z: Cin, w: first column of the chunk inside the layer
     const int b0 = blockIdx.y * kStyleSamples;
     for (int i = threadIdx.x; i < kStyleSamples * kLatent; i += blockDim.x) {
         const int sidx = i / kLatent, k = i % kLatent;
         w[sidx][k] = b0 + sidx < batch ? wplus[((size_t)(b0 + sidx) * num_ws + chunk.x) * kLatent + k] : 0.f;
     }
-    __syncthreads();
     const int col = threadIdx.x & 31, slice = threadIdx.x >> 5;
     const int gcol = chunk.y + chunk.w + col;
+    constexpr int kPerSlice = kLatent / kStyleSlices;  // 32
+    const float* m = mod_weight_cat + (size_t)(slice * kPerSlice) * total_cols + gcol;
+    float mv[kPerSlice];
+#pragma unroll
+    for (int k = 0; k < kPerSlice; ++k) mv[k] = __ldg(m + (size_t)k * total_cols);
+    __syncthreads();
     float acc[kStyleSamples];
 #pragma unroll
     for (int i = 0; i < kStyleSamples; ++i) acc[i] = 0.f;
-    const float* m = mod_weight_cat + (size_t)(slice * (kLatent / 4)) * total_cols + gcol;
-#pragma unroll 4
-    for (int k = 0; k < kLatent / 4; ++k) {
-        const float mv = __ldg(m + (size_t)k * total_cols);
 #pragma unroll
-        for (int i = 0; i < kStyleSamples; ++i) acc[i] = fmaf(w[i][slice * (kLatent / 4) + k], mv, acc[i]);
+    for (int k = 0; k < kPerSlice; ++k) {
+#pragma unroll
+        for (int i = 0; i < kStyleSamples; ++i) acc[i] = fmaf(w[i][slice * kPerSlice + k], mv[k], acc[i]);
     }
 #pragma unroll
     for (int i = 0; i < kStyleSamples; ++i) part[slice][i][col] = acc[i];
@@ -155,7 +178,10 @@ __global__ void __launch_bounds__(128) styles_all_kernel(const float* __restrict
     for (int i = threadIdx.x; i < kStyleSamples * 32; i += blockDim.x) {
         const int sidx = i >> 5, c = i & 31;
         if (b0 + sidx >= batch) continue;
-        const float v = (part[0][sidx][c] + part[1][sidx][c]) + (part[2][sidx][c] + part[3][sidx][c]);
+        float v = 0.f;
+#pragma unroll
+        for (int q = 0; q < kStyleSlices; q += 4)
+            v += (part[q][sidx][c] + part[q + 1][sidx][c]) + (part[q + 2][sidx][c] + part[q + 3][sidx][c]);
         styles_out[(size_t)batch * chunk.y + (size_t)(b0 + sidx) * chunk.z + chunk.w + c] =
             v + mod_bias_cat[chunk.y + chunk.w + c] + 1.0f;
     }
@@ -169,14 +195,22 @@ struct DemodChunk {
     int demod_col0;   // first column of the layer in the concatenated demod space
 };
 
-__global__ void __launch_bounds__(128) demod_all_kernel(const float* __restrict__ styles_all, int batch,
-                                                        const float* __restrict__ wsq_cat,
-                                                        const DemodChunk* __restrict__ chunks,
-                                                        float* __restrict__ demod_out) {
+__global__ void __launch_bounds__(32 * kStyleSlices) demod_all_kernel(const float* __restrict__ styles_all, int batch,
+                                                                      const float* __restrict__ wsq_cat,
+                                                                      const DemodChunk* __restrict__ chunks,
+                                                                      float* __restrict__ demod_out) {
     __shared__ float s2[kStyleSamples][kLatent];
-    __shared__ float part[4][kStyleSamples][32];
+    __shared__ float part[kStyleSlices][kStyleSamples][32];
     const DemodChunk chunk = chunks[blockIdx.x];
     const int b0 = blockIdx.y * kStyleSamples;
+    const int col = threadIdx.x & 31, slice = threadIdx.x >> 5;
+    const int per_slice = (chunk.c_in + kStyleSlices - 1) / kStyleSlices;  // 1 ... 32 rows per slice
+    const int rows = min(per_slice, chunk.c_in - slice * per_slice);       // <= 0 for the slices past a short Cin
+    const float* m = wsq_cat + chunk.wsq_offset + (size_t)(slice * per_slice) * chunk.c_out + chunk.co0 + col;
+    constexpr int kMaxPerSlice = kLatent / kStyleSlices;
+    float mv[kMaxPerSlice];
+#pragma unroll
+    for (int k = 0; k < kMaxPerSlice; ++k) mv[k] = k < rows ? __ldg(m + (size_t)k * chunk.c_out) : 0.f;
     for (int i = threadIdx.x; i < kStyleSamples * chunk.c_in; i += blockDim.x) {
         const int sidx = i / chunk.c_in, ci = i % chunk.c_in;
         float v = 0.f;
@@ -184,17 +218,15 @@ __global__ void __launch_bounds__(128) demod_all_kernel(const float* __restrict_
         s2[sidx][ci] = v * v;
     }
     __syncthreads();
-    const int col = threadIdx.x & 31, slice = threadIdx.x >> 5;
-    const int per_slice = chunk.c_in / 4;  // Cin is a multiple of 32
     float acc[kStyleSamples];
 #pragma unroll
     for (int i = 0; i < kStyleSamples; ++i) acc[i] = 0.f;
-    const float* m = wsq_cat + chunk.wsq_offset + (size_t)(slice * per_slice) * chunk.c_out + chunk.co0 + col;
-#pragma unroll 4
-    for (int k = 0; k < per_slice; ++k) {
-        const float mv = __ldg(m + (size_t)k * chunk.c_out);
 #pragma unroll
-        for (int i = 0; i < kStyleSamples; ++i) acc[i] = fmaf(s2[i][slice * per_slice + k], mv, acc[i]);
+    for (int k = 0; k < kMaxPerSlice; ++k) {
+        if (k < rows) {
+#pragma unroll
+            for (int i = 0; i < kStyleSamples; ++i) acc[i] = fmaf(s2[i][slice * per_slice + k], mv[k], acc[i]);
+        }
     }
 #pragma unroll
     for (int i = 0; i < kStyleSamples; ++i) part[slice][i][col] = acc[i];
@@ -202,7 +234,10 @@ __global__ void __launch_bounds__(128) demod_all_kernel(const float* __restrict_
     for (int i = threadIdx.x; i < kStyleSamples * 32; i += blockDim.x) {
         const int sidx = i >> 5, c = i & 31;
         if (b0 + sidx >= batch) continue;
-        const float v = (part[0][sidx][c] + part[1][sidx][c]) + (part[2][sidx][c] + part[3][sidx][c]);
+        float v = 0.f;
+#pragma unroll
+        for (int q = 0; q < kStyleSlices; q += 4)
+            v += (part[q][sidx][c] + part[q + 1][sidx][c]) + (part[q + 2][sidx][c] + part[q + 3][sidx][c]);
         demod_out[(size_t)batch * chunk.demod_col0 + (size_t)(b0 + sidx) * chunk.c_out + chunk.co0 + c] =
             rsqrtf(v + 1e-8f);
     }
@@ -295,9 +330,9 @@ __global__ void __launch_bounds__(256) upfir2x_pad_kernel(const T* __restrict__ 
 
 // ------------------------------------------------------------------------------------------------
 // ToRGB (1x1 modulated conv, no demod) + bias + skip upsample-add (+ uint8 conversion).
-// A group of LANES lanes owns one pixel and splits its channels in 16-byte vectors, so a warp
-// reads 32 consecutive 16-byte vectors: fully coalesced. wmod[c][j] = styles[b,c]*weight[c,j]
-// sits in shared memory (one sample per CTA row of the grid).
+// A group of LANES (<= 8) lanes owns kTorgbPixels pixels per pass and splits their channels in 16-byte vectors (a group
+// reads 128 consecutive bytes). wmod[c] = styles[b,c] * weight[c,0..2] sits in shared memory (one sample per CTA row of
+// the grid).
 // ------------------------------------------------------------------------------------------------
 // ------------------------------------------------------------------------------------------------
 // x[b,h,w,c] * styles[b,c] -> out (the pre-scaling of a modulated convolution's input when the
@@ -325,6 +360,14 @@ __global__ void __launch_bounds__(256) scale_channels_kernel(const T* __restrict
     }
 }
 
+// ToRGB launch shape (ncu of the first version, 64^2 x 512 channels: 69 % issue-slot use against 30 % DRAM - the layer was
+// bound by its own bookkeeping: a whole warp per pixel = 15 shuffle + add pairs per colour and pixel, three scalar shared
+// loads per channel, one divergent tail per pixel). Now a group of at most 8 lanes owns kTorgbPixels pixels per pass:
+// 3 shuffle steps, one float4 weight read per channel shared by the group's pixels, and the lanes of a group finish one
+// pixel each side by side; the four groups of a warp read four 128-byte runs.
+constexpr int kTorgbPixels = 4;
+constexpr int kTorgbMaxLanes = 8;
+
 template <typename T, int LANES>
 __global__ void __launch_bounds__(256) torgb_skip_kernel(const T* __restrict__ x, int h, int w, int channels,
                                                          const float* __restrict__ styles,
@@ -334,58 +377,80 @@ __global__ void __launch_bounds__(256) torgb_skip_kernel(const T* __restrict__ x
                                                          float* __restrict__ y_out,
                                                          uint8_t* __restrict__ frames, int* nonfinite) {
     constexpr int V = Vec<T>::N;
-    // [3][V][channels / V]: channel c = cv * V + k sits at slot k * (channels / V) + cv, so the lanes of a group
-    // (consecutive cv, same k) read consecutive words - [channels][3] order put them 3 * V words apart, an 8-way
-    // bank conflict on every weight read
-    extern __shared__ float wmod[];
+    // [V][channels / V] float4 (r, g, b, -): channel c = cv * V + k sits at slot k * (channels / V) + cv, so the lanes of
+    // a group (consecutive cv, same k) read consecutive 16-byte words and the groups of a warp broadcast
+    extern __shared__ float4 wmod[];
     const int b = blockIdx.y;
     const int vec_per_pixel = channels / V;
-    for (int i = threadIdx.x; i < channels * 3; i += blockDim.x) {
-        const int c = i / 3, colour = i - c * 3;
-        wmod[colour * channels + (c % V) * vec_per_pixel + c / V] = styles[(size_t)b * channels + c] * weight[i];
+    for (int c = threadIdx.x; c < channels; c += blockDim.x) {
+        const float s = styles[(size_t)b * channels + c];
+        wmod[(c % V) * vec_per_pixel + c / V] = make_float4(s * weight[3 * c], s * weight[3 * c + 1], s * weight[3 * c + 2], 0.f);
     }
     __syncthreads();
     const int pixels = h * w;
     const int group = threadIdx.x / LANES, lane = threadIdx.x % LANES;
     const int groups_per_block = blockDim.x / LANES;
     // the loop bound is CTA-uniform so the group shuffles below always see a full warp
-    for (int base = blockIdx.x * groups_per_block; base < pixels; base += gridDim.x * groups_per_block) {
-        const int p = base + group;
-        const bool valid = p < pixels;
-        const T* px = x + ((size_t)b * pixels + (valid ? p : 0)) * channels;
-        float r = 0.f, g = 0.f, bl = 0.f;
-        for (int cv = lane; valid && cv < vec_per_pixel; cv += LANES) {
-            Vec<T> v;
-            v.load(px + cv * V);
-            float f[V];
-            v.to_float(f);
+    for (int base = blockIdx.x * groups_per_block * kTorgbPixels; base < pixels; base += gridDim.x * groups_per_block * kTorgbPixels) {
+        const int p0 = base + group * kTorgbPixels;
+        const T* px[kTorgbPixels];
+#pragma unroll
+        for (int i = 0; i < kTorgbPixels; ++i) px[i] = x + ((size_t)b * pixels + (p0 + i < pixels ? p0 + i : 0)) * channels;
+        float acc[kTorgbPixels][3];
+#pragma unroll
+        for (int i = 0; i < kTorgbPixels; ++i) acc[i][0] = acc[i][1] = acc[i][2] = 0.f;
+#pragma unroll 2
+        for (int cv = lane; cv < vec_per_pixel; cv += LANES) {
+            Vec<T> v[kTorgbPixels];
+#pragma unroll
+            for (int i = 0; i < kTorgbPixels; ++i) v[i].load(px[i] + cv * V);
+            float f[kTorgbPixels][V];
+#pragma unroll
+            for (int i = 0; i < kTorgbPixels; ++i) v[i].to_float(f[i]);
 #pragma unroll
             for (int k = 0; k < V; ++k) {
-                const float* wm = wmod + k * vec_per_pixel + cv;
-                r = fmaf(f[k], wm[0], r);
-                g = fmaf(f[k], wm[channels], g);
-                bl = fmaf(f[k], wm[2 * channels], bl);
+                const float4 wv = wmod[k * vec_per_pixel + cv];
+#pragma unroll
+                for (int i = 0; i < kTorgbPixels; ++i) {
+                    acc[i][0] = fmaf(f[i][k], wv.x, acc[i][0]);
+                    acc[i][1] = fmaf(f[i][k], wv.y, acc[i][1]);
+                    acc[i][2] = fmaf(f[i][k], wv.z, acc[i][2]);
+                }
             }
         }
 #pragma unroll
         for (int o = LANES / 2; o > 0; o >>= 1) {
-            r += __shfl_xor_sync(0xffffffffu, r, o);
-            g += __shfl_xor_sync(0xffffffffu, g, o);
-            bl += __shfl_xor_sync(0xffffffffu, bl, o);
-        }
-        if (lane == 0 && valid) {
-            r += bias[0]; g += bias[1]; bl += bias[2];
-            const int hh = p / w, ww = p % w;
-            if (y_prev != nullptr) {
-                float4 up = upsample_tap(y_prev, b, h >> 1, w >> 1, hh, ww);
-                r += up.x; g += up.y; bl += up.z;
+#pragma unroll
+            for (int i = 0; i < kTorgbPixels; ++i) {
+                acc[i][0] += __shfl_xor_sync(0xffffffffu, acc[i][0], o);
+                acc[i][1] += __shfl_xor_sync(0xffffffffu, acc[i][1], o);
+                acc[i][2] += __shfl_xor_sync(0xffffffffu, acc[i][2], o);
             }
-            if (y_out != nullptr)
-                reinterpret_cast<float4*>(y_out)[(size_t)b * pixels + p] = make_float4(r, g, bl, 0.f);
-            if (frames != nullptr) {
-                uint8_t* f = frames + ((size_t)b * pixels + p) * 3;
-                f[0] = to_u8(r); f[1] = to_u8(g); f[2] = to_u8(bl);
-                flag_nonfinite(nonfinite, r, g, bl);
+        }
+        // every lane of the group holds all sums: lane j finishes pixels j, j + LANES, ...
+#pragma unroll
+        for (int t = 0; t < (kTorgbPixels + LANES - 1) / LANES; ++t) {
+            const int i = t * LANES + lane;
+            float r = 0.f, g = 0.f, bl = 0.f;
+#pragma unroll
+            for (int j = 0; j < kTorgbPixels; ++j) {
+                if (j == i) { r = acc[j][0]; g = acc[j][1]; bl = acc[j][2]; }
+            }
+            const int p = p0 + i;
+            if (i < kTorgbPixels && p < pixels) {
+                r += bias[0]; g += bias[1]; bl += bias[2];
+                const int hh = p / w, ww = p % w;
+                if (y_prev != nullptr) {
+                    float4 up = upsample_tap(y_prev, b, h >> 1, w >> 1, hh, ww);
+                    r += up.x; g += up.y; bl += up.z;
+                }
+                if (y_out != nullptr)
+                    reinterpret_cast<float4*>(y_out)[(size_t)b * pixels + p] = make_float4(r, g, bl, 0.f);
+                if (frames != nullptr) {
+                    uint8_t* f = frames + ((size_t)b * pixels + p) * 3;
+                    f[0] = to_u8(r); f[1] = to_u8(g); f[2] = to_u8(bl);
+                    flag_nonfinite(nonfinite, r, g, bl);
+                }
             }
         }
     }
@@ -560,11 +625,11 @@ static int launch_torgb(const void* x, int batch, int h, int w, int channels, co
                         const float* weight, const float* bias, const float* y_prev, float* y_out,
                         uint8_t* frames, cudaStream_t s) {
     const int vec_per_pixel = channels / Vec<T>::N;
-    const size_t smem = (size_t)channels * 3 * sizeof(float);
+    const size_t smem = (size_t)channels * sizeof(float4);
     int lanes = 1;
-    while (lanes < 32 && lanes < vec_per_pixel) lanes <<= 1;
+    while (lanes < kTorgbMaxLanes && lanes < vec_per_pixel) lanes <<= 1;
     const int groups = 256 / lanes;
-    int gx = (h * w + groups - 1) / groups;
+    int gx = (h * w + groups * kTorgbPixels - 1) / (groups * kTorgbPixels);
     const int cap = (148 * 8 + batch - 1) / batch;
     if (gx > cap) gx = cap;
     if (gx < 1) gx = 1;
@@ -576,9 +641,7 @@ static int launch_torgb(const void* x, int batch, int h, int w, int channels, co
         case 1: GANCE_TORGB(1); break;
         case 2: GANCE_TORGB(2); break;
         case 4: GANCE_TORGB(4); break;
-        case 8: GANCE_TORGB(8); break;
-        case 16: GANCE_TORGB(16); break;
-        default: GANCE_TORGB(32); break;
+        default: GANCE_TORGB(8); break;
     }
 #undef GANCE_TORGB
     return check_launch("torgb_skip_kernel");
@@ -645,12 +708,12 @@ int gance_styles_all(const float* wplus, int batch, int num_ws, const float* mod
     GANCE_REQUIRE(aligned16(style_chunks), GANCE_E_ALIGN, "gance_styles_all: style_chunks must be 16-byte aligned");
     cudaStream_t s = (cudaStream_t)stream;
     const int sample_groups = (batch + kStyleSamples - 1) / kStyleSamples;
-    styles_all_kernel<<<dim3(n_style_chunks, sample_groups), 128, 0, s>>>(
+    styles_all_kernel<<<dim3(n_style_chunks, sample_groups), 32 * kStyleSlices, 0, s>>>(
         wplus, batch, num_ws, mod_weight_cat, total_cols, mod_bias_cat, (const int4*)style_chunks, styles_out);
     int rc = check_launch("styles_all_kernel");
     if (rc != GANCE_OK || n_demod_chunks == 0) return rc;
     GANCE_REQUIRE(wsq_cat && demod_chunks && demod_out, GANCE_E_NULL, "gance_styles_all: NULL demod pointer");
-    demod_all_kernel<<<dim3(n_demod_chunks, sample_groups), 128, 0, s>>>(styles_out, batch, wsq_cat,
+    demod_all_kernel<<<dim3(n_demod_chunks, sample_groups), 32 * kStyleSlices, 0, s>>>(styles_out, batch, wsq_cat,
                                                                         (const DemodChunk*)demod_chunks, demod_out);
     return check_launch("demod_all_kernel");
 }
