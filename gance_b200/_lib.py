@@ -22,6 +22,7 @@ _SIGNATURES = {
     "gance_launch_count": (c_ulonglong, []),
     "gance_set_nonfinite_flag": (c_int, [c_void_p]),
     "gance_set_conv_pairing": (c_int, [c_int]),
+    "gance_set_conv_two_rows": (c_int, [c_int]),
     "gance_mapping": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_float, c_int, c_void_p, c_void_p]),
     "gance_style_demod": (
         c_int,

@@ -178,10 +178,10 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int group, in
             if (UP) {
                 const float2 top = __ldg(reinterpret_cast<const float2*>(noise_b + (size_t)(2 * hv) * out_w + 2 * wv));
                 const float2 bot = __ldg(reinterpret_cast<const float2*>(noise_b + (size_t)(2 * hv + 1) * out_w + 2 * wv));
-                nz4[0] = top.x * p.noise_strength; nz4[1] = top.y * p.noise_strength;
-                nz4[2] = bot.x * p.noise_strength; nz4[3] = bot.y * p.noise_strength;
+                nz4[0] = __fmul_rn(top.x, p.noise_strength); nz4[1] = __fmul_rn(top.y, p.noise_strength);
+                nz4[2] = __fmul_rn(bot.x, p.noise_strength); nz4[3] = __fmul_rn(bot.y, p.noise_strength);
             } else {
-                nz4[0] = __ldg(noise_b + (size_t)hv * out_w + wv) * p.noise_strength;
+                nz4[0] = __fmul_rn(__ldg(noise_b + (size_t)hv * out_w + wv), p.noise_strength);
             }
         }
         float red = 0.f, green = 0.f, blue = 0.f;
@@ -286,7 +286,7 @@ __device__ __forceinline__ uint32_t pack_pair(float a, float b, __nv_bfloat16*) 
 // The same staging also serves the 64-channel fused-ToRGB flavour (COEF_SMEM): 48 instead of 96 coefficient registers let it
 // keep the next tile's operands in registers and run a third epilogue group.
 template <typename T, int N_TILE, int C, bool UP, bool RGB, int GROUPS, int TILE_W_LOG2 = -1, bool PAIR = false, int APG = 1,
-          bool STAGED = false, bool COEF_SMEM = (C > 64)>
+          bool STAGED = false, bool COEF_SMEM = (C > 64), bool ROWS2 = false>
 __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int group, int warp, int lane, int total_tiles,
                                                    uint32_t tmem_base, uint64_t* tmem_full_bar,
                                                    uint64_t* tmem_empty_bar, uint8_t* stage_tile = nullptr,
@@ -306,10 +306,15 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
         return PAIR ? decode_pair_item(p, tile, pair_rank, N_TILE, ghost) : decode_tile(p, tile, N_TILE);
     };
     static_assert(C % 32 == 0 && C <= 128, "register-resident coefficients: at most 16 channels per thread, or per chunk from shared memory");
-    static_assert(N_TILE == (UP ? 4 * C : C), "GEMM columns = channels (x 4 phases for the folded up-convolution)");
+    static_assert(N_TILE == (UP ? 4 * C : (ROWS2 ? 2 * C : C)), "GEMM columns = channels (x 4 phases for the folded up-convolution, x 2 image rows for ROWS2)");
+    static_assert(!ROWS2 || (!UP && !STAGED && !PAIR && TILE_W_LOG2 >= 0), "ROWS2: plain convolution of the single-CTA halo kernel");
     static_assert(!kCoefSmem || !UP, "the shared-memory coefficient cache serves plain convolutions");
     constexpr int CPT = kCoefSmem ? 8 : C / 4;  // coefficient registers: all of the thread's channels, or one chunk's
-    constexpr int CHUNKS = N_TILE / 32;  // 32-column accumulator chunks per tile
+    // ROWS2 (modconv3x3_halo2_kernel): accumulator row (hl, wl) holds the pixels (2 hl, wl) in columns [0, C) and (2 hl + 1, wl)
+    // in columns [C, 2C) - the tile is drained as SUB = 2 sub-tiles, each exactly like a tile of the one-row kernel
+    constexpr int SUB = ROWS2 ? 2 : 1;
+    constexpr int CHUNKS = N_TILE / 32 / SUB;  // 32-column accumulator chunks per (sub-)tile
+    auto image_row = [&](int h_local, int py) { return ROWS2 ? 2 * h_local + py : h_local; };
     const int quarter = warp & 3;
     const int q4 = lane & 3, r8 = lane >> 2;
     const int out_w = UP ? 2 * p.w_out : p.w_out, out_h = UP ? 2 * p.h_out : p.h_out;
@@ -350,7 +355,7 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
         float3 skip;                // prefetch flavour: the four taps already combined (3 registers instead of 19)
         int own_h, own_w;
     };
-    auto request = [&](int tile) {
+    auto request = [&](int tile, int py) {
         Ahead n;
         n.t = decode(tile);
 #ifdef GANCE_ABL_NOLOADS
@@ -362,7 +367,7 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
             n.p00 = n.p01 = n.p10 = n.p11 = make_float4(0.f, 0.f, 0.f, 0.f);
             n.w01 = n.w10 = n.w11 = 0.f;
             n.skip = make_float3(0.f, 0.f, 0.f);
-            n.own_h = n.t.h0 + (q4 == 0 ? hl[0] : q4 == 1 ? hl[1] : q4 == 2 ? hl[2] : hl[3]);
+            n.own_h = n.t.h0 + image_row(q4 == 0 ? hl[0] : q4 == 1 ? hl[1] : q4 == 2 ? hl[2] : hl[3], py);
             n.own_w = n.t.w0 + (q4 == 0 ? wl[0] : q4 == 1 ? wl[1] : q4 == 2 ? wl[2] : wl[3]);
             return n;
         }
@@ -370,7 +375,7 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
         const float* noise_b = p.noise ? p.noise + (size_t)n.t.b0 * p.noise_batch_stride : nullptr;
 #pragma unroll
         for (int rr = 0; rr < 4; ++rr) {
-            const int h = n.t.h0 + hl[rr], w = n.t.w0 + wl[rr];
+            const int h = n.t.h0 + image_row(hl[rr], py), w = n.t.w0 + wl[rr];
             if (UP) {
                 float2 top = make_float2(0.f, 0.f), bot = top;
                 if (noise_b != nullptr) {
@@ -390,7 +395,7 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
         n.skip = make_float3(0.f, 0.f, 0.f);
         n.own_h = n.own_w = 0;
         if (RGB) {  // this lane finishes the pixel of row rr == q4
-            n.own_h = n.t.h0 + (q4 == 0 ? hl[0] : q4 == 1 ? hl[1] : q4 == 2 ? hl[2] : hl[3]);
+            n.own_h = n.t.h0 + image_row(q4 == 0 ? hl[0] : q4 == 1 ? hl[1] : q4 == 2 ? hl[2] : hl[3], py);
             n.own_w = n.t.w0 + (q4 == 0 ? wl[0] : q4 == 1 ? wl[1] : q4 == 2 ? wl[2] : wl[3]);
             if (p.y_prev != nullptr) {
                 // upsample_2d(k=[1,3,3,1]): y[2a] = .25 p[a-1] + .75 p[a]; y[2a+1] = .75 p[a] + .25 p[a+1]; taps outside
@@ -453,19 +458,25 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
 #endif
     int tile = walk_first + group * walk_stride;
     Ahead ahead;
-    if (kAheadInRegisters && tile < total_tiles) ahead = request(tile);
+    static_assert(!ROWS2 || kAheadInRegisters, "ROWS2 keeps the next sub-tile's operands in registers");
+    if (kAheadInRegisters && tile < total_tiles) ahead = request(tile, 0);
     for (; tile < total_tiles; tile += GROUPS * walk_stride, ++visit) {
         const int acc = group + GROUPS * (visit % APG);
         const uint32_t full_phase = (uint32_t)(visit / APG) & 1u;
         const bool more = tile + GROUPS * walk_stride < total_tiles;
+#pragma unroll
+      for (int py = 0; py < SUB; ++py) {
         if (!kAheadInRegisters) {
-            ahead = request(tile);
+            ahead = request(tile, py);
             if (more) prefetch(tile + GROUPS * walk_stride);
         }
         const Ahead cur = ahead;
         const TileCoord t = cur.t;
         const int b = t.b0;
-        if (kAheadInRegisters && more) ahead = request(tile + GROUPS * walk_stride);
+        if (kAheadInRegisters) {
+            if (py + 1 < SUB) ahead = request(tile, py + 1);
+            else if (more) ahead = request(tile + GROUPS * walk_stride, 0);
+        }
         if (kCoefSmem && b != cached_b) {  // group-uniform: per-sample coefficients of every channel -> the group's cache
             float4* coef_a = cache_all + group * 2 * C;
             float4* coef_b = coef_a + C;
@@ -504,7 +515,8 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
 #pragma unroll
         for (int rr = 0; rr < 4; ++rr)
 #pragma unroll
-            for (int ph = 0; ph < NP; ++ph) nz[rr][ph] = cur.nz[rr][ph] * (p.noise ? p.noise_strength : 0.f);
+            for (int ph = 0; ph < NP; ++ph)  // rounded product (never contracted into the bias add: every flavour of the epilogue
+                nz[rr][ph] = __fmul_rn(cur.nz[rr][ph], p.noise ? p.noise_strength : 0.f);  // must round the same way)
         const int own_h = cur.own_h, own_wp = cur.own_w;
         float rgb[4][3];
 #pragma unroll
@@ -517,7 +529,7 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
 #ifdef GANCE_PIPE_STATS
         const long long stat_w0 = clock64();
 #endif
-        mbar_wait(tmem_full_bar + acc, full_phase);
+        if (py == 0) mbar_wait(tmem_full_bar + acc, full_phase);
 #ifdef GANCE_PIPE_STATS
         stat_wait += clock64() - stat_w0;
 #endif
@@ -526,7 +538,7 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
         if (p.batch > 0) {  // ablation: the epilogue only hands the accumulator back
             tcgen05_fence_before();
             __syncwarp();
-            if (lane == 0) {
+            if (lane == 0 && py == SUB - 1) {
                 if (PAIR) mbar_arrive_cluster(leader_empty_base + (uint32_t)(acc * 8));
                 else mbar_arrive(tmem_empty_bar + acc);
             }
@@ -554,7 +566,7 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
             for (int h2 = 0; h2 < 2; ++h2) {
                 uint32_t r[16];
                 tmem_ld_16x256b_x4(tmem_base + ((uint32_t)(quarter * 32 + 16 * h2) << 16) +
-                                       (uint32_t)(acc * N_TILE + chunk * 32), r);
+                                       (uint32_t)(acc * N_TILE + py * C * (ROWS2 ? 1 : 0) + chunk * 32), r);
                 tmem_ld_wait();
 #pragma unroll
                 for (int s = 0; s < 2; ++s) {
@@ -592,7 +604,7 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
                                          : "memory");
                         }
                     } else if (has_out) {
-                        const int h = t.h0 + hl[rr], w = t.w0 + wl[rr];
+                        const int h = t.h0 + image_row(hl[rr], py), w = t.w0 + wl[rr];
                         const int oh = UP ? 2 * h + (phase >> 1) : h, ow = UP ? 2 * w + (phase & 1) : w;
                         // The fragment layout leaves a lane with one channel PAIR (4 bytes) of each of four 8-channel groups.
                         // Stored as they are, a warp store covers 16 bytes in each of 8 pixels - half a 32-byte sector at a
@@ -618,7 +630,7 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
         tcgen05_fence_before();
         if (STAGED) fence_proxy_async_smem();  // this thread's st.shared -> visible to the TMA unit
         __syncwarp();
-        if (lane == 0) {  // accumulator drained
+        if (lane == 0 && py == SUB - 1) {  // accumulator drained
             if (PAIR) mbar_arrive_cluster(leader_empty_base + (uint32_t)(acc * 8));
             else mbar_arrive(tmem_empty_bar + acc);
             if (STAGED) {  // the warp's 8 output rows x 16 pixels x 32 channels: rows 2 * (h0 + 4 * quarter) .., pixel pair w0 ..
@@ -664,6 +676,7 @@ __device__ __forceinline__ void conv_epilogue_frag(const ConvParams& p, int grou
                 flag_nonfinite(p.nonfinite, red, green, blue);
             }
         }
+      }  // py
     }
     if (STAGED && lane == 0) tma_store_wait_read();  // shared memory must outlive the last store's read
 #ifdef GANCE_PIPE_STATS
@@ -1188,6 +1201,172 @@ modconv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_
     }
 }
 
+// ---- two image rows per accumulator row: the 32 -> 32-channel layer (1024^2 Conv1) -------------------------------------------
+// The one-row kernel above issues 18 MMAs of N = 32 per 128 pixels, and a 128 x 32 x 16 tcgen05.mma costs ~59 cycles whatever
+// its N (the A operand is read from shared memory at the same rate; N = 64 measured 52, profiles/r02_ablation.txt): with no
+// epilogue at all that layer needed 0.97 ms. Here accumulator row (g, w) of a 16 x 8 grid holds TWO output pixels, image rows
+// 2g and 2g+1 of a 32 x 8-pixel tile, in columns [0,32) and [32,64). Input row 2g-1+r (r = 0..3) feeds output row 2g through
+// filter row ky = r and output row 2g+1 through ky = r-1, so per (r, kx) ONE MMA multiplies the shifted halo view (8-row groups
+// now spaced by TWO halo rows) with the 64 x 32 weight block [W(ky=r,kx) ; W(ky=r-1,kx)]:
+//   r = 0: N = 32 into columns [0,32)        (only the even row sees input row 2g-1)
+//   r = 1, 2: N = 64                         (weights are kept in shared memory as [kx][ky = 2,1,0] so the two blocks are adjacent)
+//   r = 3: N = 32 into columns [32,64)
+// = 12 MMAs of N = 64 + 12 of N = 32 (+1: the very first r = 1 MMA is split so that columns [32,64) start from zero) per
+// 256 pixels instead of 36 of N = 32, with NO wasted MACs. Every output element accumulates (ky, kx, 16-channel step) in the
+// order of the one-row kernel, so the results are bit-identical to it. The epilogue drains an accumulator as two sub-tiles
+// (conv_epilogue_frag, ROWS2).
+constexpr int kHalo2TileH = 32, kHalo2H = kHalo2TileH + 2;
+constexpr int kHalo2Groups = 3, kHalo2Apg = 2, kHalo2Accs = kHalo2Groups * kHalo2Apg;  // 6 x 64 of the 512 TMEM columns
+constexpr int kHalo2Threads = 64 + kHalo2Groups * kEpilogueThreads;
+constexpr int kHalo2Stages = 4;                                                        // 4 x 256 pixels in flight (8 x 128 before)
+
+template <int STAGES>
+struct Halo2Smem {
+    static constexpr int kRowBytes = 64;                        // 32 channels
+    static constexpr int kBlockBytes = 32 * kRowBytes;          // one tap: 32 output channels x 32 input channels
+    static constexpr int kWeightBytes = 9 * kBlockBytes;
+    static constexpr int kHaloBytes = kHalo2H * kHaloW * kRowBytes;
+    static constexpr int kHaloStride = (kHaloBytes + 1023) / 1024 * 1024;
+    static constexpr int kBarrierOffset = (kWeightBytes + 1023) / 1024 * 1024 + STAGES * kHaloStride;
+    static constexpr int kBytes = kBarrierOffset + (2 * STAGES + 2 * kHalo2Accs + 1) * 8 + 16 + 1024;
+};
+
+template <typename T, int STAGES, bool RGB>
+__global__ void __launch_bounds__(kHalo2Threads, 1)
+modconv3x3_halo2_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
+                        const ConvParams p) {
+    using L = Halo2Smem<STAGES>;
+    constexpr int CIN = 32, C = 32;
+    constexpr uint32_t kTmemCols = 512;
+    static_assert(kHalo2Accs * 2 * C <= 512, "TMEM columns");
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem_w = smem;
+    uint8_t* smem_halo = smem + (L::kWeightBytes + 1023) / 1024 * 1024;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarrierOffset);
+    uint64_t* empty_bar = full_bar + STAGES;
+    uint64_t* tmem_full_bar = empty_bar + STAGES;
+    uint64_t* tmem_empty_bar = tmem_full_bar + kHalo2Accs;
+    uint64_t* weight_bar = tmem_empty_bar + kHalo2Accs;
+    uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(weight_bar + 1);
+
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
+    const int lane = threadIdx.x & 31;
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmap_x);
+        prefetch_tmap(&tmap_w);
+        for (int i = 0; i < STAGES; ++i) {
+            mbar_init(full_bar + i, 1);
+            mbar_init(empty_bar + i, 1);
+        }
+        for (int i = 0; i < kHalo2Accs; ++i) {
+            mbar_init(tmem_full_bar + i, 1);
+            mbar_init(tmem_empty_bar + i, 4);
+        }
+        mbar_init(weight_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_base_slot, kTmemCols);
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_base_slot, 0);
+    const int total_tiles = p.tiles_b * p.tiles_h * p.tiles_w;  // tiles of 32 rows x 8 columns
+
+    if (warp == 0) {
+        const bool leader = elect_one_sync();
+        if (leader) {
+            mbar_expect_tx(weight_bar, L::kWeightBytes);
+            for (int tap = 0; tap < 9; ++tap)  // tap (ky, kx) -> block kx * 3 + (2 - ky)
+                tma_load_2d(smem_w + ((tap % 3) * 3 + (2 - tap / 3)) * L::kBlockBytes, &tmap_w, weight_bar, tap * CIN, 0);
+        }
+        __syncwarp();
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            const TileCoord t = decode_tile(p, tile, 2 * C);
+            mbar_wait(empty_bar + stage, phase ^ 1u);
+            if (leader) {
+                mbar_expect_tx(full_bar + stage, L::kHaloBytes);
+                tma_load_4d(smem_halo + stage * L::kHaloStride, &tmap_x, full_bar + stage, 0, t.w0 - 1, t.h0 - 1, t.b0);
+            }
+            __syncwarp();
+            if (++stage == STAGES) {
+                stage = 0;
+                phase ^= 1u;
+            }
+        }
+    } else if (warp == 1) {
+        const bool leader = elect_one_sync();
+        constexpr bool kHalfOperands = sizeof(T) == 2 && !std::is_same<T, __nv_bfloat16>::value;
+        constexpr uint32_t idesc32 = make_instr_desc(kTileM, C, kHalfOperands);
+        constexpr uint32_t idesc64 = make_instr_desc(kTileM, 2 * C, kHalfOperands);
+        mbar_wait(weight_bar, 0);
+        int stage = 0;
+        uint32_t phase = 0;
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        const uint32_t w_addr = smem_u32(smem_w);
+        const uint32_t halo_addr0 = smem_u32(smem_halo);
+        const uint64_t b_desc0 = make_smem_desc<64>(w_addr);
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            mbar_wait(tmem_empty_bar + acc, acc_phase ^ 1u);
+            mbar_wait(full_bar + stage, phase);
+            tcgen05_fence_after();
+            const uint32_t d_tmem = tmem_base + (uint32_t)(acc * 2 * C);
+            // 8-row groups of the A operand = 8 pixels of one halo row; consecutive groups are TWO halo rows apart
+            const uint64_t a_desc0 = make_smem_desc_sbo<64>(halo_addr0 + (uint32_t)(stage * L::kHaloStride), 2 * kHaloW * L::kRowBytes);
+            if (leader) {
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+#pragma unroll
+                    for (int kx = 0; kx < 3; ++kx) {
+                        const uint64_t a_desc = a_desc0 + (uint64_t)(((r * kHaloW + kx) * L::kRowBytes) >> 4);
+                        // weight blocks of this kx: [W(ky=2) | W(ky=1) | W(ky=0)]
+                        const uint64_t b_kx = b_desc0 + (uint64_t)((kx * 3 * L::kBlockBytes) >> 4);
+#pragma unroll
+                        for (int k = 0; k < CIN / kUmmaK; ++k) {
+                            const uint64_t a = a_desc + (uint64_t)(k * 2);
+                            if (r == 0) {         // W(ky=0) -> even row
+                                umma_bf16(d_tmem, a, b_kx + (uint64_t)((2 * L::kBlockBytes) >> 4) + (uint64_t)(k * 2), idesc32, (kx | k) != 0 ? 1u : 0u);
+                            } else if (r == 3) {  // W(ky=2) -> odd row
+                                umma_bf16(d_tmem + (uint32_t)C, a, b_kx + (uint64_t)(k * 2), idesc32, 1u);
+                            } else if (r == 1 && kx == 0 && k == 0) {  // the odd row's first product: its columns start from zero
+                                umma_bf16(d_tmem, a, b_kx + (uint64_t)((1 * L::kBlockBytes) >> 4), idesc32, 1u);
+                                umma_bf16(d_tmem + (uint32_t)C, a, b_kx + (uint64_t)((2 * L::kBlockBytes) >> 4), idesc32, 0u);
+                            } else {              // [W(ky=r) ; W(ky=r-1)] -> both rows
+                                umma_bf16(d_tmem, a, b_kx + (uint64_t)(((2 - r) * L::kBlockBytes) >> 4) + (uint64_t)(k * 2), idesc64, 1u);
+                            }
+                        }
+                    }
+                }
+                umma_commit(empty_bar + stage);
+                umma_commit(tmem_full_bar + acc);
+            }
+            __syncwarp();
+            if (++stage == STAGES) {
+                stage = 0;
+                phase ^= 1u;
+            }
+            if (++acc == kHalo2Accs) {
+                acc = 0;
+                acc_phase ^= 1u;
+            }
+        }
+    } else {
+        conv_epilogue_frag<T, 2 * C, C, false, RGB, kHalo2Groups, 3, false, kHalo2Apg, false, false, true>(
+            p, (warp - 2) >> 2, warp, lane, total_tiles, tmem_base, tmem_full_bar, tmem_empty_bar);
+    }
+
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tcgen05_fence_after();
+        tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
 // ---- CTA-pair flavour of the halo kernel (cta_group::2), Cin = 64 or 128 ----------------------------------------------------
 // Each CTA of the pair keeps HALF of the weight matrix resident ([K chunk][tap][N/2 rows][64 channels]), which
 //   * halves the B-operand shared-memory reads per SM (N = 128: A 32 + B 32 clk per MMA -> 32 + 16 against 64 clk of math:
@@ -1593,6 +1772,52 @@ static int configure_halo() {
     }
 }
 
+// ---- two-row halo kernel (32 -> 32 channels): tiles of 32 rows x 8 columns ---------------------------------------------------
+static int g_two_rows = 1;  // gance_set_conv_two_rows: 0 sends the 32 -> 32 layer to the one-row kernel (A/B runs, bit-identity tests)
+
+template <typename T>
+static int launch_halo2_typed(const ConvParams& p, const void* x, const void* weight, cudaStream_t stream) {
+    using L = Halo2Smem<kHalo2Stages>;
+    constexpr bool kHalf = std::is_same<T, __half>::value;
+    constexpr int CIN = 32, C = 32;
+    CUtensorMap tmap_x, tmap_w;
+    {
+        cuuint64_t dims[4] = {(cuuint64_t)CIN, (cuuint64_t)p.w_out, (cuuint64_t)p.h_out, (cuuint64_t)p.batch};
+        cuuint64_t strides[3] = {(cuuint64_t)CIN * 2, (cuuint64_t)p.w_out * CIN * 2, (cuuint64_t)p.h_out * p.w_out * CIN * 2};
+        cuuint32_t box[4] = {(cuuint32_t)CIN, (cuuint32_t)kHaloW, (cuuint32_t)kHalo2H, 1u};
+        int rc = make_tmap(&tmap_x, x, kHalf, 4, dims, strides, box, CIN * 2);
+        if (rc != GANCE_OK) return rc;
+    }
+    {
+        cuuint64_t dims[2] = {(cuuint64_t)9 * CIN, (cuuint64_t)C};
+        cuuint64_t strides[1] = {(cuuint64_t)9 * CIN * 2};
+        cuuint32_t box[2] = {(cuuint32_t)CIN, (cuuint32_t)C};
+        int rc = make_tmap(&tmap_w, weight, kHalf, 2, dims, strides, box, CIN * 2);
+        if (rc != GANCE_OK) return rc;
+    }
+    const int total_tiles = p.tiles_b * p.tiles_h * p.tiles_w;
+    const int grid = total_tiles < g_num_sms ? total_tiles : g_num_sms;
+    if (p.rgb_weight != nullptr)
+        modconv3x3_halo2_kernel<T, kHalo2Stages, true><<<grid, kHalo2Threads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
+    else
+        modconv3x3_halo2_kernel<T, kHalo2Stages, false><<<grid, kHalo2Threads, L::kBytes, stream>>>(tmap_x, tmap_w, p);
+    return check_launch("modconv3x3_halo2_kernel");
+}
+
+static int launch_halo2(bool half_operands, const ConvParams& p, const void* x, const void* weight, cudaStream_t stream) {
+    if (half_operands) return launch_halo2_typed<__half>(p, x, weight, stream);
+    return launch_halo2_typed<__nv_bfloat16>(p, x, weight, stream);
+}
+
+static int configure_halo2() {
+    using L = Halo2Smem<kHalo2Stages>;
+    int rc;
+    if ((rc = raise_smem_limit(modconv3x3_halo2_kernel<__nv_bfloat16, kHalo2Stages, false>, L::kBytes, "modconv3x3_halo2")) != GANCE_OK) return rc;
+    if ((rc = raise_smem_limit(modconv3x3_halo2_kernel<__half, kHalo2Stages, false>, L::kBytes, "modconv3x3_halo2")) != GANCE_OK) return rc;
+    if ((rc = raise_smem_limit(modconv3x3_halo2_kernel<__nv_bfloat16, kHalo2Stages, true>, L::kBytes, "modconv3x3_halo2<rgb>")) != GANCE_OK) return rc;
+    return raise_smem_limit(modconv3x3_halo2_kernel<__half, kHalo2Stages, true>, L::kBytes, "modconv3x3_halo2<rgb>");
+}
+
 // ---- CTA-pair halo launches: <N_GEMM, CIN> = <128,64> folded 1024^2 up-convolution, <64,64> 512^2 Conv1, <128,128> 256^2 Conv1
 static int g_halo_pair_clusters[3] = {0, 0, 0};
 
@@ -1745,6 +1970,7 @@ int init_tensor_core_path() {
     if ((rc = tc::configure_halo<128, 64, 2>()) != GANCE_OK) return rc;
     if ((rc = tc::configure_halo<64, 64, tc::kHaloStages64>()) != GANCE_OK) return rc;
     if ((rc = tc::configure_halo<32, 32, tc::kHaloStages32>()) != GANCE_OK) return rc;
+    if ((rc = tc::configure_halo2()) != GANCE_OK) return rc;
     if ((rc = tc::configure_phase_kernels()) != GANCE_OK) return rc;
     if ((rc = tc::configure_fused_kernels()) != GANCE_OK) return rc;
     if ((rc = tc::configure_fused_pair_kernels()) != GANCE_OK) return rc;
@@ -1853,6 +2079,12 @@ static int launch_tensor_core_conv(const char* who, const void* x, int dtype, in
             return tc::launch_halo_pair<128, 64, 3, true>(half_operands, p, x, weight, tc::g_halo_pair_clusters[0], s);
         if (c_in == 64 && c_out == 64 && halo_pair_ok(1))
             return tc::launch_halo_pair<64, 64, 4, false>(half_operands, p, x, weight, tc::g_halo_pair_clusters[1], s);
+        if (c_in == 32 && tc::g_two_rows != 0 && h_out % tc::kHalo2TileH == 0) {  // two image rows per accumulator row
+            p.tile_h = tc::kHalo2TileH; p.tile_hw_log2 = ilog2(p.tile_w * p.tile_h);
+            p.tiles_h = h_out / p.tile_h;
+            set_tile_logs();
+            return tc::launch_halo2(half_operands, p, x, weight, s);
+        }
         if (c_in == 32) return tc::launch_halo<32, 32, tc::kHaloStages32>(half_operands, p, x, weight, s);
         if (c_out == 128) return tc::launch_halo<128, 64, 2>(half_operands, p, x, weight, s);
         return tc::launch_halo<64, 64, tc::kHaloStages64>(half_operands, p, x, weight, s);
@@ -1897,6 +2129,12 @@ extern "C" int gance_debug_pipe_stats(long long* buffer) {
 extern "C" int gance_set_conv_pairing(int mode) {
     const int before = tc::g_pair_mode;
     tc::g_pair_mode = mode < 0 ? 0 : (mode > 2 ? 2 : mode);
+    return before;
+}
+
+extern "C" int gance_set_conv_two_rows(int enabled) {
+    const int before = tc::g_two_rows;
+    tc::g_two_rows = enabled != 0 ? 1 : 0;
     return before;
 }
 

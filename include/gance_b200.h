@@ -79,6 +79,11 @@ int gance_set_nonfinite_flag(int* device_flag);
  * least one work item per co-resident pair; 2 = CTA pairs whenever the shape is eligible (tests: small shapes, odd tile
  * counts). Results are the same in every mode. Process-wide, read at launch time; returns the previous mode. */
 int gance_set_conv_pairing(int mode);
+/* Tuning switch (no counterpart in the reference): 1 (default) = the 32 -> 32-channel SAME convolution (1024^2 Conv1 of
+ * config-f) runs with TWO image rows per accumulator row (N = 64 MMAs, tiles of 32 x 8 pixels) when H % 32 == 0; 0 = one row
+ * per accumulator row (N = 32 MMAs, tiles of 16 x 8). Results are bit-identical. Process-wide, read at launch time; returns
+ * the previous setting. */
+int gance_set_conv_two_rows(int enabled);
 
 /* ---- G_mapping + truncation ------------------------------------------------------------------
  * networks_stylegan2.G_mapping + the 'Truncation' block of G_main, as run by Gs.run

@@ -577,6 +577,46 @@ def _fused_conv_torgb_case(lib, mode, cin, cout, side, batch, last):
     else:
         ulp = 2.0 ** -8 if mode == "bf16" else 2.0 ** -11
         assert rel_err(out.permute(0, 3, 1, 2), want_x) < 2 * ulp
+    return y_out, frames, out
+
+
+@contextlib.contextmanager
+def conv_two_rows(lib, enabled):
+    """gance_set_conv_two_rows for the duration of a block (the 32 -> 32-channel halo kernel: N = 64 or N = 32 MMAs)."""
+    before = lib.gance_set_conv_two_rows(enabled)
+    try:
+        yield
+    finally:
+        lib.gance_set_conv_two_rows(before)
+
+
+@pytest.mark.parametrize("mode", ["bf16", "fp16"])
+@pytest.mark.parametrize("side,batch,last", [(32, 3, True), (64, 2, True), (64, 1, False), (96, 2, True), (32, 5, False)])
+def test_two_row_halo_kernel_matches_oracle_and_the_one_row_kernel(lib, mode, side, batch, last):
+    """modconv3x3_halo2_kernel (32 -> 32 channels, two image rows per accumulator row: N = 64 / N = 32 MMAs over a
+    (32+2) x (8+2) halo box, accumulators drained as two sub-tiles) with the fused ToRGB: against the oracle, and bit for
+    bit against the one-row kernel (same accumulation order per output element). Side 96 = 3 x 12 tiles."""
+    with conv_two_rows(lib, 1):
+        y2, f2, o2 = _fused_conv_torgb_case(lib, mode, 32, 32, side, batch, last)
+    with conv_two_rows(lib, 0):
+        y1, f1, o1 = _fused_conv_torgb_case(lib, mode, 32, 32, side, batch, last)
+    assert torch.equal(y2, y1) and torch.equal(f2, f1)
+    if not last:
+        assert torch.equal(o2, o1)
+
+
+@pytest.mark.parametrize("mode", ["bf16", "fp16"])
+@pytest.mark.parametrize("side,batch", [(64, 2), (32, 1), (160, 1)])
+def test_two_row_halo_kernel_plain_convolution(lib, mode, side, batch):
+    """The same kernel without ToRGB (gance_modconv3x3, 32 -> 32 channels): oracle + bit-identity with the one-row kernel."""
+    ulp = 2.0 ** -8 if mode == "bf16" else 2.0 ** -11
+    with conv_two_rows(lib, 1):
+        got2, want = _run_modconv(lib, mode, 32, 32, side, batch, 1)
+    with conv_two_rows(lib, 0):
+        got1, _ = _run_modconv(lib, mode, 32, 32, side, batch, 1)
+    assert not torch.isnan(got2.float()).any(), "kernel left output unwritten"
+    assert rel_err(got2, want) < 2 * ulp
+    assert torch.equal(got2, got1)
 
 
 def _philox4x32_10(counter: np.ndarray, key: np.ndarray) -> np.ndarray:

@@ -24,6 +24,7 @@ def main() -> None:
     ap.add_argument("--noise", default="const", choices=["const", "random", "none"])
     ap.add_argument("--library", default=None, help="an alternative build of the library (measurement variants of csrc/build.py)")
     ap.add_argument("--pairing", type=int, default=None, choices=[0, 1, 2], help="gance_set_conv_pairing")
+    ap.add_argument("--two-rows", type=int, default=None, choices=[0, 1], help="gance_set_conv_two_rows")
     ap.add_argument("--fused-min-side", type=int, default=None, help="GeneratorOnDevice.fused_min_in_resolution (A/B)")
     ap.add_argument("--only", default=None, help="print only layers whose name contains this")
     args = ap.parse_args()
@@ -31,6 +32,8 @@ def main() -> None:
         _lib.LIBRARY_PATH = Path(args.library).resolve()
     if args.pairing is not None:
         _lib.load_library().gance_set_conv_pairing(args.pairing)
+    if args.two_rows is not None:
+        _lib.load_library().gance_set_conv_two_rows(args.two_rows)
     if args.fused_min_side is not None:
         GeneratorOnDevice.fused_min_in_resolution = args.fused_min_side
     device = torch.device("cuda", 0)
