@@ -528,7 +528,7 @@ def main():
             except Exception:  # pylint: disable=broad-except
                 traffic = None
     roofline = {
-        "bound": "tensor", "kernel": "modconv3x3_{tc,pair,halo,halo_pair}_kernel + upconv_fused{,_pair}_kernel (every modulated-convolution launch of a step: tcgen05 implicit GEMMs, cta_group::1 and ::2, with fused demod/noise/bias/lrelu/FIR/ToRGB/skip/uint8 epilogues)",
+        "bound": "tensor", "kernel": "modconv3x3_{tc,pair,halo,halo2,halo_pair}_kernel + upconv_fused{,_pair}_kernel (every modulated-convolution launch of a step: tcgen05 implicit GEMMs, cta_group::1 and ::2, with fused demod/noise/bias/lrelu/FIR/ToRGB/skip/uint8 epilogues)",
         "achieved": achieved_tflops, "peak": burst_tflops, "unit": "TFLOP/s", "frac": achieved_tflops / burst_tflops,
         "peak_source": f"bf16_tflops (burst: the conv launches are timed with CUDA events inside five eager 8 ms passes right after the timed steps), {peak_source}",
         "frac_of_sustained_peak": achieved_tflops / sustained_tflops, "sustained_peak": sustained_tflops,

@@ -11,7 +11,7 @@ $CMD > gpurun_out/${tag}_plain.log 2>&1 &&
 ncu --metrics $METRICS --clock-control none -c 700 --csv --log-file gpurun_out/${tag}_launches.csv $CMD > gpurun_out/${tag}_ncu1.log 2>&1
 echo "launch list rc $?"
 $CMD > gpurun_out/${tag}_plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:"halo_kernel|halo_pair_kernel|upconv_fused" -s 18 -c 10 \
+ncu --set full --clock-control none --import-source on -k regex:"halo_kernel|halo2_kernel|halo_pair_kernel|upconv_fused" -s 18 -c 10 \
     -o gpurun_out/${tag}_convs $CMD > gpurun_out/${tag}_ncu2.log 2>&1
 echo "full capture rc $?"
 ls -la gpurun_out | head -20

@@ -12,7 +12,7 @@ import re
 import sys
 from collections import OrderedDict, defaultdict
 
-CONV = re.compile(r"modconv3x3_(tc|pair|halo|halo_pair)_kernel|upconv_fused(_pair)?_kernel|upconv_phase|modconv3x3_tf32x3")
+CONV = re.compile(r"modconv3x3_(tc|pair|halo|halo2|halo_pair)_kernel|upconv_fused(_pair)?_kernel|upconv_phase|modconv3x3_tf32x3")
 TIME, READ, WRITE = "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum"
 TENSOR = "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed"
 ISSUE = "smsp__issue_active.avg.pct_of_peak_sustained_elapsed"
