@@ -315,3 +315,25 @@ def test_stopping_an_interface_keeps_the_generator_buffers_and_unload_releases_i
         other.stop_function()  # idempotent
         network_functions.release_idle_buffers()
         assert a in released
+
+
+@pytest.mark.parametrize("resolution,folded", [(1024, {1024}), (512, set()), (256, set())])
+def test_up_convolution_kernel_choice_per_layer(resolution, folded):
+    """Which kernel each up-convolution of a config-f generator runs as (GeneratorOnDevice._up_form, no GPU needed): the
+    fused form wherever Cout % 64 == 0 - from the 4^2 -> 8^2 layer on - and the folded form for the 32-channel 1024^2 layer;
+    a forced form applies only where the shape is eligible."""
+    from gance_b200.networks.generator_spec import GeneratorSpec, synthesis_layers
+    from gance_b200.synthesis import GeneratorOnDevice
+
+    convs, _ = synthesis_layers(GeneratorSpec(resolution))
+    ups = [conv for conv in convs if conv.up]
+    assert [conv.out_resolution for conv in ups] == [2 ** r for r in range(3, resolution.bit_length())]
+    chooser = GeneratorOnDevice.__new__(GeneratorOnDevice)  # _up_form reads nothing but these two attributes
+    chooser.forced_up_form = ""
+    assert {conv.out_resolution for conv in ups if chooser._up_form(conv) == "folded"} == folded
+    assert all(chooser._up_form(conv) == "fused" for conv in ups if conv.out_resolution not in folded)
+    chooser.forced_up_form = "phase"  # needs an input side >= 32 and 64-channel multiples
+    assert {conv.out_resolution for conv in ups if chooser._up_form(conv) == "phase"} == \
+        {conv.out_resolution for conv in ups if conv.in_resolution >= 32 and conv.out_channels % 64 == 0}
+    chooser.forced_up_form = "folded"
+    assert all(chooser._up_form(conv) == "folded" for conv in ups)
